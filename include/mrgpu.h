@@ -1,0 +1,175 @@
+/*
+ * mrgpu.h -- C ABI of the B200 data plane that stands behind lua-mapreduce's
+ * task-module API (map -> combine -> partition -> shuffle -> sort/merge -> reduce).
+ *
+ * The reference has no FFI: its data plane is Lua (mapreduce/job.lua) called from
+ * mapreduce/worker.lua:73.  Each entry point below names the reference code it
+ * replaces (paths relative to the reference root); INTEGRATION.md shows the Lua
+ * C-API / LuaJIT-FFI binding a maintainer would add at those seams.
+ *
+ * Conventions: plain C types only; every function returns MR_OK (0) or an error
+ * code, with the text available from mr_last_error(); no exceptions or longjmp
+ * cross the boundary, so Lua glue turns a non-zero return into error(msg) and the
+ * reference's BROKEN/FAILED retry machinery (job.lua:322-342, worker.lua:116-137)
+ * is unchanged.  One context per process per GPU; calls on a context must be
+ * serialised by the caller (a Lua worker is single-threaded, worker.lua:54-86).
+ * Input buffers are borrowed only for the duration of the call.
+ */
+#ifndef MRGPU_H
+#define MRGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRGPU_ABI_VERSION 1
+
+typedef struct mr_ctx mr_ctx;
+typedef struct mr_result mr_result;
+
+enum mr_status {
+    MR_OK = 0,
+    MR_ERR_INVALID = 1,     /* bad argument or call order */
+    MR_ERR_CUDA = 2,        /* CUDA runtime error (sticky: destroy and recreate the context) */
+    MR_ERR_NOMEM = 3,       /* arena / key capacity exceeded */
+    MR_ERR_OVERFLOW = 4,    /* hash table full or a token longer than MR_MAX_TOKEN_BYTES */
+    MR_ERR_UNSUPPORTED = 5, /* task module asks for a map/partition/reduce kind not built */
+    MR_ERR_END = 6          /* mr_result_next: no more rows */
+};
+
+/* What the task module's `native` descriptor may name.  The Lua functions stay the
+ * semantic definition; a module without a descriptor is simply not accelerated. */
+enum mr_map_kind { MR_MAP_TOKENIZE_WS = 0 };          /* examples/WordCount/mapfn.lua:3-9 */
+enum mr_reduce_kind { MR_REDUCE_SUM_U64 = 0 };        /* examples/WordCount/reducefn.lua:1-5 */
+enum mr_partition_kind { MR_PARTITION_FNV1_LUA52 = 0 }; /* examples/WordCount/partitionfn.lua:8-16 */
+
+#define MR_MAX_TOKEN_BYTES ((1u << 26) - 1)
+
+typedef struct mr_config {
+    uint32_t struct_size;   /* sizeof(mr_config), for ABI growth */
+    int32_t device;         /* CUDA device ordinal */
+    uint32_t num_reducers;  /* NUM_REDUCERS of partitionfn.lua:2 (15 in-tree, 10 in README.md:59) */
+    uint32_t map_kind, reduce_kind, partition_kind;
+    uint64_t arena_bytes;   /* capacity for the input splits of one job, resident in HBM */
+    uint64_t max_keys;      /* capacity for distinct keys of one job (0 = derive from arena) */
+    uint64_t table_slots;   /* global hash-table slots, power of two (0 = 2 x max_keys rounded up) */
+    void *stream;           /* cudaStream_t to run on, NULL = a private stream */
+    uint32_t world_size;    /* ranks taking part in the shuffle (1 = no shuffle) */
+    uint32_t rank;
+} mr_config;
+
+typedef struct mr_job_info {
+    uint64_t n_keys;        /* rows this rank holds after reduce (distinct keys it owns) */
+    uint64_t n_tokens;      /* emits seen by this rank's map side */
+    uint64_t input_bytes;   /* split bytes mapped by this rank (padding excluded) */
+    uint64_t key_bytes;     /* sum of len(key) over this rank's rows */
+    uint64_t map_keys;      /* distinct keys after this rank's combine, before the shuffle */
+    uint32_t tie_rounds;    /* extra ordering rounds needed for keys equal in their first 7 bytes */
+    uint32_t flags;
+} mr_job_info;
+
+/* Device-side layout of the reduced rows, in the reference's final order
+ * (partition ascending, key ascending: server.lua:365, utils.lua:214).  All
+ * pointers are device pointers owned by the context, valid until mr_job_begin. */
+typedef struct mr_device_rows {
+    uint64_t n;
+    const uint32_t *part;      /* [n] */
+    const uint64_t *count;     /* [n] */
+    const uint64_t *key_off;   /* [n+1] */
+    const uint8_t *key_bytes;  /* [key_off[n]] */
+    const uint64_t *part_begin; /* [num_reducers+1] row index where each partition starts */
+} mr_device_rows;
+
+typedef struct mr_stats {
+    float map_ms;           /* CUDA-event time of the last mr_map_finish */
+    float reduce_ms;        /* CUDA-event time of the last mr_reduce_all */
+    uint64_t h2d_bytes;     /* bytes copied host->device by mr_map_split since mr_job_begin */
+    uint64_t d2h_bytes;     /* bytes copied device->host by result calls since mr_job_begin */
+    uint64_t launches;      /* kernels of this library launched since mr_job_begin */
+} mr_stats;
+
+/* Context = what one worker process keeps between jobs (job.lua:64-65 caches its
+ * modules per process the same way).  Allocates all device memory up front. */
+int mr_ctx_create(const mr_config *cfg, mr_ctx **out);
+void mr_ctx_destroy(mr_ctx *ctx);
+/* Text of the last error on ctx; ctx == NULL gives the last mr_ctx_create failure. */
+const char *mr_last_error(const mr_ctx *ctx);
+int mr_abi_version(void);
+
+/* Start a job (task iteration).  keep_input != 0 keeps the splits already staged
+ * in HBM (the "loop" iteration of server.lua:386-402 with map affinity,
+ * task.lua:279-293) and only clears keys and results. */
+int mr_job_begin(mr_ctx *ctx, int keep_input);
+
+/* Map job for one split: replaces the closure of job.lua:166-227 for
+ * MR_MAP_TOKENIZE_WS, i.e. mapfn.lua:3-9 + emit (job.lua:83-97).  The bytes are
+ * the content of the file the reference's taskfn names (taskfn.lua:8-11); they
+ * are staged into the HBM arena (host pointer: host->device copy inside the
+ * call).  Tokens never span splits. */
+int mr_map_split(mr_ctx *ctx, uint64_t split_id, const void *bytes, uint64_t n);
+/* Same with bytes already in device memory (device->device copy). */
+int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, uint64_t n);
+
+/* Runs tokenise + hash-combine over every split staged since the last
+ * mr_map_finish, then the partitioner on the distinct keys: job.lua:182-215
+ * (emit, combiner, partitionfn) for all staged map jobs at once.  Asynchronous. */
+int mr_map_finish(mr_ctx *ctx);
+
+/* Sort/merge + reduce of every partition this rank owns: replaces
+ * utils.keys_sorted (utils.lua:123-128), utils.merge_iterator + heap
+ * (utils.lua:206-271, heap.lua) and the reduce loop job.lua:264-284.
+ * Asynchronous; rows stay in HBM. */
+int mr_reduce_all(mr_ctx *ctx);
+
+/* Waits for the job's device work, finishes rare slow paths, fills info. */
+int mr_job_sync(mr_ctx *ctx, mr_job_info *info);
+
+/* Device view of the rows (after mr_job_sync). */
+int mr_device_rows_get(mr_ctx *ctx, mr_device_rows *rows);
+
+/* Bulk device->host copy of all rows (after mr_job_sync).  Any pointer may be
+ * NULL to skip that array.  key_bytes must hold info.key_bytes bytes. */
+int mr_rows_fetch(mr_ctx *ctx, uint32_t *part, uint64_t *count, uint64_t *key_off,
+                  uint8_t *key_bytes, uint64_t *part_begin);
+
+/* Result cursor of one partition = reading the file result.P<part> the reduce job
+ * writes (job.lua:272-273,287) the way server_final does (server.lua:358-383):
+ * keys ascending.  A partition that received no key yields an empty cursor (the
+ * reference creates no file for it, server.lua:297-324).  key stays valid until
+ * mr_result_release. */
+int mr_reduce_partition(mr_ctx *ctx, uint32_t part, mr_result **out);
+int mr_result_next(mr_result *res, const char **key, uint64_t *klen, uint64_t *count);
+void mr_result_release(mr_result *res);
+
+/* Shuffle seam (job.lua:208-221 write, job.lua:253-260 read): after
+ * mr_map_finish, export this rank's combined (key, count) records grouped by
+ * owner rank (owner = partition mod world_size); the caller moves the bytes
+ * (NCCL all-to-all) and imports what it received before mr_reduce_all.
+ * Record stream per destination: fixed 16-byte records {key word, count} followed
+ * by the bytes of long keys.  Pointers are device pointers owned by the context. */
+typedef struct mr_shuffle_plan {
+    const uint8_t *send_base;  /* device buffer holding every outgoing segment */
+    const uint64_t *send_off;  /* host array [world_size+1]: byte offsets per destination */
+    const uint64_t *send_nrec; /* host array [world_size]: records per destination */
+} mr_shuffle_plan;
+int mr_shuffle_export(mr_ctx *ctx, mr_shuffle_plan *plan);
+/* Reserve room for `bytes` incoming bytes; returns the device pointer to receive into. */
+int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr);
+/* recv_off: host array [world_size+1] of byte offsets per source inside the receive
+ * buffer; recv_nrec: host array [world_size] of records per source (the sender's
+ * send_nrec for this rank, exchanged with the sizes). */
+int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *recv_nrec);
+
+int mr_stats_get(mr_ctx *ctx, mr_stats *out);
+
+/* Partition id of one key on the host, same arithmetic as the device code
+ * (partitionfn.lua:8-16 in IEEE binary64).  For glue-side checks. */
+uint32_t mr_partition_of(const void *key, uint64_t klen, uint32_t num_reducers);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MRGPU_H */

@@ -1,0 +1,238 @@
+"""ctypes binding of include/mrgpu.h (libmrgpu.so).
+
+There is no CPU path: if the CUDA library cannot be loaded, or no sm_100 device is
+present, every compute entry fails loudly (NativeError).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+MR_OK, MR_ERR_INVALID, MR_ERR_CUDA, MR_ERR_NOMEM, MR_ERR_OVERFLOW, MR_ERR_UNSUPPORTED, MR_ERR_END = range(7)
+MR_MAP_TOKENIZE_WS = 0
+MR_REDUCE_SUM_U64 = 0
+MR_PARTITION_FNV1_LUA52 = 0
+
+# every symbol include/mrgpu.h declares
+EXPORTS = (
+    "mr_abi_version", "mr_ctx_create", "mr_ctx_destroy", "mr_last_error", "mr_job_begin",
+    "mr_map_split", "mr_map_split_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
+    "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
+    "mr_result_release", "mr_shuffle_export", "mr_shuffle_recv_buffer", "mr_shuffle_import",
+    "mr_stats_get", "mr_partition_of",
+)
+
+
+class NativeError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"mrgpu error {code}: {msg}")
+        self.code = code
+
+
+class Config(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("num_reducers", C.c_uint32),
+                ("map_kind", C.c_uint32), ("reduce_kind", C.c_uint32), ("partition_kind", C.c_uint32),
+                ("arena_bytes", C.c_uint64), ("max_keys", C.c_uint64), ("table_slots", C.c_uint64),
+                ("stream", C.c_void_p), ("world_size", C.c_uint32), ("rank", C.c_uint32)]
+
+
+class JobInfo(C.Structure):
+    _fields_ = [("n_keys", C.c_uint64), ("n_tokens", C.c_uint64), ("input_bytes", C.c_uint64),
+                ("key_bytes", C.c_uint64), ("map_keys", C.c_uint64), ("tie_rounds", C.c_uint32),
+                ("flags", C.c_uint32)]
+
+
+class DeviceRows(C.Structure):
+    _fields_ = [("n", C.c_uint64), ("part", C.c_void_p), ("count", C.c_void_p),
+                ("key_off", C.c_void_p), ("key_bytes", C.c_void_p), ("part_begin", C.c_void_p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("map_ms", C.c_float), ("reduce_ms", C.c_float), ("h2d_bytes", C.c_uint64),
+                ("d2h_bytes", C.c_uint64), ("launches", C.c_uint64)]
+
+
+class ShufflePlan(C.Structure):
+    _fields_ = [("send_base", C.c_void_p), ("send_off", C.POINTER(C.c_uint64)),
+                ("send_nrec", C.POINTER(C.c_uint64))]
+
+
+_lib = None
+
+
+def library_path():
+    return _build.LIB_GPU
+
+
+def load(build_if_missing=True):
+    """Loads libmrgpu.so (building it in-tree with nvcc when the sources are newer)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_GPU
+    if build_if_missing:
+        try:
+            path = _build.build_gpu()
+        except Exception as e:  # no nvcc on this box: use the prebuilt library if it is there
+            if not os.path.exists(path):
+                raise NativeError(-1, f"libmrgpu.so is missing and cannot be built: {e}")
+    if not os.path.exists(path):
+        raise NativeError(-1, "libmrgpu.so is missing; run `python __graft_entry__.py build`")
+    L = C.CDLL(path)
+    vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
+    L.mr_abi_version.restype = C.c_int
+    L.mr_ctx_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    L.mr_ctx_destroy.argtypes = [vp]
+    L.mr_ctx_destroy.restype = None
+    L.mr_last_error.argtypes = [vp]
+    L.mr_last_error.restype = C.c_char_p
+    L.mr_job_begin.argtypes = [vp, C.c_int]
+    L.mr_map_split.argtypes = [vp, u64, vp, u64]
+    L.mr_map_split_device.argtypes = [vp, u64, vp, u64]
+    L.mr_map_finish.argtypes = [vp]
+    L.mr_reduce_all.argtypes = [vp]
+    L.mr_job_sync.argtypes = [vp, C.POINTER(JobInfo)]
+    L.mr_device_rows_get.argtypes = [vp, C.POINTER(DeviceRows)]
+    L.mr_rows_fetch.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.mr_reduce_partition.argtypes = [vp, u32, C.POINTER(vp)]
+    L.mr_result_next.argtypes = [vp, C.POINTER(vp), C.POINTER(u64), C.POINTER(u64)]
+    L.mr_result_release.argtypes = [vp]
+    L.mr_result_release.restype = None
+    L.mr_shuffle_export.argtypes = [vp, C.POINTER(ShufflePlan)]
+    L.mr_shuffle_recv_buffer.argtypes = [vp, u64, C.POINTER(vp)]
+    L.mr_shuffle_import.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
+    L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
+    L.mr_partition_of.argtypes = [C.c_char_p, u64, u32]
+    L.mr_partition_of.restype = u32
+    _lib = L
+    return L
+
+
+class Rows:
+    """Host copy of the reduced rows, in the reference's final order."""
+
+    def __init__(self, part, count, key_off, key_bytes, part_begin):
+        self.part, self.count, self.key_off = part, count, key_off
+        self.key_bytes, self.part_begin = key_bytes, part_begin
+
+    @property
+    def n(self):
+        return len(self.part)
+
+    def keys(self):
+        kb = self.key_bytes.tobytes()
+        off = self.key_off
+        return [kb[int(off[i]):int(off[i + 1])] for i in range(self.n)]
+
+
+class Context:
+    """One per worker process per GPU (include/mrgpu.h: mr_ctx)."""
+
+    def __init__(self, num_reducers, arena_bytes, max_keys=0, table_slots=0, device=0, stream=None,
+                 world_size=1, rank=0):
+        self._L = load()
+        cfg = Config(C.sizeof(Config), device, num_reducers, MR_MAP_TOKENIZE_WS, MR_REDUCE_SUM_U64,
+                     MR_PARTITION_FNV1_LUA52, arena_bytes, max_keys, table_slots, stream, world_size, rank)
+        h = C.c_void_p()
+        rc = self._L.mr_ctx_create(C.byref(cfg), C.byref(h))
+        if rc != MR_OK:
+            raise NativeError(rc, (self._L.mr_last_error(None) or b"").decode())
+        self._h = h
+        self.num_reducers, self.world_size, self.rank = num_reducers, world_size, rank
+
+    def _ck(self, rc):
+        if rc != MR_OK:
+            raise NativeError(rc, (self._L.mr_last_error(self._h) or b"").decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.mr_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def job_begin(self, keep_input=False):
+        self._ck(self._L.mr_job_begin(self._h, int(keep_input)))
+
+    def map_split(self, split_id, data):
+        """data: bytes-like or a uint8 numpy array (host memory)."""
+        arr = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
+        self._ck(self._L.mr_map_split(self._h, split_id, arr.ctypes.data if arr.size else None, arr.size))
+
+    def map_split_ptr(self, split_id, ptr, n, device=False):
+        fn = self._L.mr_map_split_device if device else self._L.mr_map_split
+        self._ck(fn(self._h, split_id, ptr, n))
+
+    def map_finish(self):
+        self._ck(self._L.mr_map_finish(self._h))
+
+    def reduce_all(self):
+        self._ck(self._L.mr_reduce_all(self._h))
+
+    def job_sync(self):
+        info = JobInfo()
+        self._ck(self._L.mr_job_sync(self._h, C.byref(info)))
+        return info
+
+    def device_rows(self):
+        r = DeviceRows()
+        self._ck(self._L.mr_device_rows_get(self._h, C.byref(r)))
+        return r
+
+    def rows(self, out=None):
+        """Bulk copy of all rows to host numpy arrays (optionally into preallocated `out`)."""
+        info = self.job_sync()
+        n, kb = int(info.n_keys), int(info.key_bytes)
+        if out is None:
+            out = Rows(np.empty(n, np.uint32), np.empty(n, np.uint64), np.empty(n + 1, np.uint64),
+                       np.empty(kb, np.uint8), np.empty(self.num_reducers + 1, np.uint64))
+        self._ck(self._L.mr_rows_fetch(self._h, out.part.ctypes.data, out.count.ctypes.data,
+                                       out.key_off.ctypes.data, out.key_bytes.ctypes.data,
+                                       out.part_begin.ctypes.data))
+        return out
+
+    def partition_cursor(self, part):
+        """Iterates (key bytes, count) of one partition, keys ascending (result.P<part>)."""
+        h = C.c_void_p()
+        self._ck(self._L.mr_reduce_partition(self._h, part, C.byref(h)))
+        try:
+            key, klen, cnt = C.c_void_p(), C.c_uint64(), C.c_uint64()
+            while True:
+                rc = self._L.mr_result_next(h, C.byref(key), C.byref(klen), C.byref(cnt))
+                if rc == MR_ERR_END:
+                    break
+                self._ck(rc)
+                yield C.string_at(key.value, klen.value), int(cnt.value)
+        finally:
+            self._L.mr_result_release(h)
+
+    def stats(self):
+        s = Stats()
+        self._ck(self._L.mr_stats_get(self._h, C.byref(s)))
+        return s
+
+    # ---- shuffle seam
+    def shuffle_export(self):
+        plan = ShufflePlan()
+        self._ck(self._L.mr_shuffle_export(self._h, C.byref(plan)))
+        W = self.world_size
+        off = np.array([plan.send_off[i] for i in range(W + 1)], dtype=np.uint64)
+        nrec = np.array([plan.send_nrec[i] for i in range(W)], dtype=np.uint64)
+        return plan.send_base, off, nrec
+
+    def shuffle_recv_buffer(self, nbytes):
+        p = C.c_void_p()
+        self._ck(self._L.mr_shuffle_recv_buffer(self._h, nbytes, C.byref(p)))
+        return p.value
+
+    def shuffle_import(self, recv_off, recv_nrec):
+        ro = np.ascontiguousarray(recv_off, dtype=np.uint64)
+        rn = np.ascontiguousarray(recv_nrec, dtype=np.uint64)
+        self._ck(self._L.mr_shuffle_import(self._h, ro.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                           rn.ctypes.data_as(C.POINTER(C.c_uint64))))
+
+
+def partition_of(key: bytes, num_reducers: int) -> int:
+    return load().mr_partition_of(key, len(key), num_reducers)

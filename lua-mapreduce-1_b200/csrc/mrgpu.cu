@@ -1,0 +1,817 @@
+// mrgpu.cu -- context, staging, launch sequencing and the C ABI of include/mrgpu.h.
+// Device code lives in map_kernel.cuh (tokenise + combine) and reduce_kernels.cuh
+// (partition, radix sort, tie resolution, segmented reduce, rows).  sm_100a only.
+#include "mrgpu.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "map_kernel.cuh"
+#include "reduce_kernels.cuh"
+
+using namespace mr;
+
+static_assert(SORT_THREADS == RADIX_BINS, "one thread per radix bin");
+
+namespace {
+
+std::string g_create_error;
+
+constexpr uint64_t ARENA_SLACK = SEG + SEG_AHEAD + 256;
+
+inline uint64_t round_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+__global__ void ctl_init_kernel(Ctl *ctl)
+{
+    // everything else was zeroed by the memset before this launch
+    ctl->and_lo = ~0ull;
+    ctl->and_hi = ~0u;
+}
+
+__global__ void ctl_set_n_kernel(Ctl *ctl, unsigned long long n) { ctl->n = n; }
+
+// shuffle: count records / long bytes per destination rank
+__global__ void __launch_bounds__(256) export_count_kernel(EntryArrays ent, uint32_t world,
+                                                           unsigned long long *nrec,
+                                                           unsigned long long *nbytes, const Ctl *ctl)
+{
+    const uint64_t n = ctl->n;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint32_t d = ent.part[i] % world;
+        atomicAdd(&nrec[d], 1ull);
+        uint64_t k = ent.key[i];
+        if (key_is_long(k)) atomicAdd(&nbytes[d], (unsigned long long)key_len(k));
+    }
+}
+
+// segment layout per destination: [records 16 B each][long-key bytes]; long keys are
+// rewritten to offsets relative to the start of the segment's byte block
+__global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, const uint8_t *bytes,
+                                                             uint32_t world, uint8_t *send,
+                                                             const unsigned long long *seg_off,
+                                                             const unsigned long long *nrec_total,
+                                                             unsigned long long *rec_cur,
+                                                             unsigned long long *byte_cur, const Ctl *ctl)
+{
+    const uint64_t n = ctl->n;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint32_t d = ent.part[i] % world;
+        uint64_t k = ent.key[i];
+        uint8_t *seg = send + seg_off[d];
+        unsigned long long r = atomicAdd(&rec_cur[d], 1ull);
+        if (key_is_long(k)) {
+            uint32_t len = key_len(k);
+            unsigned long long bo = atomicAdd(&byte_cur[d], (unsigned long long)len);
+            uint8_t *dst = seg + nrec_total[d] * 16 + bo;
+            uint64_t off = key_off(k);
+            for (uint32_t j = 0; j < len; ++j) dst[j] = bytes[off + j];
+            k = make_long_key(bo, len);
+        }
+        ((unsigned long long *)seg)[2 * r] = k;
+        ((unsigned long long *)seg)[2 * r + 1] = ent.cnt[i];
+    }
+}
+
+// received segment -> entries; long keys rebased to offsets inside the receive buffer
+__global__ void __launch_bounds__(256) import_segment_kernel(const uint8_t *recv, uint64_t seg_off,
+                                                             uint64_t nrec, uint64_t ent_base,
+                                                             EntryArrays ent)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const unsigned long long *rec = (const unsigned long long *)(recv + seg_off);
+    const uint64_t bytes_at = seg_off + nrec * 16;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += stride) {
+        uint64_t k = rec[2 * i];
+        if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k));
+        ent.key[ent_base + i] = k;
+        ent.cnt[ent_base + i] = rec[2 * i + 1];
+    }
+}
+
+__global__ void __launch_bounds__(256) check_key_bytes_kernel(Ctl *ctl, unsigned long long cap)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0 && ctl->key_bytes > cap) atomicOr(&ctl->err, ERR_KEYS_FULL);
+}
+
+} // namespace
+
+struct mr_result {
+    mr_ctx *ctx;
+    uint64_t first, n, cur;
+    std::vector<uint64_t> count, key_off;
+    std::vector<uint8_t> key_bytes;
+};
+
+struct mr_ctx {
+    mr_config cfg{};
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    int sm_count = 148;
+    int map_variant = 0;
+
+    // input arena
+    uint8_t *d_arena = nullptr;
+    uint64_t arena_cap = 0;   // usable bytes (allocation has ARENA_SLACK more)
+    uint64_t used = 0;        // bytes staged so far (end of the last split)
+    uint64_t mapped_segs = 0; // segments already consumed by mr_map_finish
+    uint64_t input_bytes = 0;
+    bool any_split = false;
+
+    // tables and entries
+    GEntry *d_gtab = nullptr;
+    uint64_t slots = 0;
+    uint64_t max_keys = 0;
+    EntryArrays ent{};
+    SortBufs bufs{};
+    uint32_t *d_status = nullptr;
+    uint32_t max_tiles = 0;
+    TieItem *d_ties = nullptr;
+    uint32_t *d_posv = nullptr;
+    uint32_t *d_head = nullptr;
+    unsigned long long *d_outidx = nullptr;
+    unsigned long long *d_partial = nullptr;
+    RowArrays rows{};
+    uint64_t key_bytes_cap = 0;
+    Ctl *d_ctl = nullptr;
+    Ctl *h_ctl = nullptr; // pinned
+    const uint8_t *bytes_base = nullptr;
+
+    // shuffle
+    uint8_t *d_send = nullptr;
+    uint64_t send_cap = 0;
+    uint8_t *d_recv = nullptr;
+    uint64_t recv_cap = 0;
+    unsigned long long *d_shuf = nullptr; // [4][world]: nrec, nbytes, rec_cur, byte_cur  + [world+1] seg_off
+    std::vector<uint64_t> send_off, send_nrec;
+    bool imported = false;
+
+    // state
+    enum { IDLE, MAPPED, REDUCED, SYNCED } state = IDLE;
+    bool map_dirty = false; // splits staged since the last mr_map_finish
+    mr_job_info info{};
+    uint32_t tie_rounds = 0;
+    cudaEvent_t ev_map0 = nullptr, ev_map1 = nullptr, ev_red0 = nullptr, ev_red1 = nullptr;
+    bool map_timed = false, red_timed = false;
+    mr_stats stats{};
+
+    // host copy of the rows for cursors
+    bool rows_cached = false;
+    std::vector<uint32_t> h_part;
+    std::vector<uint64_t> h_count, h_key_off, h_part_begin;
+    std::vector<uint8_t> h_key_bytes;
+};
+
+namespace {
+
+int fail(mr_ctx *c, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(ctx, MR_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                                      \
+    } while (0)
+
+template <typename T>
+cudaError_t dmalloc(T **p, uint64_t count)
+{
+    return cudaMalloc((void **)p, std::max<uint64_t>(count, 1) * sizeof(T));
+}
+
+inline unsigned grid_for(uint64_t n, unsigned threads, unsigned cap)
+{
+    uint64_t g = (n + threads - 1) / threads;
+    return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(g, cap));
+}
+
+template <int WARPS, int LOG2>
+cudaError_t launch_map(mr_ctx *ctx, const MapParams &p)
+{
+    size_t smem = MapSmemLayout<LOG2>::total(WARPS);
+    cudaError_t ea = cudaFuncSetAttribute(map_combine_kernel<WARPS, LOG2>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (ea != cudaSuccess) return ea;
+    int ctas_per_sm = (int)(227 * 1024 / (smem + 1024));
+    ctas_per_sm = std::max(1, std::min(ctas_per_sm, 2048 / (WARPS * 32)));
+    uint64_t nwarps_needed = p.nseg;
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctas_per_sm,
+                                                 (nwarps_needed + WARPS - 1) / WARPS);
+    grid = std::max(grid, 1u);
+    map_combine_kernel<WARPS, LOG2><<<grid, WARPS * 32, smem, ctx->stream>>>(p);
+    ctx->stats.launches++;
+    return cudaGetLastError();
+}
+
+int run_general_ties(mr_ctx *ctx, uint32_t nt);
+int launch_rows(mr_ctx *ctx);
+
+} // namespace
+
+// All entry points are declared extern "C" in mrgpu.h.
+
+int mr_abi_version(void) { return MRGPU_ABI_VERSION; }
+
+const char *mr_last_error(const mr_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+uint32_t mr_partition_of(const void *key, uint64_t klen, uint32_t num_reducers)
+{
+    // host restatement of FnvLua52 (common.cuh), same IEEE operations
+    const uint8_t *k = (const uint8_t *)key;
+    volatile double h = 2166136261.0;
+    for (uint64_t i = 0; i < klen; ++i) {
+        volatile double p = h * 16777619.0;
+        volatile double q = std::floor(p * (1.0 / 4294967296.0));
+        double m = p - q * 4294967296.0;
+        h = (double)((uint32_t)m ^ (uint32_t)k[i]);
+    }
+    double r = (double)num_reducers, hh = h;
+    volatile double q = std::floor(hh / r);
+    return (uint32_t)(hh - q * r);
+}
+
+void mr_ctx_destroy(mr_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab);
+    cudaFree(ctx->ent.key); cudaFree(ctx->ent.cnt); cudaFree(ctx->ent.part);
+    for (int i = 0; i < 2; ++i) { cudaFree(ctx->bufs.hi[i]); cudaFree(ctx->bufs.lo[i]); cudaFree(ctx->bufs.val[i]); }
+    cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv); cudaFree(ctx->d_head);
+    cudaFree(ctx->d_outidx); cudaFree(ctx->d_partial);
+    cudaFree(ctx->rows.part); cudaFree(ctx->rows.count); cudaFree(ctx->rows.key_off);
+    cudaFree(ctx->rows.key_bytes); cudaFree(ctx->rows.key); cudaFree(ctx->rows.len);
+    cudaFree(ctx->rows.part_begin);
+    cudaFree(ctx->d_ctl); cudaFree(ctx->d_send); cudaFree(ctx->d_recv); cudaFree(ctx->d_shuf);
+    if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+    for (cudaEvent_t e : { ctx->ev_map0, ctx->ev_map1, ctx->ev_red0, ctx->ev_red1 })
+        if (e) cudaEventDestroy(e);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
+{
+    mr_ctx *ctx = nullptr; // CU() reports into g_create_error while ctx is null
+    if (!cfg || !out) return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: null argument");
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(mr_config))
+        return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: struct_size %u != %zu", cfg->struct_size,
+                    sizeof(mr_config));
+    if (cfg->map_kind != MR_MAP_TOKENIZE_WS || cfg->reduce_kind != MR_REDUCE_SUM_U64 ||
+        cfg->partition_kind != MR_PARTITION_FNV1_LUA52)
+        return fail(nullptr, MR_ERR_UNSUPPORTED, "mr_ctx_create: unsupported map/reduce/partition kind");
+    if (cfg->num_reducers == 0 || cfg->num_reducers > (1u << 24))
+        return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: num_reducers must be in 1..2^24");
+    if (cfg->world_size == 0 || cfg->rank >= cfg->world_size || cfg->world_size > 1024)
+        return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: bad world_size/rank");
+    if (cfg->arena_bytes == 0 || cfg->arena_bytes + ARENA_SLACK >= MAX_BYTE_SPACE)
+        return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: arena_bytes must be in 1..2^37");
+    int ndev = 0;
+    cudaError_t e0 = cudaGetDeviceCount(&ndev);
+    if (e0 != cudaSuccess || ndev == 0)
+        return fail(nullptr, MR_ERR_CUDA, "mr_ctx_create: no CUDA device (%s); there is no CPU path",
+                    cudaGetErrorString(e0));
+    if (cfg->device < 0 || cfg->device >= ndev)
+        return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: device %d out of range", cfg->device);
+    CU(cudaSetDevice(cfg->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10)
+        return fail(nullptr, MR_ERR_UNSUPPORTED,
+                    "mr_ctx_create: device is sm_%d%d, this library is built for sm_100a only", prop.major,
+                    prop.minor);
+
+    ctx = new mr_ctx();
+    ctx->cfg = *cfg;
+    ctx->sm_count = prop.multiProcessorCount;
+    if (const char *v = getenv("MRGPU_MAP_VARIANT")) ctx->map_variant = atoi(v);
+    ctx->arena_cap = round_up(cfg->arena_bytes, SEG) + SEG;
+    uint64_t mk = cfg->max_keys;
+    if (mk == 0) mk = std::min<uint64_t>(std::max<uint64_t>(cfg->arena_bytes / 64, 1u << 16), 1u << 24);
+    if (mk >= (1ull << 30)) { delete ctx; return fail(nullptr, MR_ERR_INVALID, "max_keys must be < 2^30"); }
+    ctx->max_keys = mk;
+    uint64_t slots = cfg->table_slots;
+    if (slots == 0) { slots = 1; while (slots < 2 * mk) slots <<= 1; }
+    if (slots & (slots - 1) || slots > (1ull << 31) || slots < 1024) {
+        delete ctx;
+        return fail(nullptr, MR_ERR_INVALID, "table_slots must be a power of two in 2^10..2^31");
+    }
+    ctx->slots = slots;
+    ctx->max_tiles = (uint32_t)((mk + SORT_TILE - 1) / SORT_TILE);
+    ctx->key_bytes_cap = std::min<uint64_t>(ctx->arena_cap, mk * 64) + 64;
+
+#define CUC(call)                                                                                    \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            std::string m = std::string(#call) + " failed: " + cudaGetErrorString(e_);               \
+            mr_ctx_destroy(ctx);                                                                     \
+            return fail(nullptr, e_ == cudaErrorMemoryAllocation ? MR_ERR_NOMEM : MR_ERR_CUDA, "%s", \
+                        m.c_str());                                                                  \
+        }                                                                                            \
+    } while (0)
+
+    if (cfg->stream) ctx->stream = (cudaStream_t)cfg->stream;
+    else { CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
+    CUC(dmalloc(&ctx->d_arena, ctx->arena_cap + ARENA_SLACK));
+    CUC(dmalloc(&ctx->d_gtab, slots));
+    CUC(dmalloc(&ctx->ent.key, mk)); CUC(dmalloc(&ctx->ent.cnt, mk)); CUC(dmalloc(&ctx->ent.part, mk));
+    for (int i = 0; i < 2; ++i) {
+        CUC(dmalloc(&ctx->bufs.hi[i], mk)); CUC(dmalloc(&ctx->bufs.lo[i], mk)); CUC(dmalloc(&ctx->bufs.val[i], mk));
+    }
+    CUC(dmalloc(&ctx->d_status, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS));
+    uint64_t tie_cap = 1; while (tie_cap < mk) tie_cap <<= 1;
+    CUC(dmalloc(&ctx->d_ties, tie_cap)); CUC(dmalloc(&ctx->d_posv, tie_cap));
+    CUC(dmalloc(&ctx->d_head, mk)); CUC(dmalloc(&ctx->d_outidx, mk));
+    CUC(dmalloc(&ctx->d_partial, (mk + SCAN_TILE - 1) / SCAN_TILE + 1));
+    CUC(dmalloc(&ctx->rows.part, mk)); CUC(dmalloc(&ctx->rows.count, mk));
+    CUC(dmalloc(&ctx->rows.key_off, mk + 1)); CUC(dmalloc(&ctx->rows.key_bytes, ctx->key_bytes_cap));
+    CUC(dmalloc(&ctx->rows.key, mk)); CUC(dmalloc(&ctx->rows.len, mk));
+    CUC(dmalloc(&ctx->rows.part_begin, (uint64_t)cfg->num_reducers + 1));
+    CUC(dmalloc(&ctx->d_ctl, 1));
+    CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
+    CUC(dmalloc(&ctx->d_shuf, 5ull * cfg->world_size + 1));
+    CUC(cudaEventCreate(&ctx->ev_map0)); CUC(cudaEventCreate(&ctx->ev_map1));
+    CUC(cudaEventCreate(&ctx->ev_red0)); CUC(cudaEventCreate(&ctx->ev_red1));
+    ctx->bytes_base = ctx->d_arena;
+    int rc = mr_job_begin(ctx, 0);
+    if (rc != MR_OK) { std::string m = ctx->err; mr_ctx_destroy(ctx); return fail(nullptr, rc, "%s", m.c_str()); }
+    *out = ctx;
+    return MR_OK;
+}
+
+int mr_job_begin(mr_ctx *ctx, int keep_input)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (!keep_input) {
+        ctx->used = 0; ctx->mapped_segs = 0; ctx->input_bytes = 0; ctx->any_split = false;
+        ctx->map_dirty = false;
+    } else {
+        // keep the staged splits: the next mr_map_finish maps all of them again
+        ctx->mapped_segs = 0;
+        ctx->map_dirty = ctx->any_split;
+    }
+    CU(cudaMemsetAsync(ctx->d_gtab, 0, ctx->slots * sizeof(GEntry), ctx->stream));
+    CU(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
+    ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(ctx->d_ctl);
+    CU(cudaGetLastError());
+    ctx->bytes_base = ctx->d_arena;
+    ctx->imported = false;
+    ctx->state = mr_ctx::IDLE;
+    ctx->rows_cached = false;
+    ctx->tie_rounds = 0;
+    ctx->map_timed = ctx->red_timed = false;
+    ctx->stats = mr_stats{};
+    ctx->stats.launches = 1;
+    memset(&ctx->info, 0, sizeof ctx->info);
+    return MR_OK;
+}
+
+static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKind kind)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (n && !bytes) return fail(ctx, MR_ERR_INVALID, "mr_map_split: null bytes");
+    if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_split: job already reduced; call mr_job_begin");
+    CU(cudaSetDevice(ctx->cfg.device));
+    // every split starts on a 16-byte boundary, at least one 0x20 after the previous one
+    uint64_t off = ctx->any_split ? round_up(ctx->used + 1, 16) : 0;
+    if (off + n + SEG > ctx->arena_cap)
+        return fail(ctx, MR_ERR_NOMEM, "mr_map_split: arena full (%llu + %llu > %llu bytes)",
+                    (unsigned long long)off, (unsigned long long)n, (unsigned long long)ctx->arena_cap);
+    if (off > ctx->used) CU(cudaMemsetAsync(ctx->d_arena + ctx->used, 0x20, off - ctx->used, ctx->stream));
+    if (n) CU(cudaMemcpyAsync(ctx->d_arena + off, bytes, n, kind, ctx->stream));
+    if (kind == cudaMemcpyHostToDevice) ctx->stats.h2d_bytes += n;
+    ctx->used = off + n;
+    ctx->input_bytes += n;
+    ctx->any_split = true;
+    ctx->map_dirty = true;
+    return MR_OK;
+}
+
+int mr_map_split(mr_ctx *ctx, uint64_t split_id, const void *bytes, uint64_t n)
+{
+    (void)split_id;
+    return stage_split(ctx, bytes, n, cudaMemcpyHostToDevice);
+}
+
+int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, uint64_t n)
+{
+    (void)split_id;
+    return stage_split(ctx, dev_bytes, n, cudaMemcpyDeviceToDevice);
+}
+
+int mr_map_finish(mr_ctx *ctx)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_finish: job already reduced; call mr_job_begin");
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (!ctx->map_timed) CU(cudaEventRecord(ctx->ev_map0, ctx->stream));
+    if (ctx->map_dirty) {
+        // pad the tail with spaces up to a whole segment plus the look-ahead window
+        uint64_t end = round_up(std::max<uint64_t>(ctx->used, 1), SEG);
+        CU(cudaMemsetAsync(ctx->d_arena + ctx->used, 0x20, end + SEG_AHEAD + 64 - ctx->used, ctx->stream));
+        MapParams p;
+        p.arena = ctx->d_arena;
+        p.first_seg = ctx->mapped_segs;
+        p.nseg = end / SEG - ctx->mapped_segs;
+        p.gtab = ctx->d_gtab;
+        p.gmask = (uint32_t)(ctx->slots - 1);
+        p.max_token = MR_MAX_TOKEN_BYTES;
+        p.tokens = &ctx->d_ctl->tokens;
+        p.err = &ctx->d_ctl->err;
+        if (p.nseg) {
+            cudaError_t e;
+            switch (ctx->map_variant) {
+            case 1: e = launch_map<16, 12>(ctx, p); break;
+            case 2: e = launch_map<16, 13>(ctx, p); break;
+            case 3: e = launch_map<32, 12>(ctx, p); break;
+            default: e = launch_map<32, 13>(ctx, p); break;
+            }
+            if (e != cudaSuccess) return fail(ctx, MR_ERR_CUDA, "map kernel launch: %s", cudaGetErrorString(e));
+        }
+        ctx->mapped_segs = end / SEG;
+        ctx->used = end; // later splits start in fresh segments
+        ctx->map_dirty = false;
+    }
+    CU(cudaEventRecord(ctx->ev_map1, ctx->stream));
+    ctx->map_timed = true;
+    ctx->state = mr_ctx::MAPPED;
+    return MR_OK;
+}
+
+namespace {
+
+// table -> entries (+ partition, sort keys).  Idempotent guard: done once per job.
+int launch_compact(mr_ctx *ctx)
+{
+    unsigned grid = grid_for(ctx->slots, 256, ctx->sm_count * 8);
+    compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->bytes_base,
+                                                            ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0],
+                                                            ctx->bufs.lo[0], ctx->bufs.val[0], ctx->max_keys,
+                                                            ctx->d_ctl);
+    ctx->stats.launches++;
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+int launch_sort(mr_ctx *ctx)
+{
+    cudaStream_t s = ctx->stream;
+    CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
+    sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl);
+    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 2), 256, 0, s>>>(ctx->bufs.hi[0],
+                                                                                     ctx->bufs.lo[0], ctx->d_ctl);
+    ctx->stats.launches += 2;
+    for (uint32_t pass = 0; pass < MAX_PASSES; ++pass) {
+        radix_pass_kernel<<<ctx->max_tiles, SORT_THREADS, 0, s>>>(ctx->bufs, pass, ctx->d_status, ctx->max_tiles,
+                                                                 ctx->d_ctl);
+        ctx->stats.launches++;
+    }
+    uint64_t tie_cap = 1; while (tie_cap < ctx->max_keys) tie_cap <<= 1;
+    tie_mark_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs, ctx->d_ties,
+                                                                                   (uint32_t)tie_cap, ctx->d_ctl);
+    tie_fix_small_kernel<<<1, 1024, 0, s>>>(ctx->bufs, ctx->d_ties, ctx->ent, ctx->bytes_base, ctx->d_ctl);
+    ctx->stats.launches += 2;
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+int launch_rows(mr_ctx *ctx)
+{
+    cudaStream_t s = ctx->stream;
+    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 4);
+    const unsigned tiles = (unsigned)((ctx->max_keys + SCAN_TILE - 1) / SCAN_TILE);
+    head_mark_kernel<<<g, 256, 0, s>>>(ctx->bufs, ctx->ent, ctx->bytes_base, ctx->d_head, ctx->d_ctl);
+    scan_partial_kernel<<<tiles, 256, 0, s>>>(ctx->d_head, ctx->d_partial, ctx->d_ctl, 0);
+    scan_spine_kernel<<<1, 1024, 0, s>>>(ctx->d_partial, ctx->d_ctl, 0);
+    scan_final_kernel<<<tiles, 256, 0, s>>>(ctx->d_head, ctx->d_partial, ctx->d_outidx, ctx->d_ctl, 0);
+    reduce_rows_kernel<<<g, 256, 0, s>>>(ctx->bufs, ctx->ent, ctx->d_head, ctx->d_outidx, ctx->rows, ctx->d_ctl);
+    scan_partial_kernel<<<tiles, 256, 0, s>>>(ctx->rows.len, ctx->d_partial, ctx->d_ctl, 1);
+    scan_spine_kernel<<<1, 1024, 0, s>>>(ctx->d_partial, ctx->d_ctl, 1);
+    scan_final_kernel<<<tiles, 256, 0, s>>>(ctx->rows.len, ctx->d_partial, ctx->rows.key_off, ctx->d_ctl, 1);
+    check_key_bytes_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->key_bytes_cap - 64);
+    ctx->stats.launches += 9;
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+int launch_key_bytes(mr_ctx *ctx)
+{
+    const unsigned g = grid_for(ctx->max_keys + 1, 256, ctx->sm_count * 4);
+    write_key_bytes_kernel<<<g, 256, 0, ctx->stream>>>(ctx->rows, ctx->bytes_base, ctx->cfg.num_reducers, ctx->d_ctl);
+    ctx->stats.launches++;
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+// More ties than one CTA can hold: bitonic network over the tie list in global memory.
+int run_general_ties(mr_ctx *ctx, uint32_t nt)
+{
+    cudaStream_t s = ctx->stream;
+    uint32_t np2 = 1;
+    while (np2 < nt) np2 <<= 1;
+    unsigned g = (np2 + 255) / 256;
+    tie_pad_kernel<<<g, 256, 0, s>>>(ctx->d_ties, ctx->d_posv, nt, np2);
+    ctx->stats.launches++;
+    for (uint32_t k = 2; k <= np2; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            tie_bitonic_step_kernel<<<g, 256, 0, s>>>(ctx->d_ties, ctx->d_posv, np2, k, j, ctx->ent, ctx->bytes_base);
+            ctx->stats.launches++;
+        }
+    tie_writeback_kernel<<<(nt + 255) / 256, 256, 0, s>>>(ctx->bufs, ctx->d_ties, ctx->d_posv, nt, ctx->d_ctl);
+    ctx->stats.launches++;
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+int check_device_err(mr_ctx *ctx, unsigned err)
+{
+    if (err & ERR_TOKEN_TOO_LONG)
+        return fail(ctx, MR_ERR_OVERFLOW, "a token is longer than MR_MAX_TOKEN_BYTES (%u)", MR_MAX_TOKEN_BYTES);
+    if (err & ERR_TABLE_FULL)
+        return fail(ctx, MR_ERR_OVERFLOW, "hash table full (%llu slots): raise table_slots / max_keys",
+                    (unsigned long long)ctx->slots);
+    if (err & ERR_KEYS_FULL)
+        return fail(ctx, MR_ERR_NOMEM, "more distinct keys (or key bytes) than max_keys=%llu allows",
+                    (unsigned long long)ctx->max_keys);
+    return MR_OK;
+}
+
+} // namespace
+
+int mr_reduce_all(mr_ctx *ctx)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (ctx->state == mr_ctx::IDLE) { int rc = mr_map_finish(ctx); if (rc) return rc; }
+    if (ctx->state != mr_ctx::MAPPED) return fail(ctx, MR_ERR_INVALID, "mr_reduce_all: already reduced");
+    if (ctx->map_dirty) { int rc = mr_map_finish(ctx); if (rc) return rc; }
+    CU(cudaEventRecord(ctx->ev_red0, ctx->stream));
+    int rc;
+    if (!ctx->imported) { if ((rc = launch_compact(ctx))) return rc; }
+    if ((rc = launch_sort(ctx))) return rc;
+    if ((rc = launch_rows(ctx))) return rc;
+    if ((rc = launch_key_bytes(ctx))) return rc;
+    CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
+    ctx->red_timed = true;
+    ctx->state = mr_ctx::REDUCED;
+    return MR_OK;
+}
+
+int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (ctx->state == mr_ctx::IDLE || ctx->state == mr_ctx::MAPPED) { int rc = mr_reduce_all(ctx); if (rc) return rc; }
+    if (ctx->state == mr_ctx::REDUCED) {
+        CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        int rc = check_device_err(ctx, ctx->h_ctl->err);
+        if (rc) return rc;
+        if (ctx->h_ctl->tie_overflow) {
+            // rare: many keys agree in their first 7 bytes; order them, then redo the rows
+            if ((rc = run_general_ties(ctx, ctx->h_ctl->n_tie))) return rc;
+            if ((rc = launch_rows(ctx))) return rc;
+            if ((rc = launch_key_bytes(ctx))) return rc;
+            CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
+            CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            if ((rc = check_device_err(ctx, ctx->h_ctl->err))) return rc;
+            ctx->tie_rounds = 2;
+        } else {
+            ctx->tie_rounds = ctx->h_ctl->n_tie ? 1 : 0;
+        }
+        ctx->stats.d2h_bytes += sizeof(Ctl);
+        ctx->info.n_keys = ctx->h_ctl->n_out;
+        ctx->info.n_tokens = ctx->h_ctl->tokens;
+        ctx->info.input_bytes = ctx->input_bytes;
+        ctx->info.key_bytes = ctx->h_ctl->key_bytes;
+        if (!ctx->imported) ctx->info.map_keys = ctx->h_ctl->n;
+        ctx->info.tie_rounds = ctx->tie_rounds;
+        ctx->info.flags = 0;
+        if (ctx->map_timed) cudaEventElapsedTime(&ctx->stats.map_ms, ctx->ev_map0, ctx->ev_map1);
+        if (ctx->red_timed) cudaEventElapsedTime(&ctx->stats.reduce_ms, ctx->ev_red0, ctx->ev_red1);
+        ctx->state = mr_ctx::SYNCED;
+    }
+    if (info) *info = ctx->info;
+    return MR_OK;
+}
+
+int mr_device_rows_get(mr_ctx *ctx, mr_device_rows *rows)
+{
+    if (!ctx || !rows) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::SYNCED) return fail(ctx, MR_ERR_INVALID, "mr_device_rows_get: call mr_job_sync first");
+    rows->n = ctx->info.n_keys;
+    rows->part = ctx->rows.part;
+    rows->count = (const uint64_t *)ctx->rows.count;
+    rows->key_off = (const uint64_t *)ctx->rows.key_off;
+    rows->key_bytes = ctx->rows.key_bytes;
+    rows->part_begin = (const uint64_t *)ctx->rows.part_begin;
+    return MR_OK;
+}
+
+int mr_rows_fetch(mr_ctx *ctx, uint32_t *part, uint64_t *count, uint64_t *key_off, uint8_t *key_bytes,
+                  uint64_t *part_begin)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::SYNCED) { int rc = mr_job_sync(ctx, nullptr); if (rc) return rc; }
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint64_t n = ctx->info.n_keys;
+    cudaStream_t s = ctx->stream;
+    if (part && n) { CU(cudaMemcpyAsync(part, ctx->rows.part, n * 4, cudaMemcpyDeviceToHost, s)); ctx->stats.d2h_bytes += n * 4; }
+    if (count && n) { CU(cudaMemcpyAsync(count, ctx->rows.count, n * 8, cudaMemcpyDeviceToHost, s)); ctx->stats.d2h_bytes += n * 8; }
+    if (key_off) { CU(cudaMemcpyAsync(key_off, ctx->rows.key_off, (n + 1) * 8, cudaMemcpyDeviceToHost, s)); ctx->stats.d2h_bytes += (n + 1) * 8; }
+    if (key_bytes && ctx->info.key_bytes) {
+        CU(cudaMemcpyAsync(key_bytes, ctx->rows.key_bytes, ctx->info.key_bytes, cudaMemcpyDeviceToHost, s));
+        ctx->stats.d2h_bytes += ctx->info.key_bytes;
+    }
+    if (part_begin) {
+        CU(cudaMemcpyAsync(part_begin, ctx->rows.part_begin, ((uint64_t)ctx->cfg.num_reducers + 1) * 8, cudaMemcpyDeviceToHost, s));
+        ctx->stats.d2h_bytes += ((uint64_t)ctx->cfg.num_reducers + 1) * 8;
+    }
+    CU(cudaStreamSynchronize(s));
+    return MR_OK;
+}
+
+int mr_reduce_partition(mr_ctx *ctx, uint32_t part, mr_result **out)
+{
+    if (!ctx || !out) return MR_ERR_INVALID;
+    *out = nullptr;
+    if (part >= ctx->cfg.num_reducers) return fail(ctx, MR_ERR_INVALID, "mr_reduce_partition: partition %u out of range", part);
+    if (ctx->state != mr_ctx::SYNCED) { int rc = mr_job_sync(ctx, nullptr); if (rc) return rc; }
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (!ctx->rows_cached) {
+        ctx->h_part_begin.assign((size_t)ctx->cfg.num_reducers + 1, 0);
+        CU(cudaMemcpyAsync(ctx->h_part_begin.data(), ctx->rows.part_begin, ctx->h_part_begin.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        ctx->stats.d2h_bytes += ctx->h_part_begin.size() * 8;
+        ctx->rows_cached = true;
+    }
+    const uint64_t first = ctx->h_part_begin[part], last = ctx->h_part_begin[part + 1];
+    mr_result *r = new mr_result();
+    r->ctx = ctx; r->first = first; r->n = last - first; r->cur = 0;
+    if (r->n) {
+        r->count.resize(r->n); r->key_off.resize(r->n + 1);
+        cudaStream_t s = ctx->stream;
+        cudaError_t e = cudaMemcpyAsync(r->count.data(), ctx->rows.count + first, r->n * 8, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(r->key_off.data(), ctx->rows.key_off + first, (r->n + 1) * 8, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e == cudaSuccess) {
+            uint64_t b0 = r->key_off[0], b1 = r->key_off[r->n];
+            r->key_bytes.resize(b1 - b0 + 1);
+            if (b1 > b0) e = cudaMemcpyAsync(r->key_bytes.data(), ctx->rows.key_bytes + b0, b1 - b0, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+            ctx->stats.d2h_bytes += r->n * 16 + 8 + (b1 - b0);
+        }
+        if (e != cudaSuccess) { delete r; return fail(ctx, MR_ERR_CUDA, "mr_reduce_partition: %s", cudaGetErrorString(e)); }
+    }
+    *out = r;
+    return MR_OK;
+}
+
+int mr_result_next(mr_result *res, const char **key, uint64_t *klen, uint64_t *count)
+{
+    if (!res) return MR_ERR_INVALID;
+    if (res->cur >= res->n) return MR_ERR_END;
+    uint64_t i = res->cur++;
+    uint64_t b0 = res->key_off[0];
+    if (key) *key = (const char *)res->key_bytes.data() + (res->key_off[i] - b0);
+    if (klen) *klen = res->key_off[i + 1] - res->key_off[i];
+    if (count) *count = res->count[i];
+    return MR_OK;
+}
+
+void mr_result_release(mr_result *res) { delete res; }
+
+int mr_stats_get(mr_ctx *ctx, mr_stats *out)
+{
+    if (!ctx || !out) return MR_ERR_INVALID;
+    *out = ctx->stats;
+    return MR_OK;
+}
+
+// ---------------------------------------------------------------- shuffle
+int mr_shuffle_export(mr_ctx *ctx, mr_shuffle_plan *plan)
+{
+    if (!ctx || !plan) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::MAPPED || ctx->imported)
+        return fail(ctx, MR_ERR_INVALID, "mr_shuffle_export: call after mr_map_finish, once per job");
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (ctx->map_dirty) { int rc = mr_map_finish(ctx); if (rc) return rc; }
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    int rc = launch_compact(ctx);
+    if (rc) return rc;
+    unsigned long long *nrec = ctx->d_shuf, *nbytes = ctx->d_shuf + W, *rec_cur = ctx->d_shuf + 2 * W,
+                       *byte_cur = ctx->d_shuf + 3 * W, *seg_off = ctx->d_shuf + 4 * W;
+    CU(cudaMemsetAsync(ctx->d_shuf, 0, (5ull * W + 1) * 8, s));
+    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 4);
+    export_count_kernel<<<g, 256, 0, s>>>(ctx->ent, W, nrec, nbytes, ctx->d_ctl);
+    ctx->stats.launches++;
+    std::vector<unsigned long long> h(2 * W);
+    CU(cudaMemcpyAsync(h.data(), ctx->d_shuf, 2ull * W * 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    if ((rc = check_device_err(ctx, ctx->h_ctl->err))) return rc;
+    ctx->info.map_keys = ctx->h_ctl->n;
+    ctx->send_off.assign(W + 1, 0);
+    ctx->send_nrec.assign(W, 0);
+    for (uint32_t d = 0; d < W; ++d) {
+        ctx->send_nrec[d] = h[d];
+        ctx->send_off[d + 1] = ctx->send_off[d] + round_up(h[d] * 16 + h[W + d], 16);
+    }
+    const uint64_t total = ctx->send_off[W];
+    if (total + 64 > ctx->send_cap) {
+        if (ctx->d_send) CU(cudaFree(ctx->d_send));
+        ctx->d_send = nullptr;
+        ctx->send_cap = total + total / 4 + 4096;
+        CU(dmalloc(&ctx->d_send, ctx->send_cap));
+    }
+    std::vector<unsigned long long> so(ctx->send_off.begin(), ctx->send_off.end());
+    CU(cudaMemcpyAsync(seg_off, so.data(), (W + 1) * 8ull, cudaMemcpyHostToDevice, s));
+    CU(cudaStreamSynchronize(s)); // `so` is pageable host memory going out of scope
+    CU(cudaMemsetAsync(ctx->d_send, 0, total + 64, s));
+    export_scatter_kernel<<<g, 256, 0, s>>>(ctx->ent, ctx->bytes_base, W, ctx->d_send, seg_off, nrec, rec_cur,
+                                            byte_cur, ctx->d_ctl);
+    ctx->stats.launches++;
+    CU(cudaGetLastError());
+    plan->send_base = ctx->d_send;
+    plan->send_off = ctx->send_off.data();
+    plan->send_nrec = ctx->send_nrec.data();
+    return MR_OK;
+}
+
+int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr)
+{
+    if (!ctx || !dev_ptr) return MR_ERR_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (bytes + ARENA_SLACK >= MAX_BYTE_SPACE) return fail(ctx, MR_ERR_NOMEM, "receive buffer too large");
+    if (bytes + 256 > ctx->recv_cap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        if (ctx->d_recv) CU(cudaFree(ctx->d_recv));
+        ctx->d_recv = nullptr;
+        ctx->recv_cap = bytes + bytes / 4 + 4096;
+        CU(dmalloc(&ctx->d_recv, ctx->recv_cap));
+    }
+    CU(cudaMemsetAsync(ctx->d_recv + bytes, 0, 256, ctx->stream));
+    *dev_ptr = ctx->d_recv;
+    return MR_OK;
+}
+
+int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *recv_nrec)
+{
+    if (!ctx || !recv_off || !recv_nrec) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::MAPPED) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import: call after mr_shuffle_export");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    const uint64_t *nrec = recv_nrec;
+    uint64_t base = 0;
+    for (uint32_t src = 0; src < W; ++src) {
+        uint64_t n = nrec[src];
+        if (recv_off[src] + n * 16 > recv_off[src + 1]) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import: segment %u too small", src);
+        if (base + n > ctx->max_keys) return fail(ctx, MR_ERR_NOMEM, "mr_shuffle_import: more than max_keys records");
+        if (n) {
+            import_segment_kernel<<<grid_for(n, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->d_recv, recv_off[src], n, base, ctx->ent);
+            ctx->stats.launches++;
+        }
+        base += n;
+    }
+    // fresh control block for the reduce side, keeping the token count and errors
+    CU(cudaMemsetAsync(&ctx->d_ctl->or_lo, 0, offsetof(Ctl, tokens) - offsetof(Ctl, or_lo), s));
+    ctl_init_kernel<<<1, 1, 0, s>>>(ctx->d_ctl);
+    ctl_set_n_kernel<<<1, 1, 0, s>>>(ctx->d_ctl, base);
+    ctx->bytes_base = ctx->d_recv;
+    partition_entries_kernel<<<grid_for(std::max<uint64_t>(base, 1), 256, ctx->sm_count * 4), 256, 0, s>>>(
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0], ctx->bufs.lo[0], ctx->bufs.val[0], ctx->d_ctl);
+    ctx->stats.launches += 3;
+    CU(cudaGetLastError());
+    ctx->imported = true;
+    return MR_OK;
+}
+

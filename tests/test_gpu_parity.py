@@ -1,0 +1,223 @@
+"""Parity of the CUDA data plane with the CPU oracle, through the C ABI.  Bit-exact:
+same key set, same integer counts, same partition ids, same order (partition ascending,
+key ascending in unsigned-byte order) -- SURVEY.md App. A."""
+import random
+
+import numpy as np
+import pytest
+
+from helpers import assert_rows_equal, golden, rows_digest
+from lua_mapreduce_1_b200 import _native, corpus
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(splits, R, arena=None, max_keys=1 << 16, **kw):
+    total = sum(len(s) for s in splits)
+    ctx = _native.Context(R, arena or (total + 64 * len(splits) + 4096), max_keys=max_keys, **kw)
+    try:
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+        ctx.map_finish()
+        ctx.reduce_all()
+        info = ctx.job_sync()
+        rows = ctx.rows()
+        return rows, info, ctx.stats()
+    finally:
+        ctx.close()
+
+
+def check(splits, R, **kw):
+    want = O.run_naive(splits, R)
+    got, info, st = run_gpu(splits, R, **kw)
+    assert info.n_tokens == want.tokens
+    assert info.input_bytes == sum(len(s) for s in splits)
+    assert_rows_equal(got, want, f"R={R}")
+    assert info.n_keys == want.n and info.key_bytes == len(want.key_bytes)
+    pb = np.searchsorted(want.part, np.arange(R + 1), side="left")
+    assert np.array_equal(got.part_begin.astype(np.int64), pb)
+    return got, info
+
+
+@pytest.mark.parametrize("text", [b"", b"   \n\t\r ", b"a", b"a ", b" a", b"ab cd ab", b"x" * 7, b"x" * 8,
+                                  b"x" * 9, b"\n".join([b"w"] * 100), b"a\x00b a\x00b a"])
+def test_tiny_inputs(text):
+    check([text], 15)
+
+
+def test_empty_job_and_empty_splits():
+    check([], 10)
+    check([b"", b"", b"one", b""], 10)
+
+
+def test_torture_split_matches_oracle_and_golden():
+    g = golden("torture_rows.json")
+    for R in (15, 10, 1):
+        got, _ = check([corpus.TORTURE], R)
+        assert rows_digest(got.part, got.count, got.key_off, got.key_bytes) == g[f"R{R}"]["sha256"]
+
+
+def test_tokens_never_span_splits():
+    # "ab" ends split 0 without whitespace, "cd" starts split 1: must stay two tokens
+    got, _ = check([b"x ab", b"cd y", b"ab"], 10)
+    assert b"abcd" not in got.keys()
+
+
+def test_alignment_and_segment_boundaries():
+    # tokens straddling 16-byte, 32-byte and 1024-byte (segment) boundaries, every phase
+    rnd = random.Random(11)
+    for shift in range(0, 40):
+        parts = [b" " * shift]
+        while sum(map(len, parts)) < 5000:
+            n = rnd.choice([1, 2, 3, 6, 7, 8, 9, 15, 16, 17, 31, 33, 70])
+            parts.append(bytes(rnd.choice(b"abcxyz") for _ in range(n)))
+            parts.append(rnd.choice([b" ", b"\n", b"  ", b"\t"]))
+        check([b"".join(parts)], 10)
+
+
+def test_long_token_spanning_many_segments():
+    big = b"Q" * 5000
+    check([b"a " + big + b" b " + big + b" " + big[:-1] + b" z"], 10)
+
+
+def test_reference_shaped_fixture(reference_fixture):
+    # config 1: the reference's own input (only where the reference tree is mounted)
+    g = golden("wordcount_fixture.json")
+    for R in (15, 10):
+        got, info = check(reference_fixture, R)
+        assert info.n_tokens == 4977 and info.n_keys == 1575
+        assert rows_digest(got.part, got.count, got.key_off, got.key_bytes) == g[f"R{R}"]["sha256"]
+
+
+def test_source_code_like_text():
+    # stand-in for config 1 on boxes without the reference tree: punctuation-heavy, mixed lengths
+    rnd = random.Random(5)
+    vocab = [b"local", b"function", b"end", b"=", b"==", b"--", b"{", b"}", b"return", b"self.cnn:connect()",
+             b"string.format(\"%s.P%d.M%s\",", b"if", b"then", b"utils.MAX_MAP_RESULT", b"job_mark_as_written(self,",
+             b"--------------------------------------------------------------------------"]
+    vocab += [bytes(rnd.choice(b"abcdefghijklmnopqrstuvwxyz_.():") for _ in range(rnd.randrange(1, 30)))
+              for _ in range(400)]
+    splits = []
+    for _ in range(4):
+        lines = []
+        for _ in range(400):
+            lines.append(b"  " * rnd.randrange(4) + b" ".join(rnd.choice(vocab) for _ in range(rnd.randrange(0, 9))))
+        splits.append(b"\n".join(lines))
+    for R in (15, 10):
+        check(splits, R)
+
+
+def test_many_keys_sharing_a_7_byte_prefix_small_path():
+    rnd = random.Random(2)
+    keys = {b"prefix_" + bytes(rnd.choice(b"abc") for _ in range(rnd.randrange(1, 12))) for _ in range(600)}
+    keys |= {b"prefix_", b"prefix", b"prefix_a" + b"\x00", b"prefixes"}
+    text = b" ".join(rnd.choice(sorted(keys)) for _ in range(4000))
+    got, info = check([text], 10)
+    assert info.tie_rounds == 1
+
+
+def test_many_keys_sharing_a_7_byte_prefix_general_path():
+    rnd = random.Random(4)
+    keys = sorted({b"commonprefix/" + bytes(rnd.choice(b"abcdefgh") for _ in range(rnd.randrange(1, 20)))
+                   for _ in range(6000)})
+    text = b"\n".join(rnd.choice(keys) for _ in range(30000))
+    got, info = check([text], 10, max_keys=1 << 15)
+    assert info.tie_rounds == 2
+
+
+def test_synthetic_corpus_small():
+    splits, tok = corpus.generate(lines=[3000, 3000, 1234, 1], first_split=190)
+    got, info = check(splits, 10, max_keys=1 << 18)
+    assert info.n_tokens == tok
+
+
+def test_incremental_map_finish_and_keep_input():
+    splits, tok = corpus.generate(lines=[500] * 6)
+    want = O.run_staged(splits, 10, 2)
+    ctx = _native.Context(10, 1 << 22, max_keys=1 << 17)
+    try:
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+            if i % 2 == 1:
+                ctx.map_finish()          # three partial map rounds
+        ctx.reduce_all()
+        assert_rows_equal(ctx.rows(), want, "incremental")
+        for _ in range(2):                # "loop" iteration over the resident splits
+            ctx.job_begin(keep_input=True)
+            ctx.map_finish()
+            ctx.reduce_all()
+            info = ctx.job_sync()
+            assert info.n_tokens == tok
+            assert_rows_equal(ctx.rows(), want, "keep_input")
+        ctx.job_begin()                   # fresh job on the same context, smaller input
+        ctx.map_split(0, b"fresh start fresh")
+        assert_rows_equal(ctx.rows(), O.run_naive([b"fresh start fresh"], 10), "fresh")
+    finally:
+        ctx.close()
+
+
+def test_partition_cursor_matches_rows():
+    splits, _ = corpus.generate(lines=[800, 800])
+    ctx = _native.Context(15, 1 << 21, max_keys=1 << 17)
+    try:
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+        rows = ctx.rows()
+        keys = rows.keys()
+        seen = 0
+        for p in range(15):
+            lo, hi = int(rows.part_begin[p]), int(rows.part_begin[p + 1])
+            cur = list(ctx.partition_cursor(p))
+            assert [k for k, _ in cur] == keys[lo:hi]
+            assert [c for _, c in cur] == [int(c) for c in rows.count[lo:hi]]
+            seen += len(cur)
+        assert seen == rows.n
+        with pytest.raises(_native.NativeError):
+            list(ctx.partition_cursor(15))
+    finally:
+        ctx.close()
+
+
+def test_capacity_errors_are_reported():
+    splits, _ = corpus.generate(lines=[2000])
+    with pytest.raises(_native.NativeError) as e:
+        run_gpu(splits, 10, arena=1 << 12)
+    assert e.value.code == _native.MR_ERR_NOMEM
+    with pytest.raises(_native.NativeError) as e:
+        run_gpu(splits, 10, max_keys=1 << 10, table_slots=1 << 11)
+    assert e.value.code in (_native.MR_ERR_NOMEM, _native.MR_ERR_OVERFLOW)
+
+
+def test_device_memory_input():
+    import torch
+    splits, _ = corpus.generate(lines=[1000])
+    t = torch.from_numpy(splits[0]).cuda()
+    ctx = _native.Context(10, 1 << 21, max_keys=1 << 17, stream=torch.cuda.current_stream().cuda_stream)
+    try:
+        ctx.map_split_ptr(0, t.data_ptr(), t.numel(), device=True)
+        assert_rows_equal(ctx.rows(), O.run_naive(splits, 10), "device input")
+    finally:
+        ctx.close()
+
+
+def test_config2_full_size_exact():
+    # BASELINE.json configs[1]: 197 splits, ~49 M tokens, R = 10 -- full comparison with the oracle
+    splits, tok = corpus.generate()
+    want = O.run_staged(splits, 10, O.max_threads())
+    total = sum(len(s) for s in splits)
+    ctx = _native.Context(10, total + 64 * len(splits) + 4096, max_keys=1 << 20, table_slots=1 << 21)
+    try:
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+        ctx.map_finish()
+        ctx.reduce_all()
+        info = ctx.job_sync()
+        got = ctx.rows()
+        assert info.n_tokens == tok == want.tokens
+        assert_rows_equal(got, want, "config 2")
+        # size-independent properties
+        assert int(got.count.sum()) == tok
+        assert np.all(np.diff(got.part.astype(np.int64)) >= 0)
+    finally:
+        ctx.close()
