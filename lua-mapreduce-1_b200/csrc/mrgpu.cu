@@ -483,7 +483,7 @@ int launch_sort(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
     CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
-    sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl);
+    sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->max_keys);
     radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 2), 256, 0, s>>>(ctx->bufs.hi[0],
                                                                                      ctx->bufs.lo[0], ctx->d_ctl);
     ctx->stats.launches += 2;

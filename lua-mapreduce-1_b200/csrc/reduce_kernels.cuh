@@ -132,9 +132,10 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
 // ------------------------------------------------------------------ K5 radix sort
 // One thread: split the varying bits (or ^ and) into digits of up to 8 bits, least
 // significant first; each digit is up to 8 runs of consecutive key bits.
-__global__ void sort_setup_kernel(Ctl *ctl)
+__global__ void sort_setup_kernel(Ctl *ctl, unsigned long long max_keys)
 {
     if (threadIdx.x || blockIdx.x) return;
+    if (ctl->n > max_keys) { ctl->n = max_keys; ctl->err |= ERR_KEYS_FULL; } // reported by the host
     uint64_t vlo = ctl->or_lo ^ ctl->and_lo;
     uint32_t vhi = ctl->or_hi ^ ctl->and_hi;
     if (ctl->n < 2) { vlo = 0; vhi = 0; }
