@@ -6,37 +6,46 @@
 
 namespace mr {
 
-// ---------------------------------------------------------------- key words
-// Every distinct key is identified by one 64-bit word.
-//   short key (1..7 bytes): bytes little-endian in bits 0..55, length in bits 56..62.
-//                           The word IS the key, so equality is exact.
-//   long key  (>= 8 bytes): bit 63 | byte offset (37 bits) << 26 | length (26 bits);
-//                           the offset points at one occurrence in the byte space
-//                           (input arena on the map side, receive buffer after a
-//                           shuffle); equality compares the bytes.
-// 0 is never a valid word (length >= 1), so it marks an empty table slot.
-constexpr uint64_t KEY_LONG = 1ull << 63;
+// ---------------------------------------------------------------- keys
+// Every distinct key is identified by 128 bits (k0, k1).
+//   inline key (1..15 bytes): k0 = bytes 0..7, k1 bits 0..55 = bytes 8..14 (little-endian,
+//                             zero padded), k1 bits 56..63 = length.  The pair IS the key,
+//                             so equality is exact and no input byte is ever re-read.
+//   long key (>= 16 bytes):   k1 = 0xFF << 56 | 32-bit hash of the bytes,
+//                             k0 = byte offset << 26 | length (26 bits); the offset points
+//                             at one occurrence in the byte space (input arena on the map
+//                             side, receive buffer after a shuffle); equality = same hash,
+//                             same length, same bytes.
+// k1 == 0 never occurs for a valid key (length >= 1), so it marks an empty table slot.
+constexpr int INLINE_MAX = 15;
+constexpr uint64_t TAG_LONG = 0xFFull << 56;
+constexpr uint64_t LOW56 = (1ull << 56) - 1;
 constexpr int LONG_LEN_BITS = 26;
 constexpr uint64_t LONG_LEN_MASK = (1ull << LONG_LEN_BITS) - 1;
 constexpr uint64_t MAX_BYTE_SPACE = 1ull << 37;
 
-__host__ __device__ __forceinline__ bool key_is_long(uint64_t k) { return (k >> 63) != 0; }
-__host__ __device__ __forceinline__ uint32_t key_len(uint64_t k)
+struct Key {
+    unsigned long long k0, k1;
+};
+
+__host__ __device__ __forceinline__ bool key_is_long(const Key &k) { return (k.k1 >> 56) == 0xFF; }
+__host__ __device__ __forceinline__ uint32_t key_len(const Key &k)
 {
-    return key_is_long(k) ? (uint32_t)(k & LONG_LEN_MASK) : (uint32_t)(k >> 56);
+    return key_is_long(k) ? (uint32_t)(k.k0 & LONG_LEN_MASK) : (uint32_t)(k.k1 >> 56);
 }
-__host__ __device__ __forceinline__ uint64_t key_off(uint64_t k)
+__host__ __device__ __forceinline__ uint64_t key_off(const Key &k) { return k.k0 >> LONG_LEN_BITS; }
+__host__ __device__ __forceinline__ Key make_long_key(uint64_t off, uint32_t len, uint32_t hash)
 {
-    return (k & ~KEY_LONG) >> LONG_LEN_BITS;
-}
-__host__ __device__ __forceinline__ uint64_t make_long_key(uint64_t off, uint32_t len)
-{
-    return KEY_LONG | (off << LONG_LEN_BITS) | len;
+    Key k;
+    k.k0 = (off << LONG_LEN_BITS) | len;
+    k.k1 = TAG_LONG | hash;
+    return k;
 }
 
-struct GEntry {
-    unsigned long long key;
+struct __align__(32) GEntry {
+    unsigned long long k0, k1;
     unsigned long long cnt;
+    unsigned long long pad;
 };
 
 // error bits accumulated on the device (Ctl::err)
@@ -66,14 +75,28 @@ __device__ __forceinline__ uint32_t nonspace_nibble(uint32_t x)
 }
 
 // ---------------------------------------------------------------- hashing
-__device__ __forceinline__ uint32_t hash_word(uint64_t key)
+__device__ __forceinline__ uint32_t mix32(uint32_t h)
 {
-    uint32_t lo = (uint32_t)key, hi = (uint32_t)(key >> 32);
-    uint32_t h = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u);
     h ^= h >> 15; h *= 0x2C1B3C6Du;
     h ^= h >> 12; h *= 0x297A2D39u;
     h ^= h >> 15;
     return h;
+}
+
+// hash of a short key held in one word (shared-memory table)
+__device__ __forceinline__ uint32_t hash_word(uint64_t w)
+{
+    return mix32(((uint32_t)w * 0x9E3779B1u) ^ ((uint32_t)(w >> 32) * 0x85EBCA77u));
+}
+
+// hash of a full key (global table).  A long key hashes by its byte hash only, so that
+// every occurrence of the same bytes lands on the same probe sequence.
+__device__ __forceinline__ uint32_t hash_key(const Key &k)
+{
+    if (key_is_long(k)) return mix32((uint32_t)k.k1 * 0x9E3779B1u + 0x7F4A7C15u);
+    uint32_t h = ((uint32_t)k.k0 * 0x9E3779B1u) ^ ((uint32_t)(k.k0 >> 32) * 0x85EBCA77u);
+    h ^= ((uint32_t)k.k1 * 0xC2B2AE3Du) ^ ((uint32_t)(k.k1 >> 32) * 0x27D4EB2Fu);
+    return mix32(h);
 }
 
 // 8 bytes at an arbitrary byte offset, little-endian.  May read up to 15 bytes past
@@ -109,19 +132,36 @@ __device__ inline bool bytes_equal(const uint8_t *base, uint64_t a, uint64_t b, 
     return true;
 }
 
-// unsigned-byte lexicographic compare of two long keys, shorter first on equal prefix
-// (Lua string `<`, utils.lua:126 / utils.lua:214)
-__device__ inline int long_key_compare(const uint8_t *base, uint64_t ka, uint64_t kb)
+__device__ __forceinline__ bool same_key(const Key &a, const Key &b, const uint8_t *bytes)
 {
-    uint32_t la = key_len(ka), lb = key_len(kb);
-    uint64_t oa = key_off(ka), ob = key_off(kb);
-    uint32_t n = la < lb ? la : lb;
-    for (uint32_t i = 0; i < n; i += 8) {
-        uint64_t m = low_bytes_mask(n - i);
-        uint64_t wa = bswap64(load8(base, oa + i) & m), wb = bswap64(load8(base, ob + i) & m);
-        if (wa != wb) return wa < wb ? -1 : 1;
+    if (a.k1 != b.k1) return false;       // length / hash differ
+    if (a.k0 == b.k0) return true;
+    if (!key_is_long(a)) return false;
+    uint32_t la = key_len(a);
+    return la == key_len(b) && bytes_equal(bytes, key_off(a), key_off(b), la);
+}
+
+// Sort word of a key for ordering round r: key bytes 7r .. 7r+6 big-endian in the top 56
+// bits, min(remaining length, 8) in the low byte.  Numeric order of the words of round 0,
+// then round 1, ... is unsigned-byte lexicographic order with the shorter key first
+// (Lua string `<`, utils.lua:126 / utils.lua:214).
+__device__ inline uint64_t sort_chunk(const Key &k, const uint8_t *bytes, uint32_t round)
+{
+    const uint32_t len = key_len(k);
+    const uint32_t skip = 7u * round;
+    if (skip >= len) return 0;
+    const uint32_t rem = len - skip;
+    uint64_t w;
+    if (!key_is_long(k)) {
+        const uint64_t hi = k.k1 & LOW56;
+        if (round == 0) w = k.k0;
+        else if (round == 1) w = (k.k0 >> 56) | (hi << 8);
+        else w = hi >> 48;               // byte 14
+    } else {
+        w = load8(bytes, key_off(k) + skip);
     }
-    return la < lb ? -1 : (la > lb ? 1 : 0);
+    w &= low_bytes_mask(rem < 7 ? rem : 7);
+    return (bswap64(w) & ~0xFFull) | (rem < 8 ? rem : 8);
 }
 
 // ---------------------------------------------------------------- partitioner
@@ -147,15 +187,16 @@ struct FnvLua52 {
     }
 };
 
-__device__ inline uint32_t partition_of_key(uint64_t key, const uint8_t *bytes, uint32_t num_reducers)
+__device__ inline uint32_t partition_of_key(const Key &k, const uint8_t *bytes, uint32_t num_reducers)
 {
     FnvLua52 f;
-    if (!key_is_long(key)) {
-        uint32_t len = (uint32_t)(key >> 56);
-        for (uint32_t i = 0; i < len; ++i) f.byte((uint32_t)(key >> (8 * i)) & 0xFFu);
+    const uint32_t len = key_len(k);
+    if (!key_is_long(k)) {
+        const uint32_t n0 = len < 8 ? len : 8;
+        for (uint32_t i = 0; i < n0; ++i) f.byte((uint32_t)(k.k0 >> (8 * i)) & 0xFFu);
+        for (uint32_t i = 8; i < len; ++i) f.byte((uint32_t)(k.k1 >> (8 * (i - 8))) & 0xFFu);
     } else {
-        uint32_t len = key_len(key);
-        uint64_t off = key_off(key);
+        const uint64_t off = key_off(k);
         for (uint32_t i = 0; i < len; i += 8) {
             uint64_t w = load8(bytes, off + i);
             uint32_t n = len - i < 8 ? len - i : 8;
@@ -165,62 +206,42 @@ __device__ inline uint32_t partition_of_key(uint64_t key, const uint8_t *bytes, 
     return f.partition(num_reducers);
 }
 
-// Sort word of a key for ordering round r (7 key bytes per round, big-endian, then
-// min(remaining length, 8)): numeric order of the words of round 0, then round 1,
-// ... is unsigned-byte lexicographic order with the shorter key first.
-__device__ inline uint64_t sort_chunk(uint64_t key, const uint8_t *bytes, uint32_t round)
-{
-    if (!key_is_long(key)) {
-        if (round) return 0;
-        return bswap64(key); // byte0 on top ... byte6, then the length byte (<= 7)
-    }
-    uint32_t len = key_len(key);
-    uint64_t skip = 7ull * round;
-    if (skip >= len) return 0;
-    uint32_t rem = len - (uint32_t)skip;
-    uint64_t w = load8(bytes, key_off(key) + skip) & low_bytes_mask(rem < 7 ? rem : 7);
-    return (bswap64(w) & ~0xFFull) | (rem < 8 ? rem : 8);
-}
-
 // ---------------------------------------------------------------- global table
-// Open addressing, linear probing, 16-byte slots {key word, count}.  Keys are
-// claimed with a 64-bit CAS and never change afterwards; counts are added with
-// fire-and-forget 64-bit reductions.
+// Open addressing, linear probing, 32-byte slots {k0, k1, count, -}.  A key is claimed
+// with ONE 128-bit compare-and-swap on (k0, k1) and never changes afterwards; counts
+// are added with fire-and-forget 64-bit reductions.
 constexpr uint32_t GT_MAX_PROBES = 1u << 14;
 
-__device__ inline void gtable_add_short(GEntry *gt, uint32_t gmask, uint64_t key, uint64_t n,
-                                        unsigned int *err)
+__device__ __forceinline__ Key cas128(GEntry *slot, const Key &desired)
 {
-    uint32_t slot = hash_word(key) & gmask;
-    for (uint32_t probes = 0; probes < GT_MAX_PROBES; ++probes) {
-        unsigned long long k = __ldcg(&gt[slot].key);
-        if (k == 0) {
-            k = atomicCAS(&gt[slot].key, 0ull, (unsigned long long)key);
-            if (k == 0) k = key;
-        }
-        if (k == key) {
-            atomicAdd(&gt[slot].cnt, (unsigned long long)n);
-            return;
-        }
-        slot = (slot + 1) & gmask;
-    }
-    atomicOr(err, ERR_TABLE_FULL);
+    Key old;
+    asm volatile(
+        "{\n\t"
+        ".reg .b128 cmp, des, res;\n\t"
+        "mov.b128 cmp, {%2, %3};\n\t"
+        "mov.b128 des, {%4, %5};\n\t"
+        "atom.global.cas.b128 res, [%6], cmp, des;\n\t"
+        "mov.b128 {%0, %1}, res;\n\t"
+        "}\n"
+        : "=l"(old.k0), "=l"(old.k1)
+        : "l"(0ull), "l"(0ull), "l"(desired.k0), "l"(desired.k1), "l"(slot)
+        : "memory");
+    return old;
 }
 
-// key = long reference into `bytes`; h = hash of its bytes
-__device__ inline void gtable_add_long(GEntry *gt, uint32_t gmask, const uint8_t *bytes,
-                                       uint64_t key, uint32_t h, uint64_t n, unsigned int *err)
+__device__ inline void gtable_add(GEntry *gt, uint32_t gmask, const uint8_t *bytes, const Key &key,
+                                  uint64_t n, unsigned int *err)
 {
-    uint32_t slot = h & gmask;
-    uint32_t len = key_len(key);
+    uint32_t slot = hash_key(key) & gmask;
     for (uint32_t probes = 0; probes < GT_MAX_PROBES; ++probes) {
-        unsigned long long k = __ldcg(&gt[slot].key);
-        if (k == 0) {
-            k = atomicCAS(&gt[slot].key, 0ull, (unsigned long long)key);
-            if (k == 0) k = key;
+        ulonglong2 v = __ldcg((const ulonglong2 *)&gt[slot]);
+        Key cur;
+        cur.k0 = v.x; cur.k1 = v.y;
+        if (cur.k1 == 0) {
+            cur = cas128(&gt[slot], key);
+            if (cur.k1 == 0) cur = key; // the slot is ours
         }
-        if (key_is_long(k) && key_len(k) == len &&
-            bytes_equal(bytes, key_off(k), key_off(key), len)) {
+        if (same_key(cur, key, bytes)) {
             atomicAdd(&gt[slot].cnt, (unsigned long long)n);
             return;
         }
@@ -256,6 +277,8 @@ __device__ inline uint32_t scan_long_token(const uint8_t *bytes, uint64_t off, u
     *hash_out = (uint32_t)(h >> 32);
     return len;
 }
+
+
 
 __device__ __forceinline__ uint32_t lanemask_lt()
 {

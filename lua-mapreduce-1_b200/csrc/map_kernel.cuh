@@ -8,20 +8,22 @@
 // 16-byte boundary, every gap and the tail filled with 0x20, so split boundaries are
 // token boundaries and the kernel never needs to know where splits start.  The arena
 // is cut into segments of SEG = 1024 bytes; a warp owns a segment at a time:
-//   1. each lane loads its 32 consecutive bytes (2 x 16-byte loads, one 32-byte sector
-//      per lane), writes them to the warp's staging buffer and derives a 32-bit
+//   1. each lane loads its 32 consecutive bytes (2 x 16-byte streaming loads, one 32-byte
+//      sector per lane), writes them to the warp's staging buffer and derives a 32-bit
 //      non-whitespace mask with byte-parallel arithmetic; the 32 masks form a 1024-bit
 //      bitmap in shared memory (plus one word for the 32 look-ahead bytes);
 //   2. token starts (mask & ~(mask << 1 | carry-from-previous-lane)) are counted,
 //      warp-scanned and their positions compacted into a per-warp list, so that
-//   3. every lane takes ONE token: 8 bytes from the staging buffer (3 aligned words +
-//      funnel shifts), its length from the bitmap (funnel shift + find-first-zero), and
-//      for length <= 7 packs the key word, hashes it and bumps its slot in the CTA's
-//      shared-memory table (LDS probe + ATOMS.ADD; ATOMS.CAS.64 only on first sight).
-// Keys that do not fit the CTA table and keys of 8+ bytes are queued per warp and
-// drained 32 at a time against the global table, so global-memory latency is paid by
-// full warps and never inside the per-token loop.  At the end every CTA flushes its
-// table into the global one.
+//   3. every lane takes ONE token: its length from the bitmap (funnel shift +
+//      find-first-zero), 16 bytes from the staging buffer (5 aligned words + funnel
+//      shifts) packed into the 128-bit inline key.  Keys of <= 7 bytes go to the CTA's
+//      shared-memory table: 4-way buckets read with two 16-byte loads, no probe loop,
+//      ATOMS.ADD on a hit, ATOMS.CAS.64 only on first sight.
+// Keys the CTA table does not hold (bucket full, or 8..15 bytes) are queued per warp and
+// inserted into the global table 32 at a time, so global-memory latency is paid by full
+// warps and never inside the per-token loop; tokens of 16+ bytes take a separate rare
+// path that keeps a reference to their bytes.  At the end every CTA flushes its table
+// into the global one.
 #pragma once
 #include "common.cuh"
 
@@ -29,7 +31,7 @@ namespace mr {
 
 constexpr int SEG = 1024;              // bytes per warp segment
 constexpr int SEG_AHEAD = 32;          // look-ahead bytes staged past the segment
-constexpr int SMEM_MAX_PROBES = 6;
+constexpr int WAYS = 4;
 
 struct MapParams {
     const uint8_t *arena;
@@ -46,8 +48,8 @@ struct __align__(16) WarpSmem {
     uint32_t stage[(SEG + SEG_AHEAD) / 4]; // 1056 B
     uint32_t bitmap[SEG / 32 + 4];         // 33 used
     uint16_t pos[SEG / 2];                 // token start positions (max one per 2 bytes)
-    unsigned long long missq[64];          // short keys for the global table
-    unsigned long long longq[64];          // arena offsets of 8+ byte tokens
+    Key gq[64];                            // keys waiting for the global table
+    unsigned long long longq[32];          // arena offsets of 16+ byte tokens
 };
 
 template <int LOG2_SLOTS>
@@ -55,26 +57,43 @@ struct MapSmemLayout {
     static constexpr int SLOTS = 1 << LOG2_SLOTS;
     static constexpr size_t keys_bytes = (size_t)SLOTS * 8;
     static constexpr size_t cnt_bytes = (size_t)SLOTS * 4;
-    static constexpr size_t misc_bytes = 16;
-    static constexpr size_t warp_off = keys_bytes + cnt_bytes + misc_bytes;
+    static constexpr size_t warp_off = keys_bytes + cnt_bytes;
     static constexpr size_t total(int warps) { return warp_off + (size_t)warps * sizeof(WarpSmem); }
 };
 
-__device__ __forceinline__ void drain_miss(const MapParams &p, WarpSmem *ws, uint32_t first,
-                                           uint32_t n, uint32_t lane)
+__device__ __forceinline__ uint4 ld_stream(const uint4 *p)
 {
-    if (lane < n) gtable_add_short(p.gtab, p.gmask, ws->missq[first + lane], 1, p.err);
+    // streaming read: the input is touched once, keep L2 for the hash table
+    uint4 r;
+    asm volatile("ld.global.cs.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
 }
 
-__device__ __forceinline__ void drain_long(const MapParams &p, WarpSmem *ws, uint32_t first,
-                                           uint32_t n, uint32_t lane)
+__device__ __forceinline__ ulonglong2 lds128(const void *p)
+{
+    // one 16-byte shared-memory load of two table keys (other warps update the table concurrently)
+    ulonglong2 r;
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "r"(a));
+    return r;
+}
+
+__device__ __forceinline__ void drain_keys(const MapParams &p, WarpSmem *ws, uint32_t first, uint32_t n,
+                                           uint32_t lane)
+{
+    if (lane < n) gtable_add(p.gtab, p.gmask, p.arena, ws->gq[first + lane], 1, p.err);
+}
+
+__device__ __forceinline__ void drain_long(const MapParams &p, WarpSmem *ws, uint32_t n, uint32_t lane)
 {
     if (lane < n) {
-        uint64_t off = ws->longq[first + lane];
+        uint64_t off = ws->longq[lane];
         uint32_t h;
         uint32_t len = scan_long_token(p.arena, off, p.max_token, &h);
         if (len == 0) atomicOr(p.err, ERR_TOKEN_TOO_LONG);
-        else gtable_add_long(p.gtab, p.gmask, p.arena, make_long_key(off, len), h, 1, p.err);
+        else gtable_add(p.gtab, p.gmask, p.arena, make_long_key(off, len, h), 1, p.err);
     }
 }
 
@@ -82,22 +101,19 @@ template <int WARPS, int LOG2_SLOTS>
 __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
 {
     using L = MapSmemLayout<LOG2_SLOTS>;
-    constexpr uint32_t SLOTS = L::SLOTS, SMASK = SLOTS - 1;
-    constexpr uint32_t FILL_LIMIT = SLOTS - SLOTS / 4; // stop inserting at 75 % load
+    constexpr uint32_t SLOTS = L::SLOTS, BUCKETS = SLOTS / WAYS;
     extern __shared__ __align__(16) uint8_t smem[];
     unsigned long long *tkeys = (unsigned long long *)smem;
     unsigned int *tcnt = (unsigned int *)(smem + L::keys_bytes);
-    unsigned int *tused = (unsigned int *)(smem + L::keys_bytes + L::cnt_bytes);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpSmem *ws = (WarpSmem *)(smem + L::warp_off) + warp;
 
     for (uint32_t i = tid; i < SLOTS; i += WARPS * 32) { tkeys[i] = 0; tcnt[i] = 0; }
-    if (tid == 0) *tused = 0;
     __syncthreads();
 
     const uint32_t lt = lanemask_lt();
-    uint32_t nmiss = 0, nlong = 0; // warp-uniform queue fills
+    uint32_t nq = 0; // warp-uniform fill of gq
     unsigned long long my_tokens = 0;
     const uint64_t gwarp = (uint64_t)blockIdx.x * WARPS + warp, nwarps = (uint64_t)gridDim.x * WARPS;
 
@@ -105,7 +121,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         const uint64_t base = (p.first_seg + s) * SEG;
         const uint4 *src = (const uint4 *)(p.arena + base);
         // ---- 1. load + stage + non-space mask
-        uint4 a = __ldg(src + 2 * lane), b = __ldg(src + 2 * lane + 1);
+        uint4 a = ld_stream(src + 2 * lane), b = ld_stream(src + 2 * lane + 1);
         uint4 ahead = make_uint4(0, 0, 0, 0);
         if (lane < SEG_AHEAD / 16) ahead = __ldg(src + SEG / 16 + lane);
         uint32_t prev_ns = 0; // is the byte before the segment a token byte?
@@ -124,7 +140,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                           nonspace_nibble(ahead.z) << 8 | nonspace_nibble(ahead.w) << 12;
             am <<= 16 * lane;
             am |= __shfl_xor_sync(0x3u, am, 1);
-            if (lane == 0) { ws->bitmap[32] = am; ws->bitmap[33] = 0; }
+            if (lane == 0) ws->bitmap[32] = am;
         }
         // ---- 2. token starts, scan, compaction
         uint32_t carry = __shfl_up_sync(0xFFFFFFFFu, m >> 31, 1);
@@ -144,72 +160,85 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             ws->pos[o++] = (uint16_t)(lane * 32 + bit);
         }
         my_tokens += cnt;
-        const bool can_insert = *(volatile unsigned int *)tused < FILL_LIMIT;
-        uint32_t inserted = 0;
         __syncwarp();
         // ---- 3. one token per lane
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
             const uint32_t j = t0 + lane;
-            bool miss = false, is_long = false;
-            uint64_t key = 0;
+            bool to_global = false, is_long = false;
+            Key key;
+            key.k0 = 0; key.k1 = 0;
             uint32_t pos = 0;
             if (j < total) {
                 pos = ws->pos[j];
-                uint32_t w = pos >> 5, sh = pos & 31;
-                uint32_t bits = __funnelshift_r(ws->bitmap[w], ws->bitmap[w + 1], sh);
-                uint32_t len = (uint32_t)__ffs((int)~bits) - 1u; // 0xFFFFFFFF when 32+ bytes
-                if (len > 7) {
+                const uint32_t w = pos >> 5, sh = pos & 31;
+                const uint32_t bits = __funnelshift_r(ws->bitmap[w], ws->bitmap[w + 1], sh);
+                const uint32_t len = (uint32_t)__ffs((int)~bits) - 1u; // 0xFFFFFFFF when 32+ bytes
+                if (len > INLINE_MAX) {
                     is_long = true;
                 } else {
-                    uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
-                    uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2];
-                    uint64_t raw = (uint64_t)__funnelshift_r(x0, x1, bs) |
-                                   ((uint64_t)__funnelshift_r(x1, x2, bs) << 32);
-                    key = (raw & ((1ull << (8 * len)) - 1)) | ((uint64_t)len << 56);
-                    uint32_t slot = hash_word(key) >> (32 - LOG2_SLOTS);
-                    miss = true;
-#pragma unroll 1
-                    for (int pr = 0; pr < SMEM_MAX_PROBES; ++pr) {
-                        unsigned long long k = *(volatile unsigned long long *)&tkeys[slot];
-                        if (k == 0) {
-                            if (!can_insert) break;
-                            k = atomicCAS(&tkeys[slot], 0ull, (unsigned long long)key);
-                            if (k == 0) { k = key; ++inserted; }
+                    const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
+                    const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2],
+                                   x3 = ws->stage[wi + 3], x4 = ws->stage[wi + 4];
+                    const uint64_t r0 = (uint64_t)__funnelshift_r(x0, x1, bs) |
+                                        ((uint64_t)__funnelshift_r(x1, x2, bs) << 32);
+                    const uint64_t r1 = (uint64_t)__funnelshift_r(x2, x3, bs) |
+                                        ((uint64_t)__funnelshift_r(x3, x4, bs) << 32);
+                    // keep bytes [0, len): byte masks for the low and the high word
+                    const uint64_t m0 = len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1);
+                    const uint64_t m1 = len <= 8 ? 0ull : ((1ull << (8 * (len - 8))) - 1);
+                    key.k0 = r0 & m0;
+                    key.k1 = (r1 & m1) | ((uint64_t)len << 56);
+                    to_global = true;
+                    if (len <= 7) {
+                        const unsigned long long sk = key.k0 | key.k1; // bytes + length in one word
+                        const uint32_t bucket = hash_word(sk) >> (32 - (LOG2_SLOTS - 2));
+                        const unsigned long long *bk = tkeys + bucket * WAYS;
+                        const ulonglong2 q0 = lds128(bk), q1 = lds128(bk + 2);
+                        int way = q0.x == sk ? 0 : q0.y == sk ? 1 : q1.x == sk ? 2 : q1.y == sk ? 3 : -1;
+                        if (way < 0) {
+                            const int e = q0.x == 0 ? 0 : q0.y == 0 ? 1 : q1.x == 0 ? 2 : q1.y == 0 ? 3 : -1;
+                            if (e >= 0) {
+                                const unsigned long long old = atomicCAS(&tkeys[bucket * WAYS + e], 0ull, sk);
+                                if (old == 0 || old == sk) way = e;
+                            }
                         }
-                        if (k == key) {
-                            atomicAdd(&tcnt[slot], 1u);
-                            miss = false;
-                            break;
+                        if (way >= 0) {
+                            atomicAdd(&tcnt[bucket * WAYS + way], 1u);
+                            to_global = false;
                         }
-                        slot = (slot + 1) & SMASK;
                     }
                 }
             }
             // queue what the CTA table did not take
-            uint32_t mm = __ballot_sync(0xFFFFFFFFu, miss);
-            if (miss) ws->missq[nmiss + __popc(mm & lt)] = key;
-            nmiss += __popc(mm);
-            uint32_t lm = __ballot_sync(0xFFFFFFFFu, is_long);
-            if (is_long) ws->longq[nlong + __popc(lm & lt)] = base + pos;
-            nlong += __popc(lm);
+            const uint32_t gm = __ballot_sync(0xFFFFFFFFu, to_global);
+            if (to_global) ws->gq[nq + __popc(gm & lt)] = key;
+            nq += __popc(gm);
+            const uint32_t lm = __ballot_sync(0xFFFFFFFFu, is_long);
+            if (lm) { // rare: handle immediately, one token per lane
+                if (is_long) ws->longq[__popc(lm & lt)] = base + pos;
+                __syncwarp();
+                drain_long(p, ws, __popc(lm), lane);
+            }
             __syncwarp();
-            if (nmiss >= 32) { nmiss -= 32; drain_miss(p, ws, nmiss, 32, lane); __syncwarp(); }
-            if (nlong >= 32) { nlong -= 32; drain_long(p, ws, nlong, 32, lane); __syncwarp(); }
+            if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
         }
-        if (inserted) atomicAdd(tused, inserted);
         __syncwarp();
     }
-    // leftovers
-    drain_miss(p, ws, 0, nmiss, lane);
-    drain_long(p, ws, 0, nlong, lane);
+    drain_keys(p, ws, 0, nq, lane);
     for (int d = 16; d; d >>= 1) my_tokens += __shfl_xor_sync(0xFFFFFFFFu, my_tokens, d);
     if (lane == 0 && my_tokens) atomicAdd(p.tokens, my_tokens);
     __syncthreads();
     // flush the CTA table
     for (uint32_t i = tid; i < SLOTS; i += WARPS * 32) {
-        unsigned long long k = tkeys[i];
-        if (k) gtable_add_short(p.gtab, p.gmask, k, tcnt[i], p.err);
+        const unsigned long long sk = tkeys[i];
+        if (sk) {
+            Key k;
+            k.k0 = sk & LOW56;
+            k.k1 = sk & ~LOW56;
+            gtable_add(p.gtab, p.gmask, p.arena, k, tcnt[i], p.err);
+        }
     }
+    (void)BUCKETS;
 }
 
 } // namespace mr

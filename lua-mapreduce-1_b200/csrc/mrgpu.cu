@@ -26,6 +26,7 @@ namespace {
 std::string g_create_error;
 
 constexpr uint64_t ARENA_SLACK = SEG + SEG_AHEAD + 256;
+constexpr uint64_t REC_BYTES = 24; // shuffle record {k0, k1, count}
 
 inline uint64_t round_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
@@ -48,13 +49,13 @@ __global__ void __launch_bounds__(256) export_count_kernel(EntryArrays ent, uint
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         uint32_t d = ent.part[i] % world;
         atomicAdd(&nrec[d], 1ull);
-        uint64_t k = ent.key[i];
+        Key k = ent.key(i);
         if (key_is_long(k)) atomicAdd(&nbytes[d], (unsigned long long)key_len(k));
     }
 }
 
-// segment layout per destination: [records 16 B each][long-key bytes]; long keys are
-// rewritten to offsets relative to the start of the segment's byte block
+// segment layout per destination: [records 24 B each {k0, k1, count}][long-key bytes]; long
+// keys are rewritten to offsets relative to the start of the segment's byte block
 __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, const uint8_t *bytes,
                                                              uint32_t world, uint8_t *send,
                                                              const unsigned long long *seg_off,
@@ -66,19 +67,20 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         uint32_t d = ent.part[i] % world;
-        uint64_t k = ent.key[i];
+        Key k = ent.key(i);
         uint8_t *seg = send + seg_off[d];
         unsigned long long r = atomicAdd(&rec_cur[d], 1ull);
         if (key_is_long(k)) {
             uint32_t len = key_len(k);
             unsigned long long bo = atomicAdd(&byte_cur[d], (unsigned long long)len);
-            uint8_t *dst = seg + nrec_total[d] * 16 + bo;
+            uint8_t *dst = seg + nrec_total[d] * REC_BYTES + bo;
             uint64_t off = key_off(k);
             for (uint32_t j = 0; j < len; ++j) dst[j] = bytes[off + j];
-            k = make_long_key(bo, len);
+            k = make_long_key(bo, len, (uint32_t)k.k1);
         }
-        ((unsigned long long *)seg)[2 * r] = k;
-        ((unsigned long long *)seg)[2 * r + 1] = ent.cnt[i];
+        ((unsigned long long *)seg)[3 * r] = k.k0;
+        ((unsigned long long *)seg)[3 * r + 1] = k.k1;
+        ((unsigned long long *)seg)[3 * r + 2] = ent.cnt[i];
     }
 }
 
@@ -89,12 +91,12 @@ __global__ void __launch_bounds__(256) import_segment_kernel(const uint8_t *recv
 {
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const unsigned long long *rec = (const unsigned long long *)(recv + seg_off);
-    const uint64_t bytes_at = seg_off + nrec * 16;
+    const uint64_t bytes_at = seg_off + nrec * REC_BYTES;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += stride) {
-        uint64_t k = rec[2 * i];
-        if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k));
-        ent.key[ent_base + i] = k;
-        ent.cnt[ent_base + i] = rec[2 * i + 1];
+        Key k; k.k0 = rec[3 * i]; k.k1 = rec[3 * i + 1];
+        if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k), (uint32_t)k.k1);
+        ent.k0[ent_base + i] = k.k0; ent.k1[ent_base + i] = k.k1;
+        ent.cnt[ent_base + i] = rec[3 * i + 2];
     }
 }
 
@@ -256,12 +258,12 @@ void mr_ctx_destroy(mr_ctx *ctx)
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab);
-    cudaFree(ctx->ent.key); cudaFree(ctx->ent.cnt); cudaFree(ctx->ent.part);
+    cudaFree(ctx->ent.k0); cudaFree(ctx->ent.k1); cudaFree(ctx->ent.cnt); cudaFree(ctx->ent.part);
     for (int i = 0; i < 2; ++i) { cudaFree(ctx->bufs.hi[i]); cudaFree(ctx->bufs.lo[i]); cudaFree(ctx->bufs.val[i]); }
     cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv); cudaFree(ctx->d_head);
     cudaFree(ctx->d_outidx); cudaFree(ctx->d_partial);
     cudaFree(ctx->rows.part); cudaFree(ctx->rows.count); cudaFree(ctx->rows.key_off);
-    cudaFree(ctx->rows.key_bytes); cudaFree(ctx->rows.key); cudaFree(ctx->rows.len);
+    cudaFree(ctx->rows.key_bytes); cudaFree(ctx->rows.k0); cudaFree(ctx->rows.k1); cudaFree(ctx->rows.len);
     cudaFree(ctx->rows.part_begin);
     cudaFree(ctx->d_ctl); cudaFree(ctx->d_send); cudaFree(ctx->d_recv); cudaFree(ctx->d_shuf);
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
@@ -337,7 +339,8 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     else { CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
     CUC(dmalloc(&ctx->d_arena, ctx->arena_cap + ARENA_SLACK));
     CUC(dmalloc(&ctx->d_gtab, slots));
-    CUC(dmalloc(&ctx->ent.key, mk)); CUC(dmalloc(&ctx->ent.cnt, mk)); CUC(dmalloc(&ctx->ent.part, mk));
+    CUC(dmalloc(&ctx->ent.k0, mk)); CUC(dmalloc(&ctx->ent.k1, mk));
+    CUC(dmalloc(&ctx->ent.cnt, mk)); CUC(dmalloc(&ctx->ent.part, mk));
     for (int i = 0; i < 2; ++i) {
         CUC(dmalloc(&ctx->bufs.hi[i], mk)); CUC(dmalloc(&ctx->bufs.lo[i], mk)); CUC(dmalloc(&ctx->bufs.val[i], mk));
     }
@@ -348,7 +351,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->d_partial, (mk + SCAN_TILE - 1) / SCAN_TILE + 1));
     CUC(dmalloc(&ctx->rows.part, mk)); CUC(dmalloc(&ctx->rows.count, mk));
     CUC(dmalloc(&ctx->rows.key_off, mk + 1)); CUC(dmalloc(&ctx->rows.key_bytes, ctx->key_bytes_cap));
-    CUC(dmalloc(&ctx->rows.key, mk)); CUC(dmalloc(&ctx->rows.len, mk));
+    CUC(dmalloc(&ctx->rows.k0, mk)); CUC(dmalloc(&ctx->rows.k1, mk)); CUC(dmalloc(&ctx->rows.len, mk));
     CUC(dmalloc(&ctx->rows.part_begin, (uint64_t)cfg->num_reducers + 1));
     CUC(dmalloc(&ctx->d_ctl, 1));
     CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
@@ -743,7 +746,7 @@ int mr_shuffle_export(mr_ctx *ctx, mr_shuffle_plan *plan)
     ctx->send_nrec.assign(W, 0);
     for (uint32_t d = 0; d < W; ++d) {
         ctx->send_nrec[d] = h[d];
-        ctx->send_off[d + 1] = ctx->send_off[d] + round_up(h[d] * 16 + h[W + d], 16);
+        ctx->send_off[d + 1] = ctx->send_off[d] + round_up(h[d] * REC_BYTES + h[W + d], 16);
     }
     const uint64_t total = ctx->send_off[W];
     if (total + 64 > ctx->send_cap) {
@@ -794,7 +797,7 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
     uint64_t base = 0;
     for (uint32_t src = 0; src < W; ++src) {
         uint64_t n = nrec[src];
-        if (recv_off[src] + n * 16 > recv_off[src + 1]) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import: segment %u too small", src);
+        if (recv_off[src] + n * REC_BYTES > recv_off[src + 1]) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import: segment %u too small", src);
         if (base + n > ctx->max_keys) return fail(ctx, MR_ERR_NOMEM, "mr_shuffle_import: more than max_keys records");
         if (n) {
             import_segment_kernel<<<grid_for(n, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->d_recv, recv_off[src], n, base, ctx->ent);

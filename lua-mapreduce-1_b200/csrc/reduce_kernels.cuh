@@ -43,9 +43,10 @@ struct Ctl {
 
 // ------------------------------------------------------------------ K3
 struct EntryArrays {
-    unsigned long long *key;  // key word
+    unsigned long long *k0, *k1; // key words (common.cuh)
     unsigned long long *cnt;
     uint32_t *part;
+    __device__ __forceinline__ Key key(uint64_t i) const { Key k; k.k0 = k0[i]; k.k1 = k1[i]; return k; }
 };
 
 __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
@@ -82,12 +83,14 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
     const uint64_t rounds = (nslots + stride - 1) / stride;
     for (uint64_t r = 0; r < rounds; ++r) {
         uint64_t slot = r * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-        GEntry e = { 0, 0 };
+        Key key; key.k0 = 0; key.k1 = 0;
+        unsigned long long ecnt = 0;
         if (slot < nslots) {
             ulonglong2 v = __ldcg((const ulonglong2 *)&gt[slot]);
-            e.key = v.x; e.cnt = v.y;
+            key.k0 = v.x; key.k1 = v.y;
+            if (v.y) ecnt = __ldcg(&gt[slot].cnt);
         }
-        bool occ = e.key != 0;
+        bool occ = key.k1 != 0;
         uint32_t mask = __ballot_sync(0xFFFFFFFFu, occ);
         if (!mask) continue;
         unsigned long long base = 0;
@@ -96,9 +99,9 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
         if (occ) {
             uint64_t idx = base + __popc(mask & lt);
             if (idx >= max_keys) { atomicOr(&ctl->err, ERR_KEYS_FULL); continue; }
-            uint32_t part = partition_of_key(e.key, bytes, num_reducers);
-            uint64_t chunk = sort_chunk(e.key, bytes, 0);
-            ent.key[idx] = e.key; ent.cnt[idx] = e.cnt; ent.part[idx] = part;
+            uint32_t part = partition_of_key(key, bytes, num_reducers);
+            uint64_t chunk = sort_chunk(key, bytes, 0);
+            ent.k0[idx] = key.k0; ent.k1[idx] = key.k1; ent.cnt[idx] = ecnt; ent.part[idx] = part;
             sk_hi[idx] = part; sk_lo[idx] = chunk; val[idx] = (uint32_t)idx;
             hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
             any = true;
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
     const uint64_t n = ctl->n;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
-        uint64_t key = ent.key[idx];
+        Key key = ent.key(idx);
         uint32_t part = partition_of_key(key, bytes, num_reducers);
         uint64_t chunk = sort_chunk(key, bytes, 0);
         ent.part[idx] = part;
@@ -310,14 +313,19 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
 // ------------------------------------------------------------------ ties beyond 7 bytes
 struct TieItem { uint32_t pos, val; };
 
-__device__ __forceinline__ bool tie_less(const TieItem &a, const TieItem &b, const EntryArrays &ent,
-                                         const uint8_t *bytes)
+__device__ inline bool tie_less(const TieItem &a, const TieItem &b, const EntryArrays &ent,
+                                const uint8_t *bytes)
 {
     if (a.pos == 0xFFFFFFFFu || b.pos == 0xFFFFFFFFu) return a.pos != 0xFFFFFFFFu && b.pos == 0xFFFFFFFFu;
     uint32_t pa = ent.part[a.val], pb = ent.part[b.val];
     if (pa != pb) return pa < pb;
-    int c = long_key_compare(bytes, ent.key[a.val], ent.key[b.val]);
-    if (c) return c < 0;
+    const Key ka = ent.key(a.val), kb = ent.key(b.val);
+    // round by round, 7 key bytes at a time (round 0 is what the radix sort already used)
+    for (uint32_t r = 0;; ++r) {
+        uint64_t ca = sort_chunk(ka, bytes, r), cb = sort_chunk(kb, bytes, r);
+        if (ca != cb) return ca < cb;
+        if ((ca & 0xFF) < 8) break; // both keys end here: equal
+    }
     return a.val < b.val;
 }
 
@@ -499,14 +507,6 @@ __global__ void __launch_bounds__(256) scan_final_kernel(const uint32_t *in, con
 }
 
 // ------------------------------------------------------------------ K6 / K7
-__device__ __forceinline__ bool same_key(uint64_t ka, uint64_t kb, const uint8_t *bytes)
-{
-    if (ka == kb) return true;
-    if (!key_is_long(ka) || !key_is_long(kb)) return false;
-    uint32_t la = key_len(ka);
-    return la == key_len(kb) && bytes_equal(bytes, key_off(ka), key_off(kb), la);
-}
-
 // head[i] = 1 when sorted position i starts a new key
 __global__ void __launch_bounds__(256) head_mark_kernel(SortBufs bufs, EntryArrays ent, const uint8_t *bytes,
                                                         uint32_t *head, const Ctl *ctl)
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(256) head_mark_kernel(SortBufs bufs, EntryArra
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         uint32_t h = 1;
         if (i > 0 && bufs.hi[fin][i] == bufs.hi[fin][i - 1] && bufs.lo[fin][i] == bufs.lo[fin][i - 1])
-            h = same_key(ent.key[bufs.val[fin][i]], ent.key[bufs.val[fin][i - 1]], bytes) ? 0u : 1u;
+            h = same_key(ent.key(bufs.val[fin][i]), ent.key(bufs.val[fin][i - 1]), bytes) ? 0u : 1u;
         head[i] = h;
     }
 }
@@ -527,7 +527,7 @@ struct RowArrays {
     unsigned long long *count;
     unsigned long long *key_off; // [n_out + 1]
     uint8_t *key_bytes;
-    unsigned long long *key;     // key word of the row (internal)
+    unsigned long long *k0, *k1; // key words of the row (internal)
     uint32_t *len;
     unsigned long long *part_begin; // [R + 1]
 };
@@ -546,10 +546,10 @@ __global__ void __launch_bounds__(256) reduce_rows_kernel(SortBufs bufs, EntryAr
         unsigned long long c = ent.cnt[v];
         for (uint64_t j = i + 1; j < n && !head[j]; ++j) c += ent.cnt[bufs.val[fin][j]];
         uint64_t o = out_idx[i];
-        uint64_t key = ent.key[v];
+        const Key key = ent.key(v);
         rows.part[o] = ent.part[v];
         rows.count[o] = c;
-        rows.key[o] = key;
+        rows.k0[o] = key.k0; rows.k1[o] = key.k1;
         rows.len[o] = key_len(key);
     }
 }
@@ -566,11 +566,12 @@ __global__ void __launch_bounds__(256) write_key_bytes_kernel(RowArrays rows, co
         uint32_t p_cur = o == n ? num_reducers : rows.part[o];
         for (uint32_t p = p_prev; p <= p_cur && p <= num_reducers; ++p) rows.part_begin[p] = o;
         if (o == n) { rows.key_off[n] = ctl->key_bytes; break; }
-        uint64_t key = rows.key[o];
+        Key key; key.k0 = rows.k0[o]; key.k1 = rows.k1[o];
         uint8_t *dst = rows.key_bytes + rows.key_off[o];
         uint32_t len = rows.len[o];
         if (!key_is_long(key)) {
-            for (uint32_t i = 0; i < len; ++i) dst[i] = (uint8_t)(key >> (8 * i));
+            for (uint32_t i = 0; i < len && i < 8; ++i) dst[i] = (uint8_t)(key.k0 >> (8 * i));
+            for (uint32_t i = 8; i < len; ++i) dst[i] = (uint8_t)(key.k1 >> (8 * (i - 8)));
         } else {
             uint64_t off = key_off(key);
             for (uint32_t i = 0; i < len; i += 8) {
