@@ -71,13 +71,21 @@ __device__ __forceinline__ uint4 ld_stream(const uint4 *p)
     return r;
 }
 
-__device__ __forceinline__ ulonglong2 lds128(const void *p)
+__device__ __forceinline__ ulonglong2 lds128(uint32_t saddr)
 {
     // one 16-byte shared-memory load of two table keys (other warps update the table concurrently)
     ulonglong2 r;
-    uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
-    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "r"(a));
+    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "r"(saddr));
     return r;
+}
+
+// x with the bytes at index >= n cleared; n may be <= 0 (clears all) or >= 4 (keeps all).
+// PTX shl clamps shift amounts above 31, which C does not.
+__device__ __forceinline__ uint32_t keep_low_bytes(uint32_t x, int n)
+{
+    uint32_t hi;
+    asm("shl.b32 %0, %1, %2;" : "=r"(hi) : "r"(0xFFFFFFFFu), "r"((uint32_t)max(n, 0) * 8u));
+    return x & ~hi;
 }
 
 __device__ __forceinline__ void drain_keys(const MapParams &p, WarpSmem *ws, uint32_t first, uint32_t n,
@@ -105,11 +113,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
     extern __shared__ __align__(16) uint8_t smem[];
     unsigned long long *tkeys = (unsigned long long *)smem;
     unsigned int *tcnt = (unsigned int *)(smem + L::keys_bytes);
+    __shared__ unsigned int tused;                       // keys held by the CTA table
+    constexpr uint32_t FILL_LIMIT = SLOTS - SLOTS / 8;   // stop trying to insert at 87.5 % load
+    const uint32_t tkeys_s = (uint32_t)__cvta_generic_to_shared(tkeys);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpSmem *ws = (WarpSmem *)(smem + L::warp_off) + warp;
 
     for (uint32_t i = tid; i < SLOTS; i += WARPS * 32) { tkeys[i] = 0; tcnt[i] = 0; }
+    if (tid == 0) tused = 0;
     __syncthreads();
 
     const uint32_t lt = lanemask_lt();
@@ -160,6 +172,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             ws->pos[o++] = (uint16_t)(lane * 32 + bit);
         }
         my_tokens += cnt;
+        const bool can_insert = *(volatile unsigned int *)&tused < FILL_LIMIT; // warp-uniform
+        uint32_t inserted = 0;
         __syncwarp();
         // ---- 3. one token per lane
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
@@ -177,29 +191,34 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                     is_long = true;
                 } else {
                     const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
-                    const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2],
-                                   x3 = ws->stage[wi + 3], x4 = ws->stage[wi + 4];
-                    const uint64_t r0 = (uint64_t)__funnelshift_r(x0, x1, bs) |
-                                        ((uint64_t)__funnelshift_r(x1, x2, bs) << 32);
-                    const uint64_t r1 = (uint64_t)__funnelshift_r(x2, x3, bs) |
-                                        ((uint64_t)__funnelshift_r(x3, x4, bs) << 32);
-                    // keep bytes [0, len): byte masks for the low and the high word
-                    const uint64_t m0 = len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1);
-                    const uint64_t m1 = len <= 8 ? 0ull : ((1ull << (8 * (len - 8))) - 1);
-                    key.k0 = r0 & m0;
-                    key.k1 = (r1 & m1) | ((uint64_t)len << 56);
+                    const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2];
+                    uint32_t x3 = 0, x4 = 0;
+                    if (len > 7) { x3 = ws->stage[wi + 3]; x4 = ws->stage[wi + 4]; }
+                    const int n = (int)len;
+                    const uint32_t w0 = keep_low_bytes(__funnelshift_r(x0, x1, bs), n);
+                    const uint32_t w1 = keep_low_bytes(__funnelshift_r(x1, x2, bs), n - 4);
+                    const uint32_t w2 = keep_low_bytes(__funnelshift_r(x2, x3, bs), n - 8);
+                    const uint32_t w3 = keep_low_bytes(__funnelshift_r(x3, x4, bs), n - 12);
+                    key.k0 = (uint64_t)w0 | ((uint64_t)w1 << 32);
+                    key.k1 = (uint64_t)w2 | ((uint64_t)(w3 | (len << 24)) << 32);
                     to_global = true;
                     if (len <= 7) {
-                        const unsigned long long sk = key.k0 | key.k1; // bytes + length in one word
-                        const uint32_t bucket = hash_word(sk) >> (32 - (LOG2_SLOTS - 2));
-                        const unsigned long long *bk = tkeys + bucket * WAYS;
-                        const ulonglong2 q0 = lds128(bk), q1 = lds128(bk + 2);
-                        int way = q0.x == sk ? 0 : q0.y == sk ? 1 : q1.x == sk ? 2 : q1.y == sk ? 3 : -1;
+                        const uint32_t skh = w1 | (len << 24);
+                        const unsigned long long sk = (uint64_t)w0 | ((uint64_t)skh << 32); // bytes + length
+                        const uint32_t bucket = (w0 * 0x9E3779B1u + skh * 0x85EBCA77u) >> (32 - (LOG2_SLOTS - 2));
+                        const uint32_t baddr = tkeys_s + bucket * (WAYS * 8);
+                        const ulonglong2 q0 = lds128(baddr);
+                        int way = q0.x == sk ? 0 : q0.y == sk ? 1 : -1;
                         if (way < 0) {
-                            const int e = q0.x == 0 ? 0 : q0.y == 0 ? 1 : q1.x == 0 ? 2 : q1.y == 0 ? 3 : -1;
-                            if (e >= 0) {
-                                const unsigned long long old = atomicCAS(&tkeys[bucket * WAYS + e], 0ull, sk);
-                                if (old == 0 || old == sk) way = e;
+                            const ulonglong2 q1 = lds128(baddr + 16);
+                            way = q1.x == sk ? 2 : q1.y == sk ? 3 : -1;
+                            if (way < 0 && can_insert) {
+                                const int e = q0.x == 0 ? 0 : q0.y == 0 ? 1 : q1.x == 0 ? 2 : q1.y == 0 ? 3 : -1;
+                                if (e >= 0) {
+                                    const unsigned long long old = atomicCAS(&tkeys[bucket * WAYS + e], 0ull, sk);
+                                    if (old == 0) ++inserted;
+                                    if (old == 0 || old == sk) way = e;
+                                }
                             }
                         }
                         if (way >= 0) {
@@ -222,6 +241,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             __syncwarp();
             if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
         }
+        if (inserted) atomicAdd(&tused, inserted);
         __syncwarp();
     }
     drain_keys(p, ws, 0, nq, lane);

@@ -472,12 +472,13 @@ namespace {
 // table -> entries (+ partition, sort keys).  Idempotent guard: done once per job.
 int launch_compact(mr_ctx *ctx)
 {
-    unsigned grid = grid_for(ctx->slots, 256, ctx->sm_count * 8);
-    compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->bytes_base,
-                                                            ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0],
-                                                            ctx->bufs.lo[0], ctx->bufs.val[0], ctx->max_keys,
-                                                            ctx->d_ctl);
-    ctx->stats.launches++;
+    const uint64_t tiles = (ctx->slots + 256 * COMPACT_ITEMS - 1) / (256 * COMPACT_ITEMS);
+    unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
+    compact_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->ent, ctx->max_keys, ctx->d_ctl);
+    partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0], ctx->bufs.lo[0], ctx->bufs.val[0],
+        ctx->max_keys, ctx->d_ctl);
+    ctx->stats.launches += 2;
     CU(cudaGetLastError());
     return MR_OK;
 }
@@ -811,7 +812,7 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
     ctl_set_n_kernel<<<1, 1, 0, s>>>(ctx->d_ctl, base);
     ctx->bytes_base = ctx->d_recv;
     partition_entries_kernel<<<grid_for(std::max<uint64_t>(base, 1), 256, ctx->sm_count * 4), 256, 0, s>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0], ctx->bufs.lo[0], ctx->bufs.val[0], ctx->d_ctl);
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0], ctx->bufs.lo[0], ctx->bufs.val[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 3;
     CU(cudaGetLastError());
     ctx->imported = true;

@@ -20,7 +20,7 @@ constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // 4096
 constexpr int SCAN_TILE = 4096;
-constexpr uint32_t TIE_SMALL_MAX = 2048; // tie entries resolved inside one CTA
+constexpr uint32_t TIE_SMALL_MAX = 1024; // tie entries resolved inside one CTA
 
 struct DigitRun { uint8_t shift, width, dst, pad; }; // shift 0..63 -> lo, 64..95 -> hi
 
@@ -69,56 +69,67 @@ __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t 
     }
 }
 
-// table slots -> dense entries (+ partition, sort key).  Order of entries is arbitrary.
-__global__ void __launch_bounds__(256) compact_partition_kernel(
-    const GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers,
-    EntryArrays ent, uint32_t *sk_hi, unsigned long long *sk_lo, uint32_t *val,
-    uint64_t max_keys, Ctl *ctl)
+// table slots -> dense entries.  Order of entries is arbitrary.  One atomic per 1024-slot
+// tile reserves the output range (a per-warp atomic on one address costs ~1.4 ns each).
+constexpr int COMPACT_ITEMS = 4;
+__global__ void __launch_bounds__(256) compact_kernel(const GEntry *gt, uint64_t nslots, EntryArrays ent,
+                                                      uint64_t max_keys, Ctl *ctl)
 {
-    const uint32_t lane = threadIdx.x & 31, lt = lanemask_lt();
-    uint32_t hi_or = 0, hi_and = ~0u;
-    uint64_t lo_or = 0, lo_and = ~0ull;
-    bool any = false;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    const uint64_t rounds = (nslots + stride - 1) / stride;
-    for (uint64_t r = 0; r < rounds; ++r) {
-        uint64_t slot = r * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-        Key key; key.k0 = 0; key.k1 = 0;
-        unsigned long long ecnt = 0;
-        if (slot < nslots) {
-            ulonglong2 v = __ldcg((const ulonglong2 *)&gt[slot]);
-            key.k0 = v.x; key.k1 = v.y;
-            if (v.y) ecnt = __ldcg(&gt[slot].cnt);
+    __shared__ unsigned int wsum[8];
+    __shared__ unsigned long long s_base;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t tile_slots = 256 * COMPACT_ITEMS;
+    const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        Key key[COMPACT_ITEMS];
+        uint32_t nocc = 0;
+#pragma unroll
+        for (int i = 0; i < COMPACT_ITEMS; ++i) {
+            uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
+            key[i].k0 = 0; key[i].k1 = 0;
+            if (slot < nslots) {
+                ulonglong2 v = __ldcg((const ulonglong2 *)&gt[slot]);
+                key[i].k0 = v.x; key[i].k1 = v.y;
+            }
+            nocc += key[i].k1 != 0;
         }
-        bool occ = key.k1 != 0;
-        uint32_t mask = __ballot_sync(0xFFFFFFFFu, occ);
-        if (!mask) continue;
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(&ctl->n, (unsigned long long)__popc(mask));
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (occ) {
-            uint64_t idx = base + __popc(mask & lt);
-            if (idx >= max_keys) { atomicOr(&ctl->err, ERR_KEYS_FULL); continue; }
-            uint32_t part = partition_of_key(key, bytes, num_reducers);
-            uint64_t chunk = sort_chunk(key, bytes, 0);
-            ent.k0[idx] = key.k0; ent.k1[idx] = key.k1; ent.cnt[idx] = ecnt; ent.part[idx] = part;
-            sk_hi[idx] = part; sk_lo[idx] = chunk; val[idx] = (uint32_t)idx;
-            hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
-            any = true;
+        uint32_t incl = nocc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        uint32_t woff = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { uint32_t c = wsum[w]; if (w < (int)warp) woff += c; total += c; }
+        if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n, (unsigned long long)total);
+        __syncthreads();
+        if (total) {
+            uint64_t idx = s_base + woff + incl - nocc;
+#pragma unroll
+            for (int i = 0; i < COMPACT_ITEMS; ++i) {
+                if (key[i].k1 == 0) continue;
+                uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
+                if (idx < max_keys) {
+                    ent.k0[idx] = key[i].k0; ent.k1[idx] = key[i].k1; ent.cnt[idx] = __ldcg(&gt[slot].cnt);
+                } else {
+                    atomicOr(&ctl->err, ERR_KEYS_FULL);
+                }
+                ++idx;
+            }
         }
+        __syncthreads();
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
 }
 
 // entries already dense (after a shuffle import): partition + sort key only
 __global__ void __launch_bounds__(256) partition_entries_kernel(
     const uint8_t *bytes, uint32_t num_reducers, EntryArrays ent, uint32_t *sk_hi,
-    unsigned long long *sk_lo, uint32_t *val, Ctl *ctl)
+    unsigned long long *sk_lo, uint32_t *val, uint64_t max_keys, Ctl *ctl)
 {
     uint32_t hi_or = 0, hi_and = ~0u;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
-    const uint64_t n = ctl->n;
+    const uint64_t n = ctl->n < max_keys ? ctl->n : max_keys;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
         Key key = ent.key(idx);
@@ -277,13 +288,22 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         __threadfence();
         unsigned int prefix = 0;
         if (tile > 0) {
+            // look back 8 tiles at a time: the 8 loads are independent, so a long chain of
+            // not-yet-inclusive predecessors costs one L2 round trip per 8 tiles, not per tile
             int t = (int)tile - 1;
-            for (;;) {
-                uint32_t s = st[(uint64_t)t * RADIX_BINS + b];
-                if ((s >> 30) == 0) continue; // not yet published (tickets guarantee it has started)
-                prefix += s & ST_VAL;
-                if ((s >> 30) == 2 || t == 0) break;
-                --t;
+            bool done = false;
+            while (!done) {
+                uint32_t sv[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) sv[k] = t - k >= 0 ? st[(uint64_t)(t - k) * RADIX_BINS + b] : (2u << 30);
+                int k = 0;
+#pragma unroll
+                for (; k < 8; ++k) {
+                    if ((sv[k] >> 30) == 0) break;           // not published yet: re-read from here
+                    prefix += sv[k] & ST_VAL;
+                    if ((sv[k] >> 30) == 2) { done = true; break; }
+                }
+                t -= k;
             }
             st[(uint64_t)tile * RADIX_BINS + b] = ST_INC | (prefix + tile_count);
         }
@@ -364,8 +384,8 @@ __global__ void __launch_bounds__(256) tie_mark_kernel(SortBufs bufs, TieItem *t
     }
 }
 
-// Up to TIE_SMALL_MAX ties: one CTA orders the positions and the entries (full key
-// compare) with bitonic networks in shared memory and writes the entries back.
+// Up to TIE_SMALL_MAX ties: one CTA copies their keys into shared memory, orders the positions
+// and the entries (full key compare) with bitonic networks and writes the entries back.
 __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, const TieItem *ties,
                                                              EntryArrays ent, const uint8_t *bytes,
                                                              Ctl *ctl)
@@ -373,16 +393,31 @@ __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, cons
     const uint32_t nt = ctl->n_tie;
     if (nt == 0) return;
     if (nt > TIE_SMALL_MAX) { if (threadIdx.x == 0) ctl->tie_overflow = 1; return; }
-    __shared__ TieItem items[TIE_SMALL_MAX];
-    __shared__ uint32_t posv[TIE_SMALL_MAX];
+    __shared__ Key skey[TIE_SMALL_MAX];
+    __shared__ uint32_t spart[TIE_SMALL_MAX], sval[TIE_SMALL_MAX], posv[TIE_SMALL_MAX];
+    __shared__ uint16_t order[TIE_SMALL_MAX];
     uint32_t np2 = 1;
     while (np2 < nt) np2 <<= 1;
     for (uint32_t i = threadIdx.x; i < np2; i += blockDim.x) {
-        TieItem t; t.pos = 0xFFFFFFFFu; t.val = 0;
-        if (i < nt) t = ties[i];
-        items[i] = t; posv[i] = t.pos;
+        order[i] = (uint16_t)i;
+        posv[i] = 0xFFFFFFFFu;
+        if (i < nt) {
+            TieItem t = ties[i];
+            posv[i] = t.pos; sval[i] = t.val; spart[i] = ent.part[t.val]; skey[i] = ent.key(t.val);
+        }
     }
     __syncthreads();
+    auto less = [&](uint32_t a, uint32_t b) -> bool { // a, b index the unsorted copies; >= nt is padding
+        if (a >= nt || b >= nt) return a < nt && b >= nt;
+        if (spart[a] != spart[b]) return spart[a] < spart[b];
+        const Key ka = skey[a], kb = skey[b];
+        for (uint32_t r = 0;; ++r) {
+            uint64_t ca = sort_chunk(ka, bytes, r), cb = sort_chunk(kb, bytes, r);
+            if (ca != cb) return ca < cb;
+            if ((ca & 0xFF) < 8) break;
+        }
+        return sval[a] < sval[b];
+    };
     for (uint32_t k = 2; k <= np2; k <<= 1)
         for (uint32_t j = k >> 1; j > 0; j >>= 1) {
             for (uint32_t i = threadIdx.x; i < np2; i += blockDim.x) {
@@ -391,15 +426,15 @@ __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, cons
                     bool up = (i & k) == 0;
                     uint32_t pa = posv[i], pb = posv[ixj];
                     if ((pa > pb) == up) { posv[i] = pb; posv[ixj] = pa; }
-                    TieItem a = items[i], b = items[ixj];
-                    bool swap = up ? tie_less(b, a, ent, bytes) : tie_less(a, b, ent, bytes);
-                    if (swap) { items[i] = b; items[ixj] = a; }
+                    uint32_t a = order[i], b = order[ixj];
+                    bool swap = up ? less(b, a) : less(a, b);
+                    if (swap) { order[i] = (uint16_t)b; order[ixj] = (uint16_t)a; }
                 }
             }
             __syncthreads();
         }
     const uint32_t fin = ctl->npasses & 1;
-    for (uint32_t i = threadIdx.x; i < nt; i += blockDim.x) bufs.val[fin][posv[i]] = items[i].val;
+    for (uint32_t i = threadIdx.x; i < nt; i += blockDim.x) bufs.val[fin][posv[i]] = sval[order[i]];
 }
 
 // General path (host-driven): bitonic steps over the tie list in global memory.
