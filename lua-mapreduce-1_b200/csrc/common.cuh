@@ -165,26 +165,30 @@ __device__ inline uint64_t sort_chunk(const Key &k, const uint8_t *bytes, uint32
 }
 
 // ---------------------------------------------------------------- partitioner
-// examples/WordCount/partitionfn.lua:10-15 in IEEE binary64 with Lua 5.2's
-// `a % b = a - floor(a/b)*b`.  h * prime exceeds 2^53 and rounds (nearest even);
-// dividing and multiplying by 2^32 are exact, so one rounding per byte, as in Lua.
+// examples/WordCount/partitionfn.lua:10-15.  Lua 5.2 numbers are IEEE binary64 and
+// `a % b = a - floor(a/b)*b`: h * prime can reach 2^57, so the product is rounded to 53
+// significant bits (nearest, ties to even) before `% 2^32` keeps its low 32 bits -- this is
+// NOT uint32 FNV-1.  The rounding is done here with integers (bit-for-bit the same result
+// as the double arithmetic: oracle/mr_oracle.c checks both forms against each other, and
+// the host-side mr_partition_of uses real doubles).  `h % NUM_REDUCERS` on integer-valued
+// doubles below 2^32 equals the integer remainder.
 struct FnvLua52 {
-    double h;
-    __device__ __forceinline__ FnvLua52() : h(2166136261.0) {}
+    uint32_t h;
+    __device__ __forceinline__ FnvLua52() : h(2166136261u) {}
     __device__ __forceinline__ void byte(uint32_t c)
     {
-        double p = __dmul_rn(h, 16777619.0);
-        double q = floor(__dmul_rn(p, 1.0 / 4294967296.0));
-        double m = __fma_rn(-q, 4294967296.0, p);
-        uint32_t u = __double2uint_rz(m);
-        h = (double)(u ^ c);
+        unsigned long long p = (unsigned long long)h * 16777619u;
+        const int top = 63 - __clzll((long long)p);
+        if (top >= 53) {
+            const int s = top - 52;
+            const unsigned long long half = 1ull << (s - 1), rem = p & ((1ull << s) - 1);
+            p >>= s;
+            if (rem > half || (rem == half && (p & 1))) ++p;
+            p <<= s;
+        }
+        h = (uint32_t)p ^ c;
     }
-    __device__ __forceinline__ uint32_t partition(uint32_t num_reducers) const
-    {
-        double r = (double)num_reducers;
-        double q = floor(__ddiv_rn(h, r));
-        return __double2uint_rz(__fma_rn(-q, r, h));
-    }
+    __device__ __forceinline__ uint32_t partition(uint32_t num_reducers) const { return h % num_reducers; }
 };
 
 __device__ inline uint32_t partition_of_key(const Key &k, const uint8_t *bytes, uint32_t num_reducers)

@@ -19,7 +19,7 @@
 
 using namespace mr;
 
-static_assert(SORT_THREADS == RADIX_BINS, "one thread per radix bin");
+static_assert(SORT_THREADS >= RADIX_BINS, "one thread per radix bin");
 
 namespace {
 
@@ -100,11 +100,6 @@ __global__ void __launch_bounds__(256) import_segment_kernel(const uint8_t *recv
     }
 }
 
-__global__ void __launch_bounds__(256) check_key_bytes_kernel(Ctl *ctl, unsigned long long cap)
-{
-    if (threadIdx.x == 0 && blockIdx.x == 0 && ctl->key_bytes > cap) atomicOr(&ctl->err, ERR_KEYS_FULL);
-}
-
 } // namespace
 
 struct mr_result {
@@ -140,9 +135,8 @@ struct mr_ctx {
     uint32_t max_tiles = 0;
     TieItem *d_ties = nullptr;
     uint32_t *d_posv = nullptr;
-    uint32_t *d_head = nullptr;
-    unsigned long long *d_outidx = nullptr;
-    unsigned long long *d_partial = nullptr;
+    RowsStatus rows_st{};
+    uint32_t rows_tiles = 0;
     RowArrays rows{};
     uint64_t key_bytes_cap = 0;
     Ctl *d_ctl = nullptr;
@@ -259,11 +253,11 @@ void mr_ctx_destroy(mr_ctx *ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab);
     cudaFree(ctx->ent.k0); cudaFree(ctx->ent.k1); cudaFree(ctx->ent.cnt); cudaFree(ctx->ent.part);
-    for (int i = 0; i < 2; ++i) { cudaFree(ctx->bufs.hi[i]); cudaFree(ctx->bufs.lo[i]); cudaFree(ctx->bufs.val[i]); }
-    cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv); cudaFree(ctx->d_head);
-    cudaFree(ctx->d_outidx); cudaFree(ctx->d_partial);
+    for (int i = 0; i < 2; ++i) cudaFree(ctx->bufs.item[i]);
+    cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv);
+    cudaFree(ctx->rows_st.heads);
     cudaFree(ctx->rows.part); cudaFree(ctx->rows.count); cudaFree(ctx->rows.key_off);
-    cudaFree(ctx->rows.key_bytes); cudaFree(ctx->rows.k0); cudaFree(ctx->rows.k1); cudaFree(ctx->rows.len);
+    cudaFree(ctx->rows.key_bytes);
     cudaFree(ctx->rows.part_begin);
     cudaFree(ctx->d_ctl); cudaFree(ctx->d_send); cudaFree(ctx->d_recv); cudaFree(ctx->d_shuf);
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
@@ -342,16 +336,17 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->ent.k0, mk)); CUC(dmalloc(&ctx->ent.k1, mk));
     CUC(dmalloc(&ctx->ent.cnt, mk)); CUC(dmalloc(&ctx->ent.part, mk));
     for (int i = 0; i < 2; ++i) {
-        CUC(dmalloc(&ctx->bufs.hi[i], mk)); CUC(dmalloc(&ctx->bufs.lo[i], mk)); CUC(dmalloc(&ctx->bufs.val[i], mk));
+        CUC(dmalloc(&ctx->bufs.item[i], mk));
     }
     CUC(dmalloc(&ctx->d_status, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS));
     uint64_t tie_cap = 1; while (tie_cap < mk) tie_cap <<= 1;
     CUC(dmalloc(&ctx->d_ties, tie_cap)); CUC(dmalloc(&ctx->d_posv, tie_cap));
-    CUC(dmalloc(&ctx->d_head, mk)); CUC(dmalloc(&ctx->d_outidx, mk));
-    CUC(dmalloc(&ctx->d_partial, (mk + SCAN_TILE - 1) / SCAN_TILE + 1));
+    ctx->rows_tiles = (uint32_t)((mk + ROWS_TILE - 1) / ROWS_TILE) + 1;
+    CUC(dmalloc(&ctx->rows_st.heads, 3ull * ctx->rows_tiles));
+    ctx->rows_st.bytes_agg = ctx->rows_st.heads + ctx->rows_tiles;
+    ctx->rows_st.bytes_inc = ctx->rows_st.heads + 2ull * ctx->rows_tiles;
     CUC(dmalloc(&ctx->rows.part, mk)); CUC(dmalloc(&ctx->rows.count, mk));
     CUC(dmalloc(&ctx->rows.key_off, mk + 1)); CUC(dmalloc(&ctx->rows.key_bytes, ctx->key_bytes_cap));
-    CUC(dmalloc(&ctx->rows.k0, mk)); CUC(dmalloc(&ctx->rows.k1, mk)); CUC(dmalloc(&ctx->rows.len, mk));
     CUC(dmalloc(&ctx->rows.part_begin, (uint64_t)cfg->num_reducers + 1));
     CUC(dmalloc(&ctx->d_ctl, 1));
     CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
@@ -476,8 +471,7 @@ int launch_compact(mr_ctx *ctx)
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
     compact_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->ent, ctx->max_keys, ctx->d_ctl);
     partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0], ctx->bufs.lo[0], ctx->bufs.val[0],
-        ctx->max_keys, ctx->d_ctl);
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 2;
     CU(cudaGetLastError());
     return MR_OK;
@@ -488,8 +482,7 @@ int launch_sort(mr_ctx *ctx)
     cudaStream_t s = ctx->stream;
     CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
     sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->max_keys);
-    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 2), 256, 0, s>>>(ctx->bufs.hi[0],
-                                                                                     ctx->bufs.lo[0], ctx->d_ctl);
+    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->d_ctl);
     ctx->stats.launches += 2;
     for (uint32_t pass = 0; pass < MAX_PASSES; ++pass) {
         radix_pass_kernel<<<ctx->max_tiles, SORT_THREADS, 0, s>>>(ctx->bufs, pass, ctx->d_status, ctx->max_tiles,
@@ -497,8 +490,8 @@ int launch_sort(mr_ctx *ctx)
         ctx->stats.launches++;
     }
     uint64_t tie_cap = 1; while (tie_cap < ctx->max_keys) tie_cap <<= 1;
-    tie_mark_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs, ctx->d_ties,
-                                                                                   (uint32_t)tie_cap, ctx->d_ctl);
+    tie_mark_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, s>>>(
+        ctx->bufs, ctx->d_ties, (uint32_t)tie_cap, ctx->ent, ctx->bytes_base, ctx->d_ctl);
     tie_fix_small_kernel<<<1, 1024, 0, s>>>(ctx->bufs, ctx->d_ties, ctx->ent, ctx->bytes_base, ctx->d_ctl);
     ctx->stats.launches += 2;
     CU(cudaGetLastError());
@@ -508,27 +501,13 @@ int launch_sort(mr_ctx *ctx)
 int launch_rows(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
-    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 4);
-    const unsigned tiles = (unsigned)((ctx->max_keys + SCAN_TILE - 1) / SCAN_TILE);
-    head_mark_kernel<<<g, 256, 0, s>>>(ctx->bufs, ctx->ent, ctx->bytes_base, ctx->d_head, ctx->d_ctl);
-    scan_partial_kernel<<<tiles, 256, 0, s>>>(ctx->d_head, ctx->d_partial, ctx->d_ctl, 0);
-    scan_spine_kernel<<<1, 1024, 0, s>>>(ctx->d_partial, ctx->d_ctl, 0);
-    scan_final_kernel<<<tiles, 256, 0, s>>>(ctx->d_head, ctx->d_partial, ctx->d_outidx, ctx->d_ctl, 0);
-    reduce_rows_kernel<<<g, 256, 0, s>>>(ctx->bufs, ctx->ent, ctx->d_head, ctx->d_outidx, ctx->rows, ctx->d_ctl);
-    scan_partial_kernel<<<tiles, 256, 0, s>>>(ctx->rows.len, ctx->d_partial, ctx->d_ctl, 1);
-    scan_spine_kernel<<<1, 1024, 0, s>>>(ctx->d_partial, ctx->d_ctl, 1);
-    scan_final_kernel<<<tiles, 256, 0, s>>>(ctx->rows.len, ctx->d_partial, ctx->rows.key_off, ctx->d_ctl, 1);
-    check_key_bytes_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->key_bytes_cap - 64);
-    ctx->stats.launches += 9;
-    CU(cudaGetLastError());
-    return MR_OK;
-}
-
-int launch_key_bytes(mr_ctx *ctx)
-{
-    const unsigned g = grid_for(ctx->max_keys + 1, 256, ctx->sm_count * 4);
-    write_key_bytes_kernel<<<g, 256, 0, ctx->stream>>>(ctx->rows, ctx->bytes_base, ctx->cfg.num_reducers, ctx->d_ctl);
-    ctx->stats.launches++;
+    CU(cudaMemsetAsync(ctx->rows.count, 0, ctx->max_keys * 8, s));
+    CU(cudaMemsetAsync(ctx->rows_st.heads, 0, 3ull * ctx->rows_tiles * 8, s));
+    CU(cudaMemsetAsync(&ctx->d_ctl->rows_ticket, 0, sizeof(unsigned int), s));
+    rows_kernel<<<ctx->rows_tiles, ROWS_THREADS, 0, s>>>(ctx->bufs, ctx->ent, ctx->bytes_base, ctx->rows,
+                                                        ctx->cfg.num_reducers, ctx->key_bytes_cap - 64,
+                                                        ctx->rows_st, ctx->d_ctl);
+    ctx->stats.launches += 1;
     CU(cudaGetLastError());
     return MR_OK;
 }
@@ -580,7 +559,6 @@ int mr_reduce_all(mr_ctx *ctx)
     if (!ctx->imported) { if ((rc = launch_compact(ctx))) return rc; }
     if ((rc = launch_sort(ctx))) return rc;
     if ((rc = launch_rows(ctx))) return rc;
-    if ((rc = launch_key_bytes(ctx))) return rc;
     CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
     ctx->red_timed = true;
     ctx->state = mr_ctx::REDUCED;
@@ -601,14 +579,13 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
             // rare: many keys agree in their first 7 bytes; order them, then redo the rows
             if ((rc = run_general_ties(ctx, ctx->h_ctl->n_tie))) return rc;
             if ((rc = launch_rows(ctx))) return rc;
-            if ((rc = launch_key_bytes(ctx))) return rc;
-            CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
+                    CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
             CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
             CU(cudaStreamSynchronize(ctx->stream));
             if ((rc = check_device_err(ctx, ctx->h_ctl->err))) return rc;
             ctx->tie_rounds = 2;
         } else {
-            ctx->tie_rounds = ctx->h_ctl->n_tie ? 1 : 0;
+            ctx->tie_rounds = (ctx->h_ctl->n_tie || ctx->h_ctl->tie_small) ? 1 : 0;
         }
         ctx->stats.d2h_bytes += sizeof(Ctl);
         ctx->info.n_keys = ctx->h_ctl->n_out;
@@ -812,7 +789,7 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
     ctl_set_n_kernel<<<1, 1, 0, s>>>(ctx->d_ctl, base);
     ctx->bytes_base = ctx->d_recv;
     partition_entries_kernel<<<grid_for(std::max<uint64_t>(base, 1), 256, ctx->sm_count * 4), 256, 0, s>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.hi[0], ctx->bufs.lo[0], ctx->bufs.val[0], ctx->max_keys, ctx->d_ctl);
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 3;
     CU(cudaGetLastError());
     ctx->imported = true;

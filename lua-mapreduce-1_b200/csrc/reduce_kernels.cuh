@@ -8,6 +8,7 @@
 //   K6  segmented reduce: equal neighbours (same key from several sources) are summed
 //       (merge_min_keys utils.lua:232-247 + reducefn.lua:1-5)
 //   K7  rows: partition, count, key offsets, packed key bytes, partition starts
+// K6 and K7 are one single-pass kernel (decoupled look-back over tiles).
 #pragma once
 #include "common.cuh"
 
@@ -16,13 +17,24 @@ namespace mr {
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX_BINS = 1 << RADIX_BITS;
 constexpr int MAX_PASSES = 12;          // 96 bits / 8
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int SORT_ITEMS = 8;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // 4096
-constexpr int SCAN_TILE = 4096;
-constexpr uint32_t TIE_SMALL_MAX = 1024; // tie entries resolved inside one CTA
+constexpr int ROWS_THREADS = 256;
+constexpr int ROWS_ITEMS = 8;
+constexpr int ROWS_TILE = ROWS_THREADS * ROWS_ITEMS; // 2048
+constexpr uint32_t TIE_SMALL_GROUP = 16;  // tie groups up to this size are ordered by one thread
+constexpr uint32_t TIE_SMALL_MAX = 1024;  // members of larger groups one CTA can order
 
 struct DigitRun { uint8_t shift, width, dst, pad; }; // shift 0..63 -> lo, 64..95 -> hi
+
+// what the radix sort moves: 96-bit sort key + index of the entry
+struct __align__(16) SortItem {
+    unsigned long long lo; // 7 key bytes big-endian << 8 | min(len, 8)
+    uint32_t hi;           // partition
+    uint32_t val;          // entry index
+};
 
 struct Ctl {
     unsigned long long n;            // entries (distinct keys before the merge)
@@ -30,8 +42,10 @@ struct Ctl {
     unsigned int or_hi, and_hi;
     unsigned int npasses;
     unsigned int err;
-    unsigned int n_tie;              // entries whose order needs bytes beyond the first 7
+    unsigned int n_tie;              // members of tie groups larger than TIE_SMALL_GROUP
     unsigned int tie_overflow;       // n_tie > TIE_SMALL_MAX: host must run the general path
+    unsigned int tie_small;          // tie groups ordered in place
+    unsigned int rows_ticket;
     unsigned long long n_out;        // rows after the segmented reduce
     unsigned long long key_bytes;    // sum of key lengths over rows
     unsigned long long tokens;
@@ -41,7 +55,6 @@ struct Ctl {
     unsigned int ghist[MAX_PASSES][RADIX_BINS];
 };
 
-// ------------------------------------------------------------------ K3
 struct EntryArrays {
     unsigned long long *k0, *k1; // key words (common.cuh)
     unsigned long long *cnt;
@@ -49,6 +62,7 @@ struct EntryArrays {
     __device__ __forceinline__ Key key(uint64_t i) const { Key k; k.k0 = k0[i]; k.k1 = k1[i]; return k; }
 };
 
+// ------------------------------------------------------------------ K3
 __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
                                              uint64_t lo_or, uint64_t lo_and, bool any)
 {
@@ -121,10 +135,9 @@ __global__ void __launch_bounds__(256) compact_kernel(const GEntry *gt, uint64_t
     }
 }
 
-// entries already dense (after a shuffle import): partition + sort key only
+// dense entries -> partition id + sort item (+ which key bits vary at all)
 __global__ void __launch_bounds__(256) partition_entries_kernel(
-    const uint8_t *bytes, uint32_t num_reducers, EntryArrays ent, uint32_t *sk_hi,
-    unsigned long long *sk_lo, uint32_t *val, uint64_t max_keys, Ctl *ctl)
+    const uint8_t *bytes, uint32_t num_reducers, EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl)
 {
     uint32_t hi_or = 0, hi_and = ~0u;
     uint64_t lo_or = 0, lo_and = ~0ull;
@@ -136,7 +149,8 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
         uint32_t part = partition_of_key(key, bytes, num_reducers);
         uint64_t chunk = sort_chunk(key, bytes, 0);
         ent.part[idx] = part;
-        sk_hi[idx] = part; sk_lo[idx] = chunk; val[idx] = (uint32_t)idx;
+        SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
+        items[idx] = it;
         hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
         any = true;
     }
@@ -184,8 +198,7 @@ __device__ __forceinline__ uint32_t extract_digit(const DigitRun *runs, uint32_t
 }
 
 // digit histograms of every pass in one read of the keys
-__global__ void __launch_bounds__(256) radix_hist_kernel(const uint32_t *sk_hi,
-                                                         const unsigned long long *sk_lo, Ctl *ctl)
+__global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, Ctl *ctl)
 {
     __shared__ unsigned int h[MAX_PASSES][RADIX_BINS];
     __shared__ DigitRun runs[MAX_PASSES][8];
@@ -199,9 +212,8 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const uint32_t *sk_hi,
     __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        uint32_t hi = sk_hi[i];
-        uint64_t lo = sk_lo[i];
-        for (uint32_t p = 0; p < np; ++p) atomicAdd(&h[p][extract_digit(runs[p], nruns[p], hi, lo)], 1u);
+        const SortItem it = items[i];
+        for (uint32_t p = 0; p < np; ++p) atomicAdd(&h[p][extract_digit(runs[p], nruns[p], it.hi, it.lo)], 1u);
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < np * RADIX_BINS; i += blockDim.x) {
@@ -214,9 +226,7 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const uint32_t *sk_hi,
 constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_VAL = (1u << 30) - 1;
 
 struct SortBufs {
-    uint32_t *hi[2];
-    unsigned long long *lo[2];
-    uint32_t *val[2];
+    SortItem *item[2];
 };
 
 // One LSD pass (stable): tile-local ranking by warp-level digit matching, tile offsets
@@ -228,33 +238,31 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
     if (pass >= ctl->npasses) return;
     const uint64_t n = ctl->n;
     __shared__ uint32_t s_tile;
-    __shared__ unsigned int whist[SORT_THREADS / 32][RADIX_BINS];
+    __shared__ unsigned int whist[SORT_WARPS][RADIX_BINS];
     __shared__ unsigned int bin_base[RADIX_BINS];
-    __shared__ unsigned int scan_tmp[SORT_THREADS / 32];
+    __shared__ unsigned int scan_tmp[RADIX_BINS / 32];
     __shared__ DigitRun runs[8];
     __shared__ unsigned int s_nruns;
     if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->tickets[pass], 1u);
     if (threadIdx.x < 8) runs[threadIdx.x] = ctl->runs[pass][threadIdx.x];
     if (threadIdx.x == 8) s_nruns = ctl->nruns[pass];
-    for (uint32_t i = threadIdx.x; i < (SORT_THREADS / 32) * RADIX_BINS; i += SORT_THREADS)
-        (&whist[0][0])[i] = 0;
+    for (uint32_t i = threadIdx.x; i < SORT_WARPS * RADIX_BINS; i += SORT_THREADS) (&whist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = s_tile;
     if ((uint64_t)tile * SORT_TILE >= n) return;
-    const uint32_t src = pass & 1, dst = src ^ 1;
+    const SortItem *src = bufs.item[pass & 1];
+    SortItem *dst = bufs.item[(pass & 1) ^ 1];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt = lanemask_lt();
     const uint32_t nruns = s_nruns;
 
-    uint32_t k_hi[SORT_ITEMS], k_val[SORT_ITEMS];
-    uint64_t k_lo[SORT_ITEMS];
+    SortItem it[SORT_ITEMS];
     uint16_t k_rank[SORT_ITEMS], k_dig[SORT_ITEMS];
     const uint64_t wbase = (uint64_t)tile * SORT_TILE + (uint64_t)warp * (32 * SORT_ITEMS);
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
         uint64_t idx = wbase + (uint64_t)i * 32 + lane;
-        bool valid = idx < n;
-        if (valid) { k_hi[i] = bufs.hi[src][idx]; k_lo[i] = bufs.lo[src][idx]; k_val[i] = bufs.val[src][idx]; }
-        else { k_hi[i] = 0; k_lo[i] = 0; k_val[i] = 0; }
+        if (idx < n) it[i] = src[idx];
+        else { it[i].lo = 0; it[i].hi = 0; it[i].val = 0; }
     }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
@@ -263,7 +271,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         uint32_t act = __ballot_sync(0xFFFFFFFFu, valid);
         uint32_t d = 0, r = 0;
         if (valid) {
-            d = extract_digit(runs, nruns, k_hi[i], k_lo[i]);
+            d = extract_digit(runs, nruns, it[i].hi, it[i].lo);
             uint32_t peers = __match_any_sync(act, d);
             uint32_t leader = __ffs((int)peers) - 1;
             uint32_t old = 0;
@@ -275,18 +283,18 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         __syncwarp();
     }
     __syncthreads();
-    // thread b owns bin b: per-warp exclusive offsets, tile count, look-back
-    {
+    // thread b < 256 owns bin b: per-warp exclusive offsets, tile count, look-back
+    unsigned int prefix = 0, g = 0, incl = 0;
+    if (threadIdx.x < RADIX_BINS) {
         const uint32_t b = threadIdx.x;
         unsigned int run = 0;
 #pragma unroll
-        for (int w = 0; w < SORT_THREADS / 32; ++w) { unsigned int c = whist[w][b]; whist[w][b] = run; run += c; }
+        for (int w = 0; w < SORT_WARPS; ++w) { unsigned int c = whist[w][b]; whist[w][b] = run; run += c; }
         const unsigned int tile_count = run;
         volatile uint32_t *st = status + ((uint64_t)pass * max_tiles) * RADIX_BINS;
         if (tile == 0) st[(uint64_t)tile * RADIX_BINS + b] = ST_INC | tile_count;
         else st[(uint64_t)tile * RADIX_BINS + b] = ST_AGG | tile_count;
         __threadfence();
-        unsigned int prefix = 0;
         if (tile > 0) {
             // look back 8 tiles at a time: the 8 loads are independent, so a long chain of
             // not-yet-inclusive predecessors costs one L2 round trip per 8 tiles, not per tile
@@ -308,15 +316,17 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
             st[(uint64_t)tile * RADIX_BINS + b] = ST_INC | (prefix + tile_count);
         }
         // exclusive scan of the global histogram = start of every bin
-        unsigned int g = ctl->ghist[pass][b];
-        unsigned int incl = g;
+        g = ctl->ghist[pass][b];
+        incl = g;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
         if (lane == 31) scan_tmp[warp] = incl;
-        __syncthreads();
+    }
+    __syncthreads();
+    if (threadIdx.x < RADIX_BINS) {
         unsigned int wsum = 0;
         for (uint32_t w = 0; w < warp; ++w) wsum += scan_tmp[w];
-        bin_base[b] = wsum + incl - g + prefix;
+        bin_base[threadIdx.x] = wsum + incl - g + prefix;
     }
     __syncthreads();
 #pragma unroll
@@ -325,13 +335,29 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         if (idx < n) {
             uint32_t d = k_dig[i];
             uint64_t o = (uint64_t)bin_base[d] + whist[warp][d] + k_rank[i];
-            bufs.hi[dst][o] = k_hi[i]; bufs.lo[dst][o] = k_lo[i]; bufs.val[dst][o] = k_val[i];
+            dst[o] = it[i];
         }
     }
 }
 
 // ------------------------------------------------------------------ ties beyond 7 bytes
+// After the radix sort, keys that agree in (partition, first 7 bytes) and have more bytes
+// sit next to each other in arbitrary order ("tie group").  Groups of up to
+// TIE_SMALL_GROUP keys (the normal case in text) are ordered in place by one thread;
+// members of larger groups are collected and ordered by bitonic networks.
 struct TieItem { uint32_t pos, val; };
+
+// full order of two keys of the same partition, round by round (7 key bytes per round)
+__device__ inline bool key_less(const Key &ka, const Key &kb, uint32_t va, uint32_t vb, const uint8_t *bytes,
+                                uint32_t first_round)
+{
+    for (uint32_t r = first_round;; ++r) {
+        uint64_t ca = sort_chunk(ka, bytes, r), cb = sort_chunk(kb, bytes, r);
+        if (ca != cb) return ca < cb;
+        if ((ca & 0xFF) < 8) break; // both keys end here: equal keys (same key from two sources)
+    }
+    return va < vb;
+}
 
 __device__ inline bool tie_less(const TieItem &a, const TieItem &b, const EntryArrays &ent,
                                 const uint8_t *bytes)
@@ -339,53 +365,70 @@ __device__ inline bool tie_less(const TieItem &a, const TieItem &b, const EntryA
     if (a.pos == 0xFFFFFFFFu || b.pos == 0xFFFFFFFFu) return a.pos != 0xFFFFFFFFu && b.pos == 0xFFFFFFFFu;
     uint32_t pa = ent.part[a.val], pb = ent.part[b.val];
     if (pa != pb) return pa < pb;
-    const Key ka = ent.key(a.val), kb = ent.key(b.val);
-    // round by round, 7 key bytes at a time (round 0 is what the radix sort already used)
-    for (uint32_t r = 0;; ++r) {
-        uint64_t ca = sort_chunk(ka, bytes, r), cb = sort_chunk(kb, bytes, r);
-        if (ca != cb) return ca < cb;
-        if ((ca & 0xFF) < 8) break; // both keys end here: equal
-    }
-    return a.val < b.val;
+    return key_less(ent.key(a.val), ent.key(b.val), a.val, b.val, bytes, 0);
 }
 
-// Marks sorted positions whose (partition, first 7 bytes) equals a neighbour's while
-// more key bytes remain, and appends them (unordered) to the tie list.
 __global__ void __launch_bounds__(256) tie_mark_kernel(SortBufs bufs, TieItem *ties, uint32_t tie_cap,
-                                                       Ctl *ctl)
+                                                       EntryArrays ent, const uint8_t *bytes, Ctl *ctl)
 {
     const uint64_t n = ctl->n;
-    const uint32_t fin = ctl->npasses & 1;
-    const uint32_t *hi = bufs.hi[fin];
-    const unsigned long long *lo = bufs.lo[fin];
+    SortItem *items = bufs.item[ctl->npasses & 1];
     const uint32_t lane = threadIdx.x & 31, lt = lanemask_lt();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t rounds = (n + stride - 1) / stride;
     for (uint64_t r = 0; r < rounds; ++r) {
-        uint64_t i = r * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-        bool tie = false;
+        const uint64_t i = r * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        bool big = false;
+        uint32_t myval = 0;
         if (i < n) {
-            uint64_t l = lo[i];
-            if ((l & 0xFF) == 8) {
-                uint32_t h = hi[i];
-                tie = (i > 0 && hi[i - 1] == h && lo[i - 1] == l) ||
-                      (i + 1 < n && hi[i + 1] == h && lo[i + 1] == l);
+            const SortItem me = items[i];
+            if ((me.lo & 0xFF) == 8) {
+                // extent of my group, looking at most TIE_SMALL_GROUP items each way
+                uint64_t lo_i = i, hi_i = i + 1;
+                while (lo_i > 0 && i - lo_i < TIE_SMALL_GROUP) {
+                    const SortItem o = items[lo_i - 1];
+                    if (o.hi != me.hi || o.lo != me.lo) break;
+                    --lo_i;
+                }
+                while (hi_i < n && hi_i - lo_i <= TIE_SMALL_GROUP) {
+                    const SortItem o = items[hi_i];
+                    if (o.hi != me.hi || o.lo != me.lo) break;
+                    ++hi_i;
+                }
+                const uint32_t g = (uint32_t)(hi_i - lo_i);
+                if (g > TIE_SMALL_GROUP) {
+                    big = true;
+                    myval = me.val;
+                } else if (g > 1 && lo_i == i) {
+                    // head of a small group: insertion sort of the entry indices by full key
+                    uint32_t v[TIE_SMALL_GROUP];
+                    for (uint32_t a = 0; a < g; ++a) v[a] = items[i + a].val;
+                    for (uint32_t a = 1; a < g; ++a) {
+                        const uint32_t x = v[a];
+                        const Key kx = ent.key(x);
+                        uint32_t b = a;
+                        while (b > 0 && key_less(kx, ent.key(v[b - 1]), x, v[b - 1], bytes, 1)) { v[b] = v[b - 1]; --b; }
+                        v[b] = x;
+                    }
+                    for (uint32_t a = 0; a < g; ++a) items[i + a].val = v[a];
+                    atomicAdd(&ctl->tie_small, 1u);
+                }
             }
         }
-        uint32_t m = __ballot_sync(0xFFFFFFFFu, tie);
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, big);
         if (!m) continue;
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(&ctl->n_tie, (unsigned int)__popc(m));
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (tie) {
+        if (big) {
             uint32_t k = base + __popc(m & lt);
-            if (k < tie_cap) { ties[k].pos = (uint32_t)i; ties[k].val = bufs.val[fin][i]; }
+            if (k < tie_cap) { ties[k].pos = (uint32_t)i; ties[k].val = myval; }
         }
     }
 }
 
-// Up to TIE_SMALL_MAX ties: one CTA copies their keys into shared memory, orders the positions
-// and the entries (full key compare) with bitonic networks and writes the entries back.
+// Up to TIE_SMALL_MAX members of large groups: one CTA copies their keys into shared memory,
+// orders the positions and the entries (full key compare) with bitonic networks and writes back.
 __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, const TieItem *ties,
                                                              EntryArrays ent, const uint8_t *bytes,
                                                              Ctl *ctl)
@@ -410,13 +453,7 @@ __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, cons
     auto less = [&](uint32_t a, uint32_t b) -> bool { // a, b index the unsorted copies; >= nt is padding
         if (a >= nt || b >= nt) return a < nt && b >= nt;
         if (spart[a] != spart[b]) return spart[a] < spart[b];
-        const Key ka = skey[a], kb = skey[b];
-        for (uint32_t r = 0;; ++r) {
-            uint64_t ca = sort_chunk(ka, bytes, r), cb = sort_chunk(kb, bytes, r);
-            if (ca != cb) return ca < cb;
-            if ((ca & 0xFF) < 8) break;
-        }
-        return sval[a] < sval[b];
+        return key_less(skey[a], skey[b], sval[a], sval[b], bytes, 0);
     };
     for (uint32_t k = 2; k <= np2; k <<= 1)
         for (uint32_t j = k >> 1; j > 0; j >>= 1) {
@@ -433,8 +470,8 @@ __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, cons
             }
             __syncthreads();
         }
-    const uint32_t fin = ctl->npasses & 1;
-    for (uint32_t i = threadIdx.x; i < nt; i += blockDim.x) bufs.val[fin][posv[i]] = sval[order[i]];
+    SortItem *items = bufs.item[ctl->npasses & 1];
+    for (uint32_t i = threadIdx.x; i < nt; i += blockDim.x) items[posv[i]].val = sval[order[i]];
 }
 
 // General path (host-driven): bitonic steps over the tie list in global memory.
@@ -463,157 +500,176 @@ __global__ void __launch_bounds__(256) tie_bitonic_step_kernel(TieItem *items, u
     if (swap) { items[i] = b; items[ixj] = a; }
 }
 
-__global__ void __launch_bounds__(256) tie_writeback_kernel(SortBufs bufs, const TieItem *items,
+__global__ void __launch_bounds__(256) tie_writeback_kernel(SortBufs bufs, const TieItem *ties,
                                                             const uint32_t *posv, uint32_t nt, Ctl *ctl)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < nt) bufs.val[ctl->npasses & 1][posv[i]] = items[i].val;
+    if (i < nt) bufs.item[ctl->npasses & 1][posv[i]].val = ties[i].val;
 }
 
-// ------------------------------------------------------------------ scans (3 kernels)
-// exclusive scan of a uint32 array of ctl-> length into uint64; `which` selects the
-// length and where the total goes: 0 -> n entries, total to n_out; 1 -> n_out rows,
-// total to key_bytes.
-__device__ __forceinline__ uint64_t scan_len(const Ctl *ctl, int which) { return which == 0 ? ctl->n : ctl->n_out; }
-
-__global__ void __launch_bounds__(256) scan_partial_kernel(const uint32_t *in, unsigned long long *partial,
-                                                           const Ctl *ctl, int which)
-{
-    const uint64_t n = scan_len(ctl, which);
-    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
-    if (base >= n) return;
-    __shared__ unsigned long long wsum[8];
-    unsigned long long s = 0;
-    for (uint32_t i = threadIdx.x; i < SCAN_TILE; i += 256) { uint64_t idx = base + i; if (idx < n) s += in[idx]; }
-    for (int d = 16; d; d >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, d);
-    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) { unsigned long long t = 0; for (int w = 0; w < 8; ++w) t += wsum[w]; partial[blockIdx.x] = t; }
-}
-
-__global__ void __launch_bounds__(1024) scan_spine_kernel(unsigned long long *partial, Ctl *ctl, int which)
-{
-    const uint64_t n = scan_len(ctl, which);
-    const uint32_t nt = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
-    __shared__ unsigned long long wsum[32];
-    __shared__ unsigned long long carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (uint32_t base = 0; base < nt; base += 1024) {
-        uint32_t i = base + threadIdx.x;
-        unsigned long long v = i < nt ? partial[i] : 0, incl = v;
-        for (int d = 1; d < 32; d <<= 1) { unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-        if (lane == 31) wsum[warp] = incl;
-        __syncthreads();
-        unsigned long long woff = 0;
-        for (uint32_t w = 0; w < warp; ++w) woff += wsum[w];
-        unsigned long long c = carry;
-        if (i < nt) partial[i] = c + woff + incl - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = c + woff + incl;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) { if (which == 0) ctl->n_out = carry; else ctl->key_bytes = carry; }
-}
-
-__global__ void __launch_bounds__(256) scan_final_kernel(const uint32_t *in, const unsigned long long *partial,
-                                                         unsigned long long *out, const Ctl *ctl, int which)
-{
-    const uint64_t n = scan_len(ctl, which);
-    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
-    if (base >= n) { return; }
-    __shared__ unsigned long long wsum[8];
-    // thread t handles 16 consecutive items
-    const uint64_t first = base + (uint64_t)threadIdx.x * 16;
-    uint32_t v[16];
-    unsigned long long s = 0;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) { uint64_t idx = first + i; v[i] = idx < n ? in[idx] : 0; s += v[i]; }
-    unsigned long long incl = s;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int d = 1; d < 32; d <<= 1) { unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-    if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
-    unsigned long long off = partial[blockIdx.x] + incl - s;
-    for (uint32_t w = 0; w < warp; ++w) off += wsum[w];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) { uint64_t idx = first + i; if (idx < n) out[idx] = off; off += v[i]; }
-}
-
-// ------------------------------------------------------------------ K6 / K7
-// head[i] = 1 when sorted position i starts a new key
-__global__ void __launch_bounds__(256) head_mark_kernel(SortBufs bufs, EntryArrays ent, const uint8_t *bytes,
-                                                        uint32_t *head, const Ctl *ctl)
-{
-    const uint64_t n = ctl->n;
-    const uint32_t fin = ctl->npasses & 1;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        uint32_t h = 1;
-        if (i > 0 && bufs.hi[fin][i] == bufs.hi[fin][i - 1] && bufs.lo[fin][i] == bufs.lo[fin][i - 1])
-            h = same_key(ent.key(bufs.val[fin][i]), ent.key(bufs.val[fin][i - 1]), bytes) ? 0u : 1u;
-        head[i] = h;
-    }
-}
-
+// ------------------------------------------------------------------ K6 + K7
 struct RowArrays {
     uint32_t *part;
-    unsigned long long *count;
-    unsigned long long *key_off; // [n_out + 1]
+    unsigned long long *count;      // zeroed before rows_kernel
+    unsigned long long *key_off;    // [n_out + 1]
     uint8_t *key_bytes;
-    unsigned long long *k0, *k1; // key words of the row (internal)
-    uint32_t *len;
     unsigned long long *part_begin; // [R + 1]
 };
 
-// every head sums its run of equal keys and writes the row
-__global__ void __launch_bounds__(256) reduce_rows_kernel(SortBufs bufs, EntryArrays ent, const uint32_t *head,
-                                                          const unsigned long long *out_idx, RowArrays rows,
-                                                          const Ctl *ctl)
+// look-back state of rows_kernel, one slot per tile
+struct RowsStatus {
+    unsigned long long *heads;      // flag << 62 | number of rows (aggregate or inclusive prefix)
+    unsigned long long *bytes_agg;  // key bytes of the tile
+    unsigned long long *bytes_inc;  // key bytes up to and including the tile
+};
+
+__device__ __forceinline__ void write_key_bytes(uint8_t *dst, const Key &key, uint32_t len, const uint8_t *bytes)
 {
-    const uint64_t n = ctl->n;
-    const uint32_t fin = ctl->npasses & 1;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        if (!head[i]) continue;
-        uint32_t v = bufs.val[fin][i];
-        unsigned long long c = ent.cnt[v];
-        for (uint64_t j = i + 1; j < n && !head[j]; ++j) c += ent.cnt[bufs.val[fin][j]];
-        uint64_t o = out_idx[i];
-        const Key key = ent.key(v);
-        rows.part[o] = ent.part[v];
-        rows.count[o] = c;
-        rows.k0[o] = key.k0; rows.k1[o] = key.k1;
-        rows.len[o] = key_len(key);
+    if (!key_is_long(key)) {
+        for (uint32_t i = 0; i < len && i < 8; ++i) dst[i] = (uint8_t)(key.k0 >> (8 * i));
+        for (uint32_t i = 8; i < len; ++i) dst[i] = (uint8_t)(key.k1 >> (8 * (i - 8)));
+    } else {
+        const uint64_t off = key_off(key);
+        for (uint32_t i = 0; i < len; i += 8) {
+            uint64_t w = load8(bytes, off + i);
+            uint32_t m = len - i < 8 ? len - i : 8;
+            for (uint32_t j = 0; j < m; ++j) dst[i + j] = (uint8_t)(w >> (8 * j));
+        }
     }
 }
 
-__global__ void __launch_bounds__(256) write_key_bytes_kernel(RowArrays rows, const uint8_t *bytes,
-                                                              uint32_t num_reducers, const Ctl *ctl)
+// Single pass over the sorted items: a position starts a row when its key differs from its
+// left neighbour's; rows are numbered and their key bytes placed by two running sums carried
+// across tiles with decoupled look-back; equal neighbours add their counts into the row
+// (the segmented reduce; integer adds, so the order of the atomics does not matter).
+__global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, EntryArrays ent, const uint8_t *bytes,
+                                                           RowArrays rows, uint32_t num_reducers,
+                                                           unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl)
 {
-    if (ctl->err & ERR_KEYS_FULL) return; // rows or key bytes do not fit: reported by the host
-    const uint64_t n = ctl->n_out;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t o = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; o <= n; o += stride) {
-        // partition starts: rows are partition-sorted
-        uint32_t p_prev = o == 0 ? 0u : rows.part[o - 1] + 1u;
-        uint32_t p_cur = o == n ? num_reducers : rows.part[o];
-        for (uint32_t p = p_prev; p <= p_cur && p <= num_reducers; ++p) rows.part_begin[p] = o;
-        if (o == n) { rows.key_off[n] = ctl->key_bytes; break; }
-        Key key; key.k0 = rows.k0[o]; key.k1 = rows.k1[o];
-        uint8_t *dst = rows.key_bytes + rows.key_off[o];
-        uint32_t len = rows.len[o];
-        if (!key_is_long(key)) {
-            for (uint32_t i = 0; i < len && i < 8; ++i) dst[i] = (uint8_t)(key.k0 >> (8 * i));
-            for (uint32_t i = 8; i < len; ++i) dst[i] = (uint8_t)(key.k1 >> (8 * (i - 8)));
+    __shared__ uint32_t s_tile;
+    __shared__ unsigned int wh[ROWS_THREADS / 32];
+    __shared__ unsigned long long wb[ROWS_THREADS / 32];
+    __shared__ unsigned long long s_prefix_h, s_prefix_b;
+    if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->rows_ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint64_t n = ctl->n;
+    if (n == 0) {
+        if (tile == 0) {
+            for (uint32_t p = threadIdx.x; p <= num_reducers; p += ROWS_THREADS) rows.part_begin[p] = 0;
+            if (threadIdx.x == 0) { ctl->n_out = 0; ctl->key_bytes = 0; rows.key_off[0] = 0; }
+        }
+        return;
+    }
+    if ((uint64_t)tile * ROWS_TILE >= n) return;
+    const SortItem *items = bufs.item[ctl->npasses & 1];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t base = (uint64_t)tile * ROWS_TILE + (uint64_t)threadIdx.x * ROWS_ITEMS;
+
+    SortItem it[ROWS_ITEMS];
+    SortItem prev; prev.lo = 0; prev.hi = 0; prev.val = 0;
+    if (base > 0 && base <= n) prev = items[base - 1];
+#pragma unroll
+    for (int j = 0; j < ROWS_ITEMS; ++j) {
+        if (base + j < n) it[j] = items[base + j];
+        else { it[j].lo = 0; it[j].hi = 0; it[j].val = 0; }
+    }
+    uint32_t headmask = 0, len[ROWS_ITEMS];
+    Key key[ROWS_ITEMS];
+    uint32_t nh = 0;
+    unsigned long long nb = 0;
+#pragma unroll
+    for (int j = 0; j < ROWS_ITEMS; ++j) {
+        len[j] = 0;
+        if (base + j >= n) continue;
+        const SortItem &p = j == 0 ? prev : it[j - 1];
+        bool head = base + j == 0 || p.hi != it[j].hi || p.lo != it[j].lo;
+        key[j] = ent.key(it[j].val);
+        if (!head) head = !same_key(key[j], ent.key(p.val), bytes);
+        if (head) { headmask |= 1u << j; len[j] = key_len(key[j]); ++nh; nb += len[j]; }
+    }
+    // block-wide exclusive sums of (rows, key bytes)
+    uint32_t ih = nh;
+    unsigned long long ib = nb;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t vh = __shfl_up_sync(0xFFFFFFFFu, ih, d);
+        unsigned long long vb = __shfl_up_sync(0xFFFFFFFFu, ib, d);
+        if (lane >= d) { ih += vh; ib += vb; }
+    }
+    if (lane == 31) { wh[warp] = ih; wb[warp] = ib; }
+    __syncthreads();
+    uint32_t oh = ih - nh, th = 0;
+    unsigned long long ob = ib - nb, tb = 0;
+#pragma unroll
+    for (int w = 0; w < ROWS_THREADS / 32; ++w) {
+        if (w < (int)warp) { oh += wh[w]; ob += wb[w]; }
+        th += wh[w]; tb += wb[w];
+    }
+    // publish the tile aggregate, look back for the exclusive prefix (warp 0)
+    constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62, F_VAL = (1ull << 62) - 1;
+    if (warp == 0) {
+        volatile unsigned long long *vheads = st.heads, *vagg = st.bytes_agg, *vinc = st.bytes_inc;
+        unsigned long long ph = 0, pb = 0;
+        if (tile == 0) {
+            if (lane == 0) { vinc[0] = tb; __threadfence(); vheads[0] = F_INC | th; }
         } else {
-            uint64_t off = key_off(key);
-            for (uint32_t i = 0; i < len; i += 8) {
-                uint64_t w = load8(bytes, off + i);
-                uint32_t m = len - i < 8 ? len - i : 8;
-                for (uint32_t j = 0; j < m; ++j) dst[i + j] = (uint8_t)(w >> (8 * j));
+            if (lane == 0) { vagg[tile] = tb; __threadfence(); vheads[tile] = F_AGG | th; }
+            int t = (int)tile - 1;
+            for (;;) {
+                const int idx = t - (int)lane;
+                unsigned long long w = idx >= 0 ? vheads[idx] : F_INC;
+                const uint32_t flag = (uint32_t)(w >> 62);
+                const uint32_t notready = __ballot_sync(0xFFFFFFFFu, flag == 0);
+                const uint32_t incm = __ballot_sync(0xFFFFFFFFu, flag == 2);
+                // lanes up to the first inclusive prefix take part
+                const uint32_t stop = incm ? (uint32_t)__ffs((int)incm) - 1u : 31u;
+                const uint32_t use = stop == 31 ? 0xFFFFFFFFu : ((2u << stop) - 1u);
+                if (notready & use) continue; // a needed predecessor has not published yet
+                __threadfence();
+                unsigned long long b = 0, h = 0;
+                if ((use >> lane) & 1u) {
+                    h = w & F_VAL;
+                    if (idx >= 0) b = flag == 2 ? vinc[idx] : vagg[idx];
+                }
+                for (int d = 16; d; d >>= 1) {
+                    h += __shfl_xor_sync(0xFFFFFFFFu, h, d);
+                    b += __shfl_xor_sync(0xFFFFFFFFu, b, d);
+                }
+                ph += h; pb += b;
+                if (incm) break;
+                t -= 32;
             }
+            if (lane == 0) { vinc[tile] = pb + tb; __threadfence(); vheads[tile] = F_INC | (ph + th); }
+        }
+        if (lane == 0) { s_prefix_h = ph; s_prefix_b = pb; }
+    }
+    __syncthreads();
+    unsigned long long o = s_prefix_h + oh, boff = s_prefix_b + ob;
+    const bool overflow = s_prefix_b + tb > key_bytes_cap;
+    if (overflow && threadIdx.x == 0) atomicOr(&ctl->err, ERR_KEYS_FULL);
+#pragma unroll
+    for (int j = 0; j < ROWS_ITEMS; ++j) {
+        const uint64_t pos = base + j;
+        if (pos >= n) break;
+        const SortItem &p = j == 0 ? prev : it[j - 1];
+        if ((headmask >> j) & 1u) {
+            rows.part[o] = it[j].hi;
+            rows.key_off[o] = boff;
+            if (!overflow) write_key_bytes(rows.key_bytes + boff, key[j], len[j], bytes);
+            // partition starts: rows are partition-sorted
+            const uint32_t p_first = pos == 0 ? 0u : p.hi + 1u;
+            if (pos == 0 || p.hi != it[j].hi)
+                for (uint32_t q = p_first; q <= it[j].hi && q <= num_reducers; ++q) rows.part_begin[q] = o;
+            boff += len[j];
+            ++o;
+        }
+        atomicAdd(&rows.count[o - 1], ent.cnt[it[j].val]);
+        if (pos == n - 1) { // totals and sentinels
+            ctl->n_out = o;
+            ctl->key_bytes = boff;
+            rows.key_off[o] = boff;
+            for (uint32_t q = it[j].hi + 1u; q <= num_reducers; ++q) rows.part_begin[q] = o;
         }
     }
 }
