@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(256) export_count_kernel(EntryArrays ent, uint
     const uint64_t n = ctl->n;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        uint32_t d = ent.part[i] % world;
+        uint32_t d = ent.part(i) % world;
         atomicAdd(&nrec[d], 1ull);
         Key k = ent.key(i);
         if (key_is_long(k)) atomicAdd(&nbytes[d], (unsigned long long)key_len(k));
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
     const uint64_t n = ctl->n;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        uint32_t d = ent.part[i] % world;
+        uint32_t d = ent.part(i) % world;
         Key k = ent.key(i);
         uint8_t *seg = send + seg_off[d];
         unsigned long long r = atomicAdd(&rec_cur[d], 1ull);
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
         }
         ((unsigned long long *)seg)[3 * r] = k.k0;
         ((unsigned long long *)seg)[3 * r + 1] = k.k1;
-        ((unsigned long long *)seg)[3 * r + 2] = ent.cnt[i];
+        ((unsigned long long *)seg)[3 * r + 2] = ent.cnt(i);
     }
 }
 
@@ -95,8 +95,8 @@ __global__ void __launch_bounds__(256) import_segment_kernel(const uint8_t *recv
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += stride) {
         Key k; k.k0 = rec[3 * i]; k.k1 = rec[3 * i + 1];
         if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k), (uint32_t)k.k1);
-        ent.k0[ent_base + i] = k.k0; ent.k1[ent_base + i] = k.k1;
-        ent.cnt[ent_base + i] = rec[3 * i + 2];
+        GEntry ge; ge.k0 = k.k0; ge.k1 = k.k1; ge.cnt = rec[3 * i + 2]; ge.pad = 0;
+        ent.e[ent_base + i] = ge;
     }
 }
 
@@ -252,7 +252,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab);
-    cudaFree(ctx->ent.k0); cudaFree(ctx->ent.k1); cudaFree(ctx->ent.cnt); cudaFree(ctx->ent.part);
+    cudaFree(ctx->ent.e);
     for (int i = 0; i < 2; ++i) cudaFree(ctx->bufs.item[i]);
     cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv);
     cudaFree(ctx->rows_st.heads);
@@ -333,8 +333,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     else { CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
     CUC(dmalloc(&ctx->d_arena, ctx->arena_cap + ARENA_SLACK));
     CUC(dmalloc(&ctx->d_gtab, slots));
-    CUC(dmalloc(&ctx->ent.k0, mk)); CUC(dmalloc(&ctx->ent.k1, mk));
-    CUC(dmalloc(&ctx->ent.cnt, mk)); CUC(dmalloc(&ctx->ent.part, mk));
+    CUC(dmalloc(&ctx->ent.e, mk));
     for (int i = 0; i < 2; ++i) {
         CUC(dmalloc(&ctx->bufs.item[i], mk));
     }
@@ -470,7 +469,7 @@ int launch_compact(mr_ctx *ctx)
     const uint64_t tiles = (ctx->slots + 256 * COMPACT_ITEMS - 1) / (256 * COMPACT_ITEMS);
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
     compact_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->ent, ctx->max_keys, ctx->d_ctl);
-    partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+    partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
         ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 2;
     CU(cudaGetLastError());

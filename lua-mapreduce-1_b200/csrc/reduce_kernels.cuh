@@ -24,6 +24,7 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // 4096
 constexpr int ROWS_THREADS = 256;
 constexpr int ROWS_ITEMS = 8;
 constexpr int ROWS_TILE = ROWS_THREADS * ROWS_ITEMS; // 2048
+constexpr uint32_t ROWS_STAGE = ROWS_TILE * INLINE_MAX; // key bytes of a tile of inline keys
 constexpr uint32_t TIE_SMALL_GROUP = 16;  // tie groups up to this size are ordered by one thread
 constexpr uint32_t TIE_SMALL_MAX = 1024;  // members of larger groups one CTA can order
 
@@ -55,18 +56,37 @@ struct Ctl {
     unsigned int ghist[MAX_PASSES][RADIX_BINS];
 };
 
+// Dense entries: the occupied slots of the global table copied side by side, 32 bytes each
+// {k0, k1, count, partition}, so that one 32-byte gather fetches everything about a key.
 struct EntryArrays {
-    unsigned long long *k0, *k1; // key words (common.cuh)
-    unsigned long long *cnt;
-    uint32_t *part;
-    __device__ __forceinline__ Key key(uint64_t i) const { Key k; k.k0 = k0[i]; k.k1 = k1[i]; return k; }
+    GEntry *e;
+    __device__ __forceinline__ Key key(uint64_t i) const
+    {
+        ulonglong2 v = *(const ulonglong2 *)&e[i];
+        Key k; k.k0 = v.x; k.k1 = v.y;
+        return k;
+    }
+    __device__ __forceinline__ unsigned long long cnt(uint64_t i) const { return e[i].cnt; }
+    __device__ __forceinline__ uint32_t part(uint64_t i) const { return (uint32_t)e[i].pad; }
 };
+
+// one 256-bit load (sm_100: ld.global.v4.u64), e.g. a whole table entry = one 32-byte sector
+__device__ __forceinline__ ulonglong4 ld256(const void *p)
+{
+    ulonglong4 r;
+    asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
+                 : "l"(p));
+    return r;
+}
 
 // ------------------------------------------------------------------ K3
 __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
                                              uint64_t lo_or, uint64_t lo_and, bool any)
 {
-    // warp-reduce then one atomic per warp
+    // warp-reduce, block-reduce, then one set of atomics per CTA (same-address atomics serialise)
+    __shared__ uint32_t s_hi_or[8], s_hi_and[8], s_any[8];
+    __shared__ unsigned long long s_lo_or[8], s_lo_and[8];
     for (int d = 16; d; d >>= 1) {
         uint32_t o_hi_or = __shfl_xor_sync(0xFFFFFFFFu, hi_or, d);
         uint32_t o_hi_and = __shfl_xor_sync(0xFFFFFFFFu, hi_and, d);
@@ -75,11 +95,25 @@ __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t 
         hi_or |= o_hi_or; hi_and &= o_hi_and; lo_or |= o_lo_or; lo_and &= o_lo_and;
     }
     uint32_t anym = __ballot_sync(0xFFFFFFFFu, any);
-    if ((threadIdx.x & 31) == 0 && anym) {
-        atomicOr(&ctl->or_hi, hi_or);
-        atomicAnd(&ctl->and_hi, hi_and);
-        atomicOr(&ctl->or_lo, (unsigned long long)lo_or);
-        atomicAnd(&ctl->and_lo, (unsigned long long)lo_and);
+    const uint32_t warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) {
+        s_hi_or[warp] = hi_or; s_hi_and[warp] = hi_and; s_lo_or[warp] = lo_or; s_lo_and[warp] = lo_and;
+        s_any[warp] = anym;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t a = 0;
+        for (uint32_t w = 0; w < blockDim.x / 32; ++w) {
+            a |= s_any[w];
+            if (!s_any[w]) continue;
+            hi_or |= s_hi_or[w]; hi_and &= s_hi_and[w]; lo_or |= s_lo_or[w]; lo_and &= s_lo_and[w];
+        }
+        if (a) {
+            atomicOr(&ctl->or_hi, hi_or);
+            atomicAnd(&ctl->and_hi, hi_and);
+            atomicOr(&ctl->or_lo, (unsigned long long)lo_or);
+            atomicAnd(&ctl->and_lo, (unsigned long long)lo_and);
+        }
     }
 }
 
@@ -124,7 +158,8 @@ __global__ void __launch_bounds__(256) compact_kernel(const GEntry *gt, uint64_t
                 if (key[i].k1 == 0) continue;
                 uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
                 if (idx < max_keys) {
-                    ent.k0[idx] = key[i].k0; ent.k1[idx] = key[i].k1; ent.cnt[idx] = __ldcg(&gt[slot].cnt);
+                    GEntry ge; ge.k0 = key[i].k0; ge.k1 = key[i].k1; ge.cnt = __ldcg(&gt[slot].cnt); ge.pad = 0;
+                    ((ulonglong4 *)ent.e)[idx] = *(ulonglong4 *)&ge;
                 } else {
                     atomicOr(&ctl->err, ERR_KEYS_FULL);
                 }
@@ -148,7 +183,7 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
         Key key = ent.key(idx);
         uint32_t part = partition_of_key(key, bytes, num_reducers);
         uint64_t chunk = sort_chunk(key, bytes, 0);
-        ent.part[idx] = part;
+        ent.e[idx].pad = part;
         SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
         items[idx] = it;
         hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
@@ -363,7 +398,7 @@ __device__ inline bool tie_less(const TieItem &a, const TieItem &b, const EntryA
                                 const uint8_t *bytes)
 {
     if (a.pos == 0xFFFFFFFFu || b.pos == 0xFFFFFFFFu) return a.pos != 0xFFFFFFFFu && b.pos == 0xFFFFFFFFu;
-    uint32_t pa = ent.part[a.val], pb = ent.part[b.val];
+    uint32_t pa = ent.part(a.val), pb = ent.part(b.val);
     if (pa != pb) return pa < pb;
     return key_less(ent.key(a.val), ent.key(b.val), a.val, b.val, bytes, 0);
 }
@@ -446,7 +481,7 @@ __global__ void __launch_bounds__(1024) tie_fix_small_kernel(SortBufs bufs, cons
         posv[i] = 0xFFFFFFFFu;
         if (i < nt) {
             TieItem t = ties[i];
-            posv[i] = t.pos; sval[i] = t.val; spart[i] = ent.part[t.val]; skey[i] = ent.key(t.val);
+            posv[i] = t.pos; sval[i] = t.val; spart[i] = ent.part(t.val); skey[i] = ent.key(t.val);
         }
     }
     __syncthreads();
@@ -576,15 +611,17 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
     }
     uint32_t headmask = 0, len[ROWS_ITEMS];
     Key key[ROWS_ITEMS];
+    unsigned long long cnt[ROWS_ITEMS];
     uint32_t nh = 0;
     unsigned long long nb = 0;
 #pragma unroll
     for (int j = 0; j < ROWS_ITEMS; ++j) {
-        len[j] = 0;
+        len[j] = 0; cnt[j] = 0;
         if (base + j >= n) continue;
         const SortItem &p = j == 0 ? prev : it[j - 1];
         bool head = base + j == 0 || p.hi != it[j].hi || p.lo != it[j].lo;
-        key[j] = ent.key(it[j].val);
+        const ulonglong4 e = ld256(&ent.e[it[j].val]); // key + count in one 32-byte gather
+        key[j].k0 = e.x; key[j].k1 = e.y; cnt[j] = e.z;
         if (!head) head = !same_key(key[j], ent.key(p.val), bytes);
         if (head) { headmask |= 1u << j; len[j] = key_len(key[j]); ++nh; nb += len[j]; }
     }
@@ -646,17 +683,25 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
     }
     __syncthreads();
     unsigned long long o = s_prefix_h + oh, boff = s_prefix_b + ob;
-    const bool overflow = s_prefix_b + tb > key_bytes_cap;
+    const unsigned long long tile_b0 = s_prefix_b;
+    const bool overflow = tile_b0 + tb > key_bytes_cap;
     if (overflow && threadIdx.x == 0) atomicOr(&ctl->err, ERR_KEYS_FULL);
+    // key bytes of the tile go through shared memory when they fit, so that global memory
+    // sees 16-byte coalesced stores; the staging buffer keeps the destination's alignment
+    __shared__ __align__(16) uint8_t sbytes[ROWS_STAGE + 16];
+    const uint32_t mis = (uint32_t)(tile_b0 & 15);
+    const bool staged = !overflow && tb <= ROWS_STAGE;
 #pragma unroll
     for (int j = 0; j < ROWS_ITEMS; ++j) {
         const uint64_t pos = base + j;
         if (pos >= n) break;
         const SortItem &p = j == 0 ? prev : it[j - 1];
-        if ((headmask >> j) & 1u) {
+        const bool head = (headmask >> j) & 1u;
+        if (head) {
             rows.part[o] = it[j].hi;
             rows.key_off[o] = boff;
-            if (!overflow) write_key_bytes(rows.key_bytes + boff, key[j], len[j], bytes);
+            if (staged) write_key_bytes(sbytes + mis + (uint32_t)(boff - tile_b0), key[j], len[j], bytes);
+            else if (!overflow) write_key_bytes(rows.key_bytes + boff, key[j], len[j], bytes);
             // partition starts: rows are partition-sorted
             const uint32_t p_first = pos == 0 ? 0u : p.hi + 1u;
             if (pos == 0 || p.hi != it[j].hi)
@@ -664,12 +709,28 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
             boff += len[j];
             ++o;
         }
-        atomicAdd(&rows.count[o - 1], ent.cnt[it[j].val]);
+        // a row whose neighbours on both sides are other rows needs no atomic
+        const bool next_known = j + 1 < ROWS_ITEMS;
+        const bool next_head = next_known && (pos + 1 >= n || ((headmask >> (j + 1)) & 1u));
+        if (head && next_head) rows.count[o - 1] = cnt[j];
+        else atomicAdd(&rows.count[o - 1], cnt[j]);
         if (pos == n - 1) { // totals and sentinels
             ctl->n_out = o;
             ctl->key_bytes = boff;
             rows.key_off[o] = boff;
             for (uint32_t q = it[j].hi + 1u; q <= num_reducers; ++q) rows.part_begin[q] = o;
+        }
+    }
+    if (staged) {
+        __syncthreads();
+        uint8_t *dst = rows.key_bytes + (tile_b0 - mis); // 16-byte aligned
+        const uint32_t end = mis + (uint32_t)tb;
+        for (uint32_t c = threadIdx.x * 16; c < end; c += ROWS_THREADS * 16) {
+            if (c >= mis && c + 16 <= end) {
+                *(uint4 *)(dst + c) = *(const uint4 *)(sbytes + c);
+            } else { // first / last chunk shared with a neighbouring tile: bytes only
+                for (uint32_t q = c < mis ? mis : c; q < c + 16 && q < end; ++q) dst[q] = sbytes[q];
+            }
         }
     }
 }
