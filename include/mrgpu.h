@@ -169,6 +169,29 @@ int mr_stats_get(mr_ctx *ctx, mr_stats *out);
  * (partitionfn.lua:8-16 in IEEE binary64).  For glue-side checks. */
 uint32_t mr_partition_of(const void *key, uint64_t klen, uint32_t num_reducers);
 
+/* No counterpart in the reference (it has no device memory to manage).  Counts the
+ * whitespace-separated tokens of a device buffer WITHOUT allocating anything: for hosts that
+ * have given all device memory to their own pool, or that cannot take the device-wide
+ * synchronisation of cudaMalloc/cudaFree where they call this.  The caller owns input and
+ * output; the hash table the tokens are combined in is a fixed array inside the library
+ * (4 MiB per GPU, held until exit), hence the limits: n_bytes <= MR_STATIC_MAX_BYTES, tokens
+ * of at most 15 bytes, out_capacity >= number of distinct tokens (anything beyond is
+ * refused with an error code and, if err_text is given, a message).
+ * dev_text, dev_out, dev_n_out are device pointers; records come out in no particular
+ * order; *n_tokens (host, may be NULL) receives the token count.  The call clears the shared
+ * array, runs on `stream` and returns after synchronising it.  All calls on a device share
+ * the array: calls whose GPU work could overlap must be serialised by the caller.  The first
+ * call on each device looks up the array's address; make it before any stream capture. */
+#define MR_STATIC_MAX_BYTES (128u * 1024u)
+typedef struct mr_token_count {
+    uint8_t key[15];   /* token bytes, zero padded */
+    uint8_t len;       /* 1..15 */
+    uint64_t count;
+} mr_token_count;
+int mr_count_tokens_static(const void *dev_text, uint64_t n_bytes, mr_token_count *dev_out,
+                           uint64_t out_capacity, uint64_t *dev_n_out, uint64_t *n_tokens, void *stream,
+                           char *err_text, uint64_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,7 +21,7 @@ EXPORTS = (
     "mr_map_split", "mr_map_split_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
     "mr_result_release", "mr_shuffle_export", "mr_shuffle_recv_buffer", "mr_shuffle_import",
-    "mr_stats_get", "mr_partition_of",
+    "mr_stats_get", "mr_partition_of", "mr_count_tokens_static",
 )
 
 
@@ -106,6 +106,7 @@ def load(build_if_missing=True):
     L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
     L.mr_partition_of.argtypes = [C.c_char_p, u64, u32]
     L.mr_partition_of.restype = u32
+    L.mr_count_tokens_static.argtypes = [vp, u64, vp, u64, vp, C.POINTER(u64), vp, C.c_char_p, u64]
     _lib = L
     return L
 
@@ -236,3 +237,19 @@ class Context:
 
 def partition_of(key: bytes, num_reducers: int) -> int:
     return load().mr_partition_of(key, len(key), num_reducers)
+
+
+STATIC_MAX_BYTES = 128 * 1024
+TOKEN_COUNT_DTYPE = np.dtype([("key", "S15"), ("len", np.uint8), ("count", np.uint64)])
+
+
+def count_tokens_static(dev_text, n_bytes, dev_out, out_capacity, dev_n_out, stream=None):
+    """mr_count_tokens_static: every pointer is a raw device address owned by the caller; nothing is
+    allocated on the device.  Returns the number of tokens; raises NativeError with the library's text."""
+    err = C.create_string_buffer(256)
+    ntok = C.c_uint64(0)
+    rc = load().mr_count_tokens_static(dev_text, n_bytes, dev_out, out_capacity, dev_n_out, C.byref(ntok),
+                                       stream, err, len(err))
+    if rc != MR_OK:
+        raise NativeError(rc, err.value.decode())
+    return int(ntok.value)
