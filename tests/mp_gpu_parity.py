@@ -1,0 +1,58 @@
+"""Run under torchrun with one rank per GPU (nccl): multi-GPU parity of the whole job with the oracle.
+Every rank maps its shard, the partitions are exchanged with ONE all-to-all, the owner merges; the
+rows of every owned partition must equal the whole-job oracle rows of that partition, in order."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from lua_mapreduce_1_b200 import _native, corpus, parallel  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+
+def main():
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    for R, lines in ((10, [2000, 1500, 1, 0, 1800, 900, 2100, 333, 1200]), (15, [500] * 5)):
+        splits, _ = corpus.generate(lines=lines, threads=4)
+        splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+        want = O.run_staged(splits, R, 4)
+        ctx = _native.Context(R, 1 << 24, max_keys=1 << 19, device=local_rank, stream=stream.cuda_stream,
+                              world_size=world, rank=rank)
+        for it in range(2):                      # second pass re-uses the resident splits (keep_input)
+            if it == 0:
+                for i in parallel.shard_splits(len(splits), world, rank):
+                    ctx.map_split(i, splits[i])
+            else:
+                ctx.job_begin(keep_input=True)
+            ctx.map_finish()
+            sent, received = parallel.shuffle(ctx)
+            ctx.reduce_all()
+            got = ctx.rows()
+            owned = np.array([parallel.owner_of_partition(int(p), world) == rank for p in want.part], dtype=bool)
+            keys = want.keys()
+            wk = [k for k, o in zip(keys, owned) if o]
+            assert got.n == int(owned.sum()), (rank, got.n, int(owned.sum()))
+            assert got.keys() == wk, f"rank {rank}: keys / order differ"
+            assert np.array_equal(got.part, want.part[owned]) and np.array_equal(got.count, want.count[owned])
+            tot = torch.tensor([int(got.count.sum())], dtype=torch.int64, device=dev)
+            dist.all_reduce(tot)
+            assert int(tot.item()) == want.tokens
+        ctx.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    print(f"rank {rank}/{world}: multi-GPU parity ok")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,54 @@
+"""Run under torchrun (gloo, CPU): the host-side shuffle logic of parallel.py with world_size ranks.
+
+Each rank plays one GPU rank with the ORACLE standing in for the device kernels (this is test code):
+it counts its shard of the splits, packs (key, count) records per owner rank in the library's wire
+format, moves them with parallel.exchange_plan / exchange_segments, merges what it received, and
+checks its partitions against the whole-job oracle."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from lua_mapreduce_1_b200 import corpus, parallel  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+from wire import pack_segments, unpack_segments  # noqa: E402
+
+R = 10
+
+
+def main():
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    lines = [300, 1, 250, 0, 400, 123, 77]
+    splits, _ = corpus.generate(lines=lines, threads=2)
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))      # long keys travel as bytes
+    mine = parallel.shard_splits(len(splits), world, rank)
+    assert sorted(sum((parallel.shard_splits(len(splits), world, r) for r in range(world)), [])) == \
+        list(range(len(splits)))
+    local = O.run_naive([splits[i] for i in mine], R)                 # map + combine of this rank
+    send, send_off, send_nrec = pack_segments(local, world)
+    recv_bytes, recv_nrec, recv_off = parallel.exchange_plan(np.diff(send_off), send_nrec)
+    recv = parallel.exchange_segments(torch.from_numpy(send), send_off,
+                                      lambda n: torch.empty(max(n, 1), dtype=torch.uint8), recv_bytes)
+    merged = unpack_segments(recv.numpy(), recv_off, recv_nrec)       # {key: count}, summed over sources
+    want = O.run_naive(splits, R)                                      # whole job
+    owned = {k: c for p, k, c in zip(want.part, want.keys(), (int(c) for c in want.count))
+             if parallel.owner_of_partition(int(p), world) == rank}
+    assert merged == owned, (len(merged), len(owned))
+    # every partition has exactly one owner and nothing is lost
+    tot = torch.tensor([sum(merged.values())], dtype=torch.int64)
+    dist.all_reduce(tot)
+    assert int(tot.item()) == want.tokens
+    dist.barrier()
+    dist.destroy_process_group()
+    print(f"rank {rank}: ok, {len(merged)} keys owned")
+
+
+if __name__ == "__main__":
+    main()

@@ -221,3 +221,20 @@ def test_config2_full_size_exact():
         assert np.all(np.diff(got.part.astype(np.int64)) >= 0)
     finally:
         ctx.close()
+
+
+def test_multi_gpu_shuffle_parity():
+    # all visible GPUs (>= 2), one rank each, nccl all-to-all; skipped on a single-GPU box
+    import os
+    import subprocess
+    import sys
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", "29655", os.path.join(root, "tests", "mp_gpu_parity.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
+    assert p.stdout.count("multi-GPU parity ok") == n
