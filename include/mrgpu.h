@@ -144,18 +144,26 @@ int mr_reduce_partition(mr_ctx *ctx, uint32_t part, mr_result **out);
 int mr_result_next(mr_result *res, const char **key, uint64_t *klen, uint64_t *count);
 void mr_result_release(mr_result *res);
 
-/* Shuffle seam (job.lua:208-221 write, job.lua:253-260 read): after
- * mr_map_finish, export this rank's combined (key, count) records grouped by
- * owner rank (owner = partition mod world_size); the caller moves the bytes
- * (NCCL all-to-all) and imports what it received before mr_reduce_all.
- * Record stream per destination: fixed 16-byte records {key word, count} followed
- * by the bytes of long keys.  Pointers are device pointers owned by the context. */
+/* Shuffle seam (job.lua:208-221 write, job.lua:253-260 read).  After mr_map_finish:
+ *   1. mr_shuffle_count   tallies this rank's combined (key, count) records per owner rank
+ *                         (owner = partition mod world_size); *dev_counts is a DEVICE array
+ *                         [2 * world_size]: records per destination, then long-key bytes per
+ *                         destination.  Asynchronous: the caller gathers the counts of all ranks
+ *                         (one all-gather) and reads them once.
+ *   2. mr_shuffle_pack    given the HOST copy of this rank's counts, packs one segment per
+ *                         destination: 24-byte records {k0, k1, count} followed by the bytes of
+ *                         keys longer than 15 bytes; segment size = (24 * records + bytes)
+ *                         rounded up to 16.  Asynchronous.
+ *   3. the caller moves the segments (NCCL all-to-all) into mr_shuffle_recv_buffer and calls
+ *      mr_shuffle_import before mr_reduce_all.
+ * Pointers in the plan are owned by the context. */
 typedef struct mr_shuffle_plan {
     const uint8_t *send_base;  /* device buffer holding every outgoing segment */
     const uint64_t *send_off;  /* host array [world_size+1]: byte offsets per destination */
     const uint64_t *send_nrec; /* host array [world_size]: records per destination */
 } mr_shuffle_plan;
-int mr_shuffle_export(mr_ctx *ctx, mr_shuffle_plan *plan);
+int mr_shuffle_count(mr_ctx *ctx, const uint64_t **dev_counts);
+int mr_shuffle_pack(mr_ctx *ctx, const uint64_t *counts, mr_shuffle_plan *plan);
 /* Reserve room for `bytes` incoming bytes; returns the device pointer to receive into. */
 int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr);
 /* recv_off: host array [world_size+1] of byte offsets per source inside the receive

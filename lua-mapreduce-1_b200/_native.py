@@ -20,7 +20,7 @@ EXPORTS = (
     "mr_abi_version", "mr_ctx_create", "mr_ctx_destroy", "mr_last_error", "mr_job_begin",
     "mr_map_split", "mr_map_split_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
-    "mr_result_release", "mr_shuffle_export", "mr_shuffle_recv_buffer", "mr_shuffle_import",
+    "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
     "mr_stats_get", "mr_partition_of", "mr_count_tokens_static",
 )
 
@@ -100,7 +100,8 @@ def load(build_if_missing=True):
     L.mr_result_next.argtypes = [vp, C.POINTER(vp), C.POINTER(u64), C.POINTER(u64)]
     L.mr_result_release.argtypes = [vp]
     L.mr_result_release.restype = None
-    L.mr_shuffle_export.argtypes = [vp, C.POINTER(ShufflePlan)]
+    L.mr_shuffle_count.argtypes = [vp, C.POINTER(vp)]
+    L.mr_shuffle_pack.argtypes = [vp, C.POINTER(u64), C.POINTER(ShufflePlan)]
     L.mr_shuffle_recv_buffer.argtypes = [vp, u64, C.POINTER(vp)]
     L.mr_shuffle_import.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
@@ -215,9 +216,17 @@ class Context:
         return s
 
     # ---- shuffle seam
-    def shuffle_export(self):
+    def shuffle_count(self):
+        """Device address of this rank's [2 * world_size] counts (records, then long-key bytes, per destination)."""
+        p = C.c_void_p()
+        self._ck(self._L.mr_shuffle_count(self._h, C.byref(p)))
+        return p.value
+
+    def shuffle_pack(self, counts):
+        """counts: host copy of the array shuffle_count points at.  Returns (device base, byte offsets, records)."""
+        c = np.ascontiguousarray(counts, dtype=np.uint64)
         plan = ShufflePlan()
-        self._ck(self._L.mr_shuffle_export(self._h, C.byref(plan)))
+        self._ck(self._L.mr_shuffle_pack(self._h, c.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(plan)))
         W = self.world_size
         off = np.array([plan.send_off[i] for i in range(W + 1)], dtype=np.uint64)
         nrec = np.array([plan.send_nrec[i] for i in range(W)], dtype=np.uint64)

@@ -39,23 +39,37 @@ __global__ void ctl_init_kernel(Ctl *ctl)
 
 __global__ void ctl_set_n_kernel(Ctl *ctl, unsigned long long n) { ctl->n = n; }
 
-// shuffle: count records / long bytes per destination rank
+constexpr uint32_t MAX_WORLD = 1024;
+
+// shuffle: count records / long-key bytes per destination rank (per-CTA tallies in shared
+// memory, then one atomic per destination per CTA)
 __global__ void __launch_bounds__(256) export_count_kernel(EntryArrays ent, uint32_t world,
                                                            unsigned long long *nrec,
                                                            unsigned long long *nbytes, const Ctl *ctl)
 {
+    __shared__ unsigned int s_rec[MAX_WORLD];
+    __shared__ unsigned long long s_bytes[MAX_WORLD];
+    for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
+    __syncthreads();
     const uint64_t n = ctl->n;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         uint32_t d = ent.part(i) % world;
-        atomicAdd(&nrec[d], 1ull);
+        atomicAdd(&s_rec[d], 1u);
         Key k = ent.key(i);
-        if (key_is_long(k)) atomicAdd(&nbytes[d], (unsigned long long)key_len(k));
+        if (key_is_long(k)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(k));
+    }
+    __syncthreads();
+    for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) {
+        if (s_rec[d]) atomicAdd(&nrec[d], (unsigned long long)s_rec[d]);
+        if (s_bytes[d]) atomicAdd(&nbytes[d], s_bytes[d]);
     }
 }
 
 // segment layout per destination: [records 24 B each {k0, k1, count}][long-key bytes]; long
-// keys are rewritten to offsets relative to the start of the segment's byte block
+// keys are rewritten to offsets relative to the start of the segment's byte block.  Each CTA
+// works on one contiguous chunk of entries: tally per destination, reserve its ranges with
+// one atomic per destination, then hand out slots from shared-memory cursors.
 __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, const uint8_t *bytes,
                                                              uint32_t world, uint8_t *send,
                                                              const unsigned long long *seg_off,
@@ -63,16 +77,35 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
                                                              unsigned long long *rec_cur,
                                                              unsigned long long *byte_cur, const Ctl *ctl)
 {
+    __shared__ unsigned int s_rec[MAX_WORLD];
+    __shared__ unsigned long long s_bytes[MAX_WORLD], s_rec_base[MAX_WORLD], s_byte_base[MAX_WORLD];
     const uint64_t n = ctl->n;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+    const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
+    if (lo >= hi) return;
+    for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
+    __syncthreads();
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        uint32_t d = ent.part(i) % world;
+        atomicAdd(&s_rec[d], 1u);
+        Key k = ent.key(i);
+        if (key_is_long(k)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(k));
+    }
+    __syncthreads();
+    for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) {
+        s_rec_base[d] = s_rec[d] ? atomicAdd(&rec_cur[d], (unsigned long long)s_rec[d]) : 0;
+        s_byte_base[d] = s_bytes[d] ? atomicAdd(&byte_cur[d], s_bytes[d]) : 0;
+        s_rec[d] = 0; s_bytes[d] = 0;
+    }
+    __syncthreads();
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
         uint32_t d = ent.part(i) % world;
         Key k = ent.key(i);
         uint8_t *seg = send + seg_off[d];
-        unsigned long long r = atomicAdd(&rec_cur[d], 1ull);
+        unsigned long long r = s_rec_base[d] + atomicAdd(&s_rec[d], 1u);
         if (key_is_long(k)) {
             uint32_t len = key_len(k);
-            unsigned long long bo = atomicAdd(&byte_cur[d], (unsigned long long)len);
+            unsigned long long bo = s_byte_base[d] + atomicAdd(&s_bytes[d], (unsigned long long)len);
             uint8_t *dst = seg + nrec_total[d] * REC_BYTES + bo;
             uint64_t off = key_off(k);
             for (uint32_t j = 0; j < len; ++j) dst[j] = bytes[off + j];
@@ -141,6 +174,7 @@ struct mr_ctx {
     uint64_t key_bytes_cap = 0;
     Ctl *d_ctl = nullptr;
     Ctl *h_ctl = nullptr; // pinned
+    unsigned long long *h_stage = nullptr; // pinned, [MAX_WORLD + 1]
     const uint8_t *bytes_base = nullptr;
 
     // shuffle
@@ -151,6 +185,7 @@ struct mr_ctx {
     unsigned long long *d_shuf = nullptr; // [4][world]: nrec, nbytes, rec_cur, byte_cur  + [world+1] seg_off
     std::vector<uint64_t> send_off, send_nrec;
     bool imported = false;
+    bool shuffle_counted = false;
 
     // state
     enum { IDLE, MAPPED, REDUCED, SYNCED } state = IDLE;
@@ -261,6 +296,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     cudaFree(ctx->rows.part_begin);
     cudaFree(ctx->d_ctl); cudaFree(ctx->d_send); cudaFree(ctx->d_recv); cudaFree(ctx->d_shuf);
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     for (cudaEvent_t e : { ctx->ev_map0, ctx->ev_map1, ctx->ev_red0, ctx->ev_red1 })
         if (e) cudaEventDestroy(e);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -280,7 +316,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
         return fail(nullptr, MR_ERR_UNSUPPORTED, "mr_ctx_create: unsupported map/reduce/partition kind");
     if (cfg->num_reducers == 0 || cfg->num_reducers > (1u << 24))
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: num_reducers must be in 1..2^24");
-    if (cfg->world_size == 0 || cfg->rank >= cfg->world_size || cfg->world_size > 1024)
+    if (cfg->world_size == 0 || cfg->rank >= cfg->world_size || cfg->world_size > MAX_WORLD)
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: bad world_size/rank");
     if (cfg->arena_bytes == 0 || cfg->arena_bytes + ARENA_SLACK >= MAX_BYTE_SPACE)
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: arena_bytes must be in 1..2^37");
@@ -349,6 +385,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->rows.part_begin, (uint64_t)cfg->num_reducers + 1));
     CUC(dmalloc(&ctx->d_ctl, 1));
     CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
+    CUC(cudaMallocHost((void **)&ctx->h_stage, (MAX_WORLD + 1) * 8));
     CUC(dmalloc(&ctx->d_shuf, 5ull * cfg->world_size + 1));
     CUC(cudaEventCreate(&ctx->ev_map0)); CUC(cudaEventCreate(&ctx->ev_map1));
     CUC(cudaEventCreate(&ctx->ev_red0)); CUC(cudaEventCreate(&ctx->ev_red1));
@@ -377,6 +414,7 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
     CU(cudaGetLastError());
     ctx->bytes_base = ctx->d_arena;
     ctx->imported = false;
+    ctx->shuffle_counted = false;
     ctx->state = mr_ctx::IDLE;
     ctx->rows_cached = false;
     ctx->tie_rounds = 0;
@@ -696,46 +734,60 @@ int mr_stats_get(mr_ctx *ctx, mr_stats *out)
 }
 
 // ---------------------------------------------------------------- shuffle
-int mr_shuffle_export(mr_ctx *ctx, mr_shuffle_plan *plan)
+int mr_shuffle_count(mr_ctx *ctx, const uint64_t **dev_counts)
 {
-    if (!ctx || !plan) return MR_ERR_INVALID;
-    if (ctx->state != mr_ctx::MAPPED || ctx->imported)
-        return fail(ctx, MR_ERR_INVALID, "mr_shuffle_export: call after mr_map_finish, once per job");
+    if (!ctx || !dev_counts) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::MAPPED || ctx->imported || ctx->shuffle_counted)
+        return fail(ctx, MR_ERR_INVALID, "mr_shuffle_count: call after mr_map_finish, once per job");
     CU(cudaSetDevice(ctx->cfg.device));
     if (ctx->map_dirty) { int rc = mr_map_finish(ctx); if (rc) return rc; }
     const uint32_t W = ctx->cfg.world_size;
     cudaStream_t s = ctx->stream;
     int rc = launch_compact(ctx);
     if (rc) return rc;
-    unsigned long long *nrec = ctx->d_shuf, *nbytes = ctx->d_shuf + W, *rec_cur = ctx->d_shuf + 2 * W,
-                       *byte_cur = ctx->d_shuf + 3 * W, *seg_off = ctx->d_shuf + 4 * W;
+    sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->max_keys); // clamps n (its digit plan is redone after import)
     CU(cudaMemsetAsync(ctx->d_shuf, 0, (5ull * W + 1) * 8, s));
-    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 4);
-    export_count_kernel<<<g, 256, 0, s>>>(ctx->ent, W, nrec, nbytes, ctx->d_ctl);
-    ctx->stats.launches++;
-    std::vector<unsigned long long> h(2 * W);
-    CU(cudaMemcpyAsync(h.data(), ctx->d_shuf, 2ull * W * 8, cudaMemcpyDeviceToHost, s));
-    CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
-    if ((rc = check_device_err(ctx, ctx->h_ctl->err))) return rc;
-    ctx->info.map_keys = ctx->h_ctl->n;
+    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
+    export_count_kernel<<<g, 256, 0, s>>>(ctx->ent, W, ctx->d_shuf, ctx->d_shuf + W, ctx->d_ctl);
+    ctx->stats.launches += 2;
+    CU(cudaGetLastError());
+    ctx->shuffle_counted = true;
+    *dev_counts = (const uint64_t *)ctx->d_shuf;
+    return MR_OK;
+}
+
+int mr_shuffle_pack(mr_ctx *ctx, const uint64_t *counts, mr_shuffle_plan *plan)
+{
+    if (!ctx || !counts || !plan) return MR_ERR_INVALID;
+    if (!ctx->shuffle_counted || ctx->imported)
+        return fail(ctx, MR_ERR_INVALID, "mr_shuffle_pack: call after mr_shuffle_count");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    unsigned long long *nrec = ctx->d_shuf, *rec_cur = ctx->d_shuf + 2 * W, *byte_cur = ctx->d_shuf + 3 * W,
+                       *seg_off = ctx->d_shuf + 4 * W;
     ctx->send_off.assign(W + 1, 0);
     ctx->send_nrec.assign(W, 0);
+    uint64_t nkeys = 0;
     for (uint32_t d = 0; d < W; ++d) {
-        ctx->send_nrec[d] = h[d];
-        ctx->send_off[d + 1] = ctx->send_off[d] + round_up(h[d] * REC_BYTES + h[W + d], 16);
+        ctx->send_nrec[d] = counts[d];
+        nkeys += counts[d];
+        ctx->send_off[d + 1] = ctx->send_off[d] + round_up(counts[d] * REC_BYTES + counts[W + d], 16);
     }
+    ctx->info.map_keys = nkeys;
     const uint64_t total = ctx->send_off[W];
     if (total + 64 > ctx->send_cap) {
+        CU(cudaStreamSynchronize(s));
         if (ctx->d_send) CU(cudaFree(ctx->d_send));
         ctx->d_send = nullptr;
         ctx->send_cap = total + total / 4 + 4096;
         CU(dmalloc(&ctx->d_send, ctx->send_cap));
     }
-    std::vector<unsigned long long> so(ctx->send_off.begin(), ctx->send_off.end());
-    CU(cudaMemcpyAsync(seg_off, so.data(), (W + 1) * 8ull, cudaMemcpyHostToDevice, s));
-    CU(cudaStreamSynchronize(s)); // `so` is pageable host memory going out of scope
-    CU(cudaMemsetAsync(ctx->d_send, 0, total + 64, s));
+    // offsets go up through pinned memory so that no host synchronisation is needed
+    unsigned long long *stage = ctx->h_stage;
+    for (uint32_t d = 0; d <= W; ++d) stage[d] = ctx->send_off[d];
+    CU(cudaMemcpyAsync(seg_off, stage, (W + 1) * 8ull, cudaMemcpyHostToDevice, s));
+    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
     export_scatter_kernel<<<g, 256, 0, s>>>(ctx->ent, ctx->bytes_base, W, ctx->d_send, seg_off, nrec, rec_cur,
                                             byte_cur, ctx->d_ctl);
     ctx->stats.launches++;
@@ -783,7 +835,8 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
         base += n;
     }
     // fresh control block for the reduce side, keeping the token count and errors
-    CU(cudaMemsetAsync(&ctx->d_ctl->or_lo, 0, offsetof(Ctl, tokens) - offsetof(Ctl, or_lo), s));
+    CU(cudaMemsetAsync(&ctx->d_ctl->or_lo, 0, offsetof(Ctl, err) - offsetof(Ctl, or_lo), s));
+    CU(cudaMemsetAsync(&ctx->d_ctl->n_tie, 0, offsetof(Ctl, tokens) - offsetof(Ctl, n_tie), s));
     ctl_init_kernel<<<1, 1, 0, s>>>(ctx->d_ctl);
     ctl_set_n_kernel<<<1, 1, 0, s>>>(ctx->d_ctl, base);
     ctx->bytes_base = ctx->d_recv;

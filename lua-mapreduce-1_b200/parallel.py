@@ -2,19 +2,22 @@
 
 Replaces the reference's file-based all-to-all (every mapper writes <= R run files,
 job.lua:208-221; every reducer lists and reads <= M of them, job.lua:253-260;
-server.lua:279-329 discovers them).  Here every rank exports its combined
-(key, count) records grouped by owner rank (owner = partition mod world_size, so each
-reduce partition is owned by exactly one GPU), the segments move with ONE variable-size
-all-to-all (NCCL over NVLink on GPUs; gloo in the CPU tests of the host logic), and the
-owner merges what it received with the radix sort + segmented reduce.
+server.lua:279-329 discovers them).  Here every rank tallies its combined (key, count)
+records per owner rank (owner = partition mod world_size, so each reduce partition is owned
+by exactly one GPU), the tallies of all ranks are gathered once (the only host
+synchronisation of the shuffle), every rank packs one segment per owner, the segments move
+with ONE variable-size all-to-all (NCCL over NVLink on GPUs; gloo in the CPU tests of this
+host logic), and the owner merges what it received with the radix sort + segmented reduce.
 
-Segment wire format (per source -> destination): n records of 16 bytes
-{key word u64, count u64} followed by the bytes of the keys of 8+ bytes; a long key's
-word is 1<<63 | offset-in-byte-block << 26 | length.
+Segment wire format (per source -> destination): n records of 24 bytes {k0, k1, count}
+followed by the bytes of the keys longer than 15 bytes, the whole rounded up to 16 bytes
+(include/mrgpu.h, mr_shuffle_pack).
 """
 import numpy as np
 import torch
 import torch.distributed as dist
+
+REC_BYTES = 24
 
 
 def shard_splits(n_splits, world_size, rank):
@@ -29,8 +32,8 @@ def owner_of_partition(part, world_size):
 class _DeviceBytes:
     """Wraps a raw device pointer so torch can view it (no copy)."""
 
-    def __init__(self, ptr, n):
-        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "|u1", "data": (int(ptr), False),
+    def __init__(self, ptr, n, typestr="|u1"):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False),
                                          "version": 2}
 
 
@@ -40,39 +43,56 @@ def device_bytes(ptr, n, device):
     return torch.as_tensor(_DeviceBytes(ptr, n), device=device)
 
 
-def exchange_plan(send_bytes, send_nrec, group=None, device="cpu"):
-    """Tells every rank what it will receive.  send_bytes / send_nrec: per destination.
-    Returns (recv_bytes, recv_nrec, recv_off) as int64 numpy arrays (recv_off has W+1 entries)."""
+def device_i64(ptr, n, device):
+    return torch.as_tensor(_DeviceBytes(ptr, n, "<i8"), device=device)
+
+
+def gather_counts(counts, group=None):
+    """counts: int64 tensor [2W] of this rank (records per destination, then long-key bytes per
+    destination), on the device the backend works with.  Returns the [W, 2W] matrix of all ranks
+    as numpy -- the one host synchronisation of the shuffle."""
     W = dist.get_world_size(group)
-    meta = torch.tensor(np.stack([np.asarray(send_bytes, np.int64), np.asarray(send_nrec, np.int64)], 1),
-                        dtype=torch.int64, device=device).contiguous()
-    got = torch.empty_like(meta)
-    dist.all_to_all_single(got, meta, group=group)
-    got = got.cpu().numpy()
-    recv_bytes, recv_nrec = got[:, 0].copy(), got[:, 1].copy()
+    out = [torch.empty_like(counts) for _ in range(W)]
+    dist.all_gather(out, counts.contiguous(), group=group)
+    return torch.stack(out).cpu().numpy().astype(np.int64)
+
+
+def segment_bytes(nrec, nbytes):
+    return (nrec * REC_BYTES + nbytes + 15) // 16 * 16
+
+
+def plan_from_counts(matrix, rank):
+    """From the gathered counts: what this rank sends and receives.
+    Returns (send_off [W+1], recv_off [W+1], recv_nrec [W]) as int64 numpy arrays."""
+    W = matrix.shape[0]
+    send = segment_bytes(matrix[rank, :W], matrix[rank, W:])
+    recv = segment_bytes(matrix[:, rank], matrix[:, W + rank])
+    send_off = np.zeros(W + 1, np.int64)
     recv_off = np.zeros(W + 1, np.int64)
-    np.cumsum(recv_bytes, out=recv_off[1:])
-    return recv_bytes, recv_nrec, recv_off
+    np.cumsum(send, out=send_off[1:])
+    np.cumsum(recv, out=recv_off[1:])
+    return send_off, recv_off, matrix[:, rank].copy()
 
 
-def exchange_segments(send, send_off, recv_alloc, recv_bytes, group=None):
-    """One variable-size all-to-all of the packed segments.
-    send: uint8 tensor holding all outgoing segments; send_off: W+1 byte offsets;
-    recv_alloc(nbytes) -> uint8 tensor to receive into."""
-    send_sizes = np.diff(np.asarray(send_off, np.int64)).tolist()
-    total = int(np.sum(recv_bytes))
-    recv = recv_alloc(total)
-    dist.all_to_all_single(recv[:total], send[:int(send_off[-1])], output_split_sizes=[int(x) for x in recv_bytes],
-                           input_split_sizes=send_sizes, group=group)
+def exchange_segments(send, send_off, recv, recv_off, group=None):
+    """One variable-size all-to-all of the packed segments (uint8 tensors)."""
+    dist.all_to_all_single(recv[:int(recv_off[-1])], send[:int(send_off[-1])],
+                           output_split_sizes=np.diff(recv_off).tolist(),
+                           input_split_sizes=np.diff(send_off).tolist(), group=group)
     return recv
 
 
 def shuffle(ctx, group=None):
-    """mr_shuffle_export -> all-to-all -> mr_shuffle_import on a _native.Context (GPU ranks)."""
+    """count -> gather -> pack -> all-to-all -> import on a _native.Context (GPU ranks)."""
     dev = torch.device("cuda", torch.cuda.current_device())
-    base, off, nrec = ctx.shuffle_export()
-    send = device_bytes(base, int(off[-1]), dev)
-    recv_bytes, recv_nrec, recv_off = exchange_plan(np.diff(off.astype(np.int64)), nrec, group, dev)
-    exchange_segments(send, off, lambda n: device_bytes(ctx.shuffle_recv_buffer(n), n, dev), recv_bytes, group)
+    W, rank = ctx.world_size, ctx.rank
+    counts = device_i64(ctx.shuffle_count(), 2 * W, dev)
+    matrix = gather_counts(counts, group)
+    send_off, recv_off, recv_nrec = plan_from_counts(matrix, rank)
+    base, off, nrec = ctx.shuffle_pack(matrix[rank].astype(np.uint64))
+    assert np.array_equal(off.astype(np.int64), send_off)
+    send = device_bytes(base, int(send_off[-1]), dev)
+    recv = device_bytes(ctx.shuffle_recv_buffer(int(recv_off[-1])), int(recv_off[-1]), dev)
+    exchange_segments(send, send_off, recv, recv_off, group)
     ctx.shuffle_import(recv_off.astype(np.uint64), recv_nrec.astype(np.uint64))
-    return int(off[-1]), int(recv_off[-1])
+    return int(send_off[-1]), int(recv_off[-1])

@@ -32,10 +32,13 @@ def main():
     assert sorted(sum((parallel.shard_splits(len(splits), world, r) for r in range(world)), [])) == \
         list(range(len(splits)))
     local = O.run_naive([splits[i] for i in mine], R)                 # map + combine of this rank
-    send, send_off, send_nrec = pack_segments(local, world)
-    recv_bytes, recv_nrec, recv_off = parallel.exchange_plan(np.diff(send_off), send_nrec)
-    recv = parallel.exchange_segments(torch.from_numpy(send), send_off,
-                                      lambda n: torch.empty(max(n, 1), dtype=torch.uint8), recv_bytes)
+    send, send_off, send_nrec, send_lbytes = pack_segments(local, world)
+    counts = torch.from_numpy(np.concatenate([send_nrec, send_lbytes]).astype(np.int64))
+    matrix = parallel.gather_counts(counts)
+    plan_send_off, recv_off, recv_nrec = parallel.plan_from_counts(matrix, rank)
+    assert np.array_equal(plan_send_off, send_off)        # the plan predicts the packed layout
+    recv = torch.empty(max(int(recv_off[-1]), 1), dtype=torch.uint8)
+    parallel.exchange_segments(torch.from_numpy(send), send_off, recv, recv_off)
     merged = unpack_segments(recv.numpy(), recv_off, recv_nrec)       # {key: count}, summed over sources
     want = O.run_naive(splits, R)                                      # whole job
     owned = {k: c for p, k, c in zip(want.part, want.keys(), (int(c) for c in want.count))

@@ -19,8 +19,9 @@ def _encode(key, long_off):
 
 
 def pack_segments(rows, world):
-    """rows: oracle.Rows of one rank.  Returns (uint8 buffer, byte offsets [world+1], records [world])."""
-    segs, nrec = [], []
+    """rows: oracle.Rows of one rank.  Returns (uint8 buffer, byte offsets [world+1], records [world],
+    long-key bytes [world])."""
+    segs, nrec, lbytes = [], [], []
     for d in range(world):
         recs, blob = [], bytearray()
         for p, k, c in zip(rows.part, rows.keys(), rows.count):
@@ -34,10 +35,11 @@ def pack_segments(rows, world):
         seg += b"\0" * (-len(seg) % 16)
         segs.append(seg)
         nrec.append(len(recs))
+        lbytes.append(len(blob))
     off = np.zeros(world + 1, np.int64)
     np.cumsum([len(s) for s in segs], out=off[1:])
     buf = np.frombuffer(b"".join(segs) or b"\0", dtype=np.uint8).copy()
-    return buf, off, np.array(nrec, np.int64)
+    return buf, off, np.array(nrec, np.int64), np.array(lbytes, np.int64)
 
 
 def unpack_segments(buf, off, nrec):
