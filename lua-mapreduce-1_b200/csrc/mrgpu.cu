@@ -26,6 +26,7 @@ namespace {
 std::string g_create_error;
 
 constexpr uint64_t ARENA_SLACK = SEG + SEG_AHEAD + 256;
+constexpr uint64_t TAIL_GUARD = SEG_AHEAD + 64; // spaces after the last mapped segment (look-ahead window)
 constexpr uint64_t REC_BYTES = 24; // shuffle record {k0, k1, count}
 
 inline uint64_t round_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
@@ -38,6 +39,18 @@ __global__ void ctl_init_kernel(Ctl *ctl)
 }
 
 __global__ void ctl_set_n_kernel(Ctl *ctl, unsigned long long n) { ctl->n = n; }
+
+// gaps between staged splits (and the tail) are filled with 0x20 by ONE kernel at map time, so
+// that the host->device copies of the splits run back to back on the copy engine
+struct Gap { unsigned long long off, len; };
+constexpr uint32_t MAX_GAPS = 1u << 15;
+__global__ void __launch_bounds__(256) fill_gaps_kernel(uint8_t *arena, const Gap *gaps, uint32_t ngaps)
+{
+    for (uint32_t g = blockIdx.x; g < ngaps; g += gridDim.x) {
+        const Gap gp = gaps[g];
+        for (unsigned long long i = threadIdx.x; i < gp.len; i += blockDim.x) arena[gp.off + i] = 0x20;
+    }
+}
 
 constexpr uint32_t MAX_WORLD = 1024;
 
@@ -157,6 +170,9 @@ struct mr_ctx {
     uint64_t mapped_segs = 0; // segments already consumed by mr_map_finish
     uint64_t input_bytes = 0;
     bool any_split = false;
+    Gap *h_gaps = nullptr;    // pinned
+    Gap *d_gaps = nullptr;
+    uint32_t ngaps = 0;
 
     // tables and entries
     GEntry *d_gtab = nullptr;
@@ -192,7 +208,13 @@ struct mr_ctx {
     bool map_dirty = false; // splits staged since the last mr_map_finish
     mr_job_info info{};
     uint32_t tie_rounds = 0;
-    cudaEvent_t ev_map0 = nullptr, ev_map1 = nullptr, ev_red0 = nullptr, ev_red1 = nullptr;
+    cudaEvent_t ev_map0 = nullptr, ev_map1 = nullptr, ev_red0 = nullptr, ev_red1 = nullptr, ev_gaps = nullptr;
+    bool gaps_pending = false;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy = nullptr, ev_job = nullptr;
+    bool copies_pending = false, copy_synced = false;
+    uint64_t staged_since_map = 0, auto_map_bytes = 32ull << 20;
+    uint64_t remap_upto = 0;  // keep_input: segments that hold the resident splits
     bool map_timed = false, red_timed = false;
     mr_stats stats{};
 
@@ -297,7 +319,10 @@ void mr_ctx_destroy(mr_ctx *ctx)
     cudaFree(ctx->d_ctl); cudaFree(ctx->d_send); cudaFree(ctx->d_recv); cudaFree(ctx->d_shuf);
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
-    for (cudaEvent_t e : { ctx->ev_map0, ctx->ev_map1, ctx->ev_red0, ctx->ev_red1 })
+    if (ctx->h_gaps) cudaFreeHost(ctx->h_gaps);
+    cudaFree(ctx->d_gaps);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    for (cudaEvent_t e : { ctx->ev_map0, ctx->ev_map1, ctx->ev_red0, ctx->ev_red1, ctx->ev_gaps, ctx->ev_copy, ctx->ev_job })
         if (e) cudaEventDestroy(e);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -339,7 +364,8 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     ctx->cfg = *cfg;
     ctx->sm_count = prop.multiProcessorCount;
     if (const char *v = getenv("MRGPU_MAP_VARIANT")) ctx->map_variant = atoi(v);
-    ctx->arena_cap = round_up(cfg->arena_bytes, SEG) + SEG;
+    // room for the caller's bytes plus what each map round pads (a segment and the guard)
+    ctx->arena_cap = round_up(cfg->arena_bytes, SEG) + SEG + (cfg->arena_bytes / (16ull << 20) + 8) * (SEG + 2 * TAIL_GUARD);
     uint64_t mk = cfg->max_keys;
     if (mk == 0) mk = std::min<uint64_t>(std::max<uint64_t>(cfg->arena_bytes / 64, 1u << 16), 1u << 24);
     if (mk >= (1ull << 30)) { delete ctx; return fail(nullptr, MR_ERR_INVALID, "max_keys must be < 2^30"); }
@@ -386,9 +412,16 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->d_ctl, 1));
     CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
     CUC(cudaMallocHost((void **)&ctx->h_stage, (MAX_WORLD + 1) * 8));
+    CUC(cudaMallocHost((void **)&ctx->h_gaps, (MAX_GAPS + 1) * sizeof(Gap)));
+    CUC(dmalloc(&ctx->d_gaps, MAX_GAPS + 1));
     CUC(dmalloc(&ctx->d_shuf, 5ull * cfg->world_size + 1));
     CUC(cudaEventCreate(&ctx->ev_map0)); CUC(cudaEventCreate(&ctx->ev_map1));
     CUC(cudaEventCreate(&ctx->ev_red0)); CUC(cudaEventCreate(&ctx->ev_red1));
+    CUC(cudaEventCreateWithFlags(&ctx->ev_gaps, cudaEventDisableTiming));
+    CUC(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
+    CUC(cudaEventCreateWithFlags(&ctx->ev_job, cudaEventDisableTiming));
+    CUC(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    if (const char *v = getenv("MRGPU_AUTO_MAP_MB")) ctx->auto_map_bytes = (uint64_t)atoll(v) << 20;
     ctx->bytes_base = ctx->d_arena;
     int rc = mr_job_begin(ctx, 0);
     if (rc != MR_OK) { std::string m = ctx->err; mr_ctx_destroy(ctx); return fail(nullptr, rc, "%s", m.c_str()); }
@@ -403,10 +436,16 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
     if (!keep_input) {
         ctx->used = 0; ctx->mapped_segs = 0; ctx->input_bytes = 0; ctx->any_split = false;
         ctx->map_dirty = false;
+        ctx->ngaps = 0;
+        ctx->copy_synced = false;
+        ctx->staged_since_map = 0;
+        ctx->remap_upto = 0;
     } else {
         // keep the staged splits: the next mr_map_finish maps all of them again
+        ctx->remap_upto = std::max(ctx->remap_upto, ctx->mapped_segs);
         ctx->mapped_segs = 0;
         ctx->map_dirty = ctx->any_split;
+        ctx->staged_since_map = 0;
     }
     CU(cudaMemsetAsync(ctx->d_gtab, 0, ctx->slots * sizeof(GEntry), ctx->stream));
     CU(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
@@ -425,6 +464,22 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
     return MR_OK;
 }
 
+static int run_map_round(mr_ctx *ctx);
+
+static int flush_gaps(mr_ctx *ctx)
+{
+    if (!ctx->ngaps) return MR_OK;
+    CU(cudaMemcpyAsync(ctx->d_gaps, ctx->h_gaps, ctx->ngaps * sizeof(Gap), cudaMemcpyHostToDevice, ctx->stream));
+    fill_gaps_kernel<<<std::min<uint32_t>(ctx->ngaps, 1024u), 256, 0, ctx->stream>>>(ctx->d_arena, ctx->d_gaps, ctx->ngaps);
+    CU(cudaGetLastError());
+    // the pinned list is reused by later calls: wait until the copy above has read it
+    CU(cudaEventRecord(ctx->ev_gaps, ctx->stream));
+    ctx->gaps_pending = true;
+    ctx->stats.launches++;
+    ctx->ngaps = 0;
+    return MR_OK;
+}
+
 static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKind kind)
 {
     if (!ctx) return MR_ERR_INVALID;
@@ -437,13 +492,33 @@ static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKin
     if (off + n + SEG > ctx->arena_cap)
         return fail(ctx, MR_ERR_NOMEM, "mr_map_split: arena full (%llu + %llu > %llu bytes)",
                     (unsigned long long)off, (unsigned long long)n, (unsigned long long)ctx->arena_cap);
-    if (off > ctx->used) CU(cudaMemsetAsync(ctx->d_arena + ctx->used, 0x20, off - ctx->used, ctx->stream));
-    if (n) CU(cudaMemcpyAsync(ctx->d_arena + off, bytes, n, kind, ctx->stream));
-    if (kind == cudaMemcpyHostToDevice) ctx->stats.h2d_bytes += n;
+    if (ctx->gaps_pending) { CU(cudaEventSynchronize(ctx->ev_gaps)); ctx->gaps_pending = false; }
+    if (off > ctx->used) {
+        if (ctx->ngaps == MAX_GAPS) { int rc = flush_gaps(ctx); if (rc) return rc; }
+        ctx->h_gaps[ctx->ngaps].off = ctx->used;
+        ctx->h_gaps[ctx->ngaps].len = off - ctx->used;
+        ctx->ngaps++;
+    }
+    if (kind == cudaMemcpyHostToDevice) {
+        // host->device copies run on their own stream so that they overlap the map rounds
+        if (!ctx->copy_synced) {
+            // the arena may still be read by the previous job: wait for everything queued so far
+            CU(cudaEventRecord(ctx->ev_job, ctx->stream));
+            CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_job, 0));
+            ctx->copy_synced = true;
+        }
+        if (n) CU(cudaMemcpyAsync(ctx->d_arena + off, bytes, n, kind, ctx->copy_stream));
+        ctx->copies_pending = true;
+        ctx->stats.h2d_bytes += n;
+    } else if (n) {
+        CU(cudaMemcpyAsync(ctx->d_arena + off, bytes, n, kind, ctx->stream));
+    }
     ctx->used = off + n;
     ctx->input_bytes += n;
     ctx->any_split = true;
     ctx->map_dirty = true;
+    ctx->staged_since_map += n;
+    if (ctx->auto_map_bytes && ctx->staged_since_map >= ctx->auto_map_bytes) return run_map_round(ctx);
     return MR_OK;
 }
 
@@ -459,6 +534,56 @@ int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, u
     return stage_split(ctx, dev_bytes, n, cudaMemcpyDeviceToDevice);
 }
 
+// Maps every segment staged since the last round (tokenise + combine into the global table).
+static int run_map_round(mr_ctx *ctx)
+{
+    if (!ctx->map_dirty) return MR_OK;
+    if (ctx->copies_pending) {
+        CU(cudaEventRecord(ctx->ev_copy, ctx->copy_stream));
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));
+        ctx->copies_pending = false;
+    }
+    const bool remap_only = ctx->remap_upto && ctx->staged_since_map == 0 && ctx->ngaps == 0;
+    uint64_t end;
+    if (remap_only) {
+        end = ctx->remap_upto * SEG; // resident splits, already padded: map exactly what was mapped before
+    } else {
+        // pad the tail with spaces up to a whole segment plus the look-ahead window
+        end = round_up(std::max<uint64_t>(ctx->used, 1), SEG);
+        if (ctx->gaps_pending) { CU(cudaEventSynchronize(ctx->ev_gaps)); ctx->gaps_pending = false; }
+        if (ctx->ngaps == MAX_GAPS) { int rc = flush_gaps(ctx); if (rc) return rc; }
+        ctx->h_gaps[ctx->ngaps].off = ctx->used;
+        ctx->h_gaps[ctx->ngaps].len = end + TAIL_GUARD - ctx->used;
+        ctx->ngaps++;
+        { int rc = flush_gaps(ctx); if (rc) return rc; }
+    }
+    MapParams p;
+    p.arena = ctx->d_arena;
+    p.first_seg = ctx->mapped_segs;
+    p.nseg = end / SEG - ctx->mapped_segs;
+    p.gtab = ctx->d_gtab;
+    p.gmask = (uint32_t)(ctx->slots - 1);
+    p.max_token = MR_MAX_TOKEN_BYTES;
+    p.tokens = &ctx->d_ctl->tokens;
+    p.err = &ctx->d_ctl->err;
+    if (p.nseg) {
+        cudaError_t e;
+        switch (ctx->map_variant) {
+        case 1: e = launch_map<16, 12>(ctx, p); break;
+        case 2: e = launch_map<16, 13>(ctx, p); break;
+        case 3: e = launch_map<32, 12>(ctx, p); break;
+        default: e = launch_map<32, 13>(ctx, p); break;
+        }
+        if (e != cudaSuccess) return fail(ctx, MR_ERR_CUDA, "map kernel launch: %s", cudaGetErrorString(e));
+    }
+    ctx->mapped_segs = end / SEG;
+    // later splits start in fresh segments, past the guard this round's fill kernel writes
+    if (!remap_only) ctx->used = end + TAIL_GUARD;
+    ctx->map_dirty = false;
+    ctx->staged_since_map = 0;
+    return MR_OK;
+}
+
 int mr_map_finish(mr_ctx *ctx)
 {
     if (!ctx) return MR_ERR_INVALID;
@@ -466,33 +591,7 @@ int mr_map_finish(mr_ctx *ctx)
         return fail(ctx, MR_ERR_INVALID, "mr_map_finish: job already reduced; call mr_job_begin");
     CU(cudaSetDevice(ctx->cfg.device));
     if (!ctx->map_timed) CU(cudaEventRecord(ctx->ev_map0, ctx->stream));
-    if (ctx->map_dirty) {
-        // pad the tail with spaces up to a whole segment plus the look-ahead window
-        uint64_t end = round_up(std::max<uint64_t>(ctx->used, 1), SEG);
-        CU(cudaMemsetAsync(ctx->d_arena + ctx->used, 0x20, end + SEG_AHEAD + 64 - ctx->used, ctx->stream));
-        MapParams p;
-        p.arena = ctx->d_arena;
-        p.first_seg = ctx->mapped_segs;
-        p.nseg = end / SEG - ctx->mapped_segs;
-        p.gtab = ctx->d_gtab;
-        p.gmask = (uint32_t)(ctx->slots - 1);
-        p.max_token = MR_MAX_TOKEN_BYTES;
-        p.tokens = &ctx->d_ctl->tokens;
-        p.err = &ctx->d_ctl->err;
-        if (p.nseg) {
-            cudaError_t e;
-            switch (ctx->map_variant) {
-            case 1: e = launch_map<16, 12>(ctx, p); break;
-            case 2: e = launch_map<16, 13>(ctx, p); break;
-            case 3: e = launch_map<32, 12>(ctx, p); break;
-            default: e = launch_map<32, 13>(ctx, p); break;
-            }
-            if (e != cudaSuccess) return fail(ctx, MR_ERR_CUDA, "map kernel launch: %s", cudaGetErrorString(e));
-        }
-        ctx->mapped_segs = end / SEG;
-        ctx->used = end; // later splits start in fresh segments
-        ctx->map_dirty = false;
-    }
+    { int rc = run_map_round(ctx); if (rc) return rc; }
     CU(cudaEventRecord(ctx->ev_map1, ctx->stream));
     ctx->map_timed = true;
     ctx->state = mr_ctx::MAPPED;
