@@ -181,13 +181,17 @@ def main():
         for i, t in enumerate(pinned):
             ctx.map_split_ptr(i, t.data_ptr(), t.numel())
 
+    shuffle_slot = [None]   # None: exact-size shuffle (one host sync); then fixed slots, no sync
+
     def job(resident):
         ctx.job_begin(keep_input=resident)
         if not resident:
             stage_all()
         ctx.map_finish()
         if world > 1:
-            parallel.shuffle(ctx)
+            biggest = parallel.shuffle(ctx, slot_bytes=shuffle_slot[0])
+            if shuffle_slot[0] is None:
+                shuffle_slot[0] = parallel.slot_for(biggest)
         ctx.reduce_all()
 
     def barrier():
@@ -223,7 +227,7 @@ def main():
         ctx.map_finish()
         ev[s][1].record()
         if world > 1:
-            parallel.shuffle(ctx)
+            parallel.shuffle(ctx, slot_bytes=shuffle_slot[0])
         ctx.reduce_all()
         ev[s][2].record()
         launches += int(ctx.stats().launches)
@@ -312,7 +316,7 @@ def main():
         "config": {"workload": f"config2 x{args.scale}: synthetic Europarl-shaped word count, {nper} splits/rank, R={R}",
                    "tokens": tokens_total, "input_bytes": bytes_total, "distinct_keys": rows_total,
                    "partitions": R, "seed": hex(SEED), "parallelism": f"splits sharded over {world} rank(s), "
-                   "owner = partition mod ranks, one all-to-all",
+                   "owner = partition mod ranks, one all-to-all" + (f" (fixed {shuffle_slot[0]}-byte slots)" if world > 1 else ""),
                    "l2": "input per rank (294 MB) is larger than L2 (126 MB); no flush between steps"},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }))

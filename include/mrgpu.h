@@ -164,6 +164,13 @@ typedef struct mr_shuffle_plan {
 } mr_shuffle_plan;
 int mr_shuffle_count(mr_ctx *ctx, const uint64_t **dev_counts);
 int mr_shuffle_pack(mr_ctx *ctx, const uint64_t *counts, mr_shuffle_plan *plan);
+/* Fixed-slot variant with no host synchronisation: every destination's segment goes into a slot
+ * of slot_bytes (multiple of 16) led by a 16-byte header {records, long-key bytes}; the caller runs
+ * a plain equal-split all-to-all of world_size x slot_bytes into mr_shuffle_recv_buffer and calls
+ * mr_shuffle_import_fixed.  A segment that does not fit is reported by mr_job_sync as
+ * MR_ERR_OVERFLOW (rerun the job with a larger slot or the exact-size path above). */
+int mr_shuffle_pack_fixed(mr_ctx *ctx, uint64_t slot_bytes, const uint8_t **send_base);
+int mr_shuffle_import_fixed(mr_ctx *ctx, uint64_t slot_bytes);
 /* Reserve room for `bytes` incoming bytes; returns the device pointer to receive into. */
 int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr);
 /* recv_off: host array [world_size+1] of byte offsets per source inside the receive

@@ -21,6 +21,7 @@ EXPORTS = (
     "mr_map_split", "mr_map_split_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
     "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
+    "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
     "mr_stats_get", "mr_partition_of", "mr_count_tokens_static",
 )
 
@@ -102,6 +103,8 @@ def load(build_if_missing=True):
     L.mr_result_release.restype = None
     L.mr_shuffle_count.argtypes = [vp, C.POINTER(vp)]
     L.mr_shuffle_pack.argtypes = [vp, C.POINTER(u64), C.POINTER(ShufflePlan)]
+    L.mr_shuffle_pack_fixed.argtypes = [vp, u64, C.POINTER(vp)]
+    L.mr_shuffle_import_fixed.argtypes = [vp, u64]
     L.mr_shuffle_recv_buffer.argtypes = [vp, u64, C.POINTER(vp)]
     L.mr_shuffle_import.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
@@ -231,6 +234,14 @@ class Context:
         off = np.array([plan.send_off[i] for i in range(W + 1)], dtype=np.uint64)
         nrec = np.array([plan.send_nrec[i] for i in range(W)], dtype=np.uint64)
         return plan.send_base, off, nrec
+
+    def shuffle_pack_fixed(self, slot_bytes):
+        p = C.c_void_p()
+        self._ck(self._L.mr_shuffle_pack_fixed(self._h, slot_bytes, C.byref(p)))
+        return p.value
+
+    def shuffle_import_fixed(self, slot_bytes):
+        self._ck(self._L.mr_shuffle_import_fixed(self._h, slot_bytes))
 
     def shuffle_recv_buffer(self, nbytes):
         p = C.c_void_p()

@@ -53,6 +53,7 @@ enum : uint32_t {
     ERR_TABLE_FULL = 1u,
     ERR_TOKEN_TOO_LONG = 2u,
     ERR_KEYS_FULL = 4u,
+    ERR_SHUFFLE_FULL = 8u,
 };
 
 // ---------------------------------------------------------------- whitespace

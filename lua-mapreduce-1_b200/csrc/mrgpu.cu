@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
 {
     __shared__ unsigned int s_rec[MAX_WORLD];
     __shared__ unsigned long long s_bytes[MAX_WORLD], s_rec_base[MAX_WORLD], s_byte_base[MAX_WORLD];
+    if (ctl->err & ERR_SHUFFLE_FULL) return; // a segment does not fit its slot: reported by the host
     const uint64_t n = ctl->n;
     const uint64_t chunk = (n + gridDim.x - 1) / gridDim.x;
     const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
@@ -127,6 +128,62 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
         ((unsigned long long *)seg)[3 * r] = k.k0;
         ((unsigned long long *)seg)[3 * r + 1] = k.k1;
         ((unsigned long long *)seg)[3 * r + 2] = ent.cnt(i);
+    }
+}
+
+// fixed-slot shuffle: every destination's segment sits in a slot of slot_bytes, led by a
+// 16-byte header {records, long-key bytes}; sizes never visit the host
+__global__ void export_header_kernel(uint8_t *send, uint32_t world, unsigned long long slot_bytes,
+                                     const unsigned long long *nrec, const unsigned long long *nbytes,
+                                     unsigned long long *seg_off, Ctl *ctl)
+{
+    const uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= world) return;
+    seg_off[d] = (unsigned long long)d * slot_bytes + 16;
+    unsigned long long *hdr = (unsigned long long *)(send + (unsigned long long)d * slot_bytes);
+    if (16 + nrec[d] * REC_BYTES + nbytes[d] > slot_bytes) {
+        atomicOr(&ctl->err, ERR_SHUFFLE_FULL);
+        hdr[0] = 0; hdr[1] = 0;
+    } else {
+        hdr[0] = nrec[d]; hdr[1] = nbytes[d];
+    }
+}
+
+// received slots -> entries (all sources in one launch); sets ctl->n
+constexpr uint32_t IMPORT_CHUNKS = 32;
+__global__ void __launch_bounds__(256) import_fixed_kernel(const uint8_t *recv, uint32_t world,
+                                                           unsigned long long slot_bytes, EntryArrays ent,
+                                                           unsigned long long max_keys, Ctl *ctl)
+{
+    __shared__ unsigned long long s_base, s_n, s_total;
+    const uint32_t src = blockIdx.x / IMPORT_CHUNKS, chunk = blockIdx.x % IMPORT_CHUNKS;
+    if (threadIdx.x == 0) {
+        unsigned long long base = 0, total = 0, mine = 0;
+        for (uint32_t q = 0; q < world; ++q) {
+            const unsigned long long *hdr = (const unsigned long long *)(recv + (unsigned long long)q * slot_bytes);
+            unsigned long long n = hdr[0], b = hdr[1];
+            if (16 + n * REC_BYTES + b > slot_bytes) { n = 0; atomicOr(&ctl->err, ERR_SHUFFLE_FULL); }
+            if (q < src) base += n;
+            if (q == src) mine = n;
+            total += n;
+        }
+        if (total > max_keys) { atomicOr(&ctl->err, ERR_KEYS_FULL); total = max_keys; }
+        s_base = base; s_n = mine; s_total = total;
+        if (blockIdx.x == 0) ctl->n = total;
+    }
+    __syncthreads();
+    const unsigned long long n = s_n, base = s_base;
+    const unsigned long long seg = (unsigned long long)src * slot_bytes + 16;
+    const unsigned long long *rec = (const unsigned long long *)(recv + seg);
+    const unsigned long long bytes_at = seg + n * REC_BYTES;
+    const unsigned long long per = (n + IMPORT_CHUNKS - 1) / IMPORT_CHUNKS;
+    const unsigned long long lo = per * chunk, hi = lo + per < n ? lo + per : n;
+    for (unsigned long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        if (base + i >= s_total) break;
+        Key k; k.k0 = rec[3 * i]; k.k1 = rec[3 * i + 1];
+        if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k), (uint32_t)k.k1);
+        GEntry ge; ge.k0 = k.k0; ge.k1 = k.k1; ge.cnt = rec[3 * i + 2]; ge.pad = 0;
+        ent.e[base + i] = ge;
     }
 }
 
@@ -675,6 +732,8 @@ int check_device_err(mr_ctx *ctx, unsigned err)
     if (err & ERR_TABLE_FULL)
         return fail(ctx, MR_ERR_OVERFLOW, "hash table full (%llu slots): raise table_slots / max_keys",
                     (unsigned long long)ctx->slots);
+    if (err & ERR_SHUFFLE_FULL)
+        return fail(ctx, MR_ERR_OVERFLOW, "a shuffle segment does not fit the fixed slot: use a larger slot_bytes or the exact-size path");
     if (err & ERR_KEYS_FULL)
         return fail(ctx, MR_ERR_NOMEM, "more distinct keys (or key bytes) than max_keys=%llu allows",
                     (unsigned long long)ctx->max_keys);
@@ -894,6 +953,56 @@ int mr_shuffle_pack(mr_ctx *ctx, const uint64_t *counts, mr_shuffle_plan *plan)
     plan->send_base = ctx->d_send;
     plan->send_off = ctx->send_off.data();
     plan->send_nrec = ctx->send_nrec.data();
+    return MR_OK;
+}
+
+int mr_shuffle_pack_fixed(mr_ctx *ctx, uint64_t slot_bytes, const uint8_t **send_base)
+{
+    if (!ctx || !send_base) return MR_ERR_INVALID;
+    if (slot_bytes < 64 || slot_bytes % 16) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_pack_fixed: slot_bytes must be a multiple of 16, >= 64");
+    if (!ctx->shuffle_counted) { const uint64_t *dc; int rc = mr_shuffle_count(ctx, &dc); if (rc) return rc; }
+    if (ctx->imported) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_pack_fixed: already imported");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    unsigned long long *nrec = ctx->d_shuf, *nbytes = ctx->d_shuf + W, *rec_cur = ctx->d_shuf + 2 * W,
+                       *byte_cur = ctx->d_shuf + 3 * W, *seg_off = ctx->d_shuf + 4 * W;
+    const uint64_t total = (uint64_t)W * slot_bytes;
+    if (total + 64 > ctx->send_cap) {
+        CU(cudaStreamSynchronize(s));
+        if (ctx->d_send) CU(cudaFree(ctx->d_send));
+        ctx->d_send = nullptr;
+        ctx->send_cap = total + 4096;
+        CU(dmalloc(&ctx->d_send, ctx->send_cap));
+    }
+    export_header_kernel<<<(W + 255) / 256, 256, 0, s>>>(ctx->d_send, W, slot_bytes, nrec, nbytes, seg_off, ctx->d_ctl);
+    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
+    export_scatter_kernel<<<g, 256, 0, s>>>(ctx->ent, ctx->bytes_base, W, ctx->d_send, seg_off, nrec, rec_cur,
+                                            byte_cur, ctx->d_ctl);
+    ctx->stats.launches += 2;
+    CU(cudaGetLastError());
+    *send_base = ctx->d_send;
+    return MR_OK;
+}
+
+int mr_shuffle_import_fixed(mr_ctx *ctx, uint64_t slot_bytes)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::MAPPED) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import_fixed: call after mr_shuffle_pack_fixed");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    if ((uint64_t)W * slot_bytes + 256 > ctx->recv_cap) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import_fixed: receive buffer smaller than world_size slots");
+    CU(cudaMemsetAsync(&ctx->d_ctl->or_lo, 0, offsetof(Ctl, err) - offsetof(Ctl, or_lo), s));
+    CU(cudaMemsetAsync(&ctx->d_ctl->n_tie, 0, offsetof(Ctl, tokens) - offsetof(Ctl, n_tie), s));
+    ctl_init_kernel<<<1, 1, 0, s>>>(ctx->d_ctl);
+    import_fixed_kernel<<<W * IMPORT_CHUNKS, 256, 0, s>>>(ctx->d_recv, W, slot_bytes, ctx->ent, ctx->max_keys, ctx->d_ctl);
+    ctx->bytes_base = ctx->d_recv;
+    partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+    ctx->stats.launches += 3;
+    CU(cudaGetLastError());
+    ctx->imported = true;
     return MR_OK;
 }
 

@@ -82,10 +82,23 @@ def exchange_segments(send, send_off, recv, recv_off, group=None):
     return recv
 
 
-def shuffle(ctx, group=None):
-    """count -> gather -> pack -> all-to-all -> import on a _native.Context (GPU ranks)."""
+def shuffle(ctx, group=None, slot_bytes=None):
+    """The shuffle of one job on a _native.Context (GPU ranks).
+
+    slot_bytes=None: exact sizes -- count -> gather (one host sync) -> pack -> all-to-all -> import.
+        Returns the largest segment any rank sends to any rank, which a caller running the same
+        job shape again can turn into a slot size.
+    slot_bytes=N:    fixed slots, sizes in device-side headers, equal-split all-to-all, no host
+        synchronisation at all; a segment larger than N surfaces as MR_ERR_OVERFLOW at job_sync."""
     dev = torch.device("cuda", torch.cuda.current_device())
     W, rank = ctx.world_size, ctx.rank
+    if slot_bytes:
+        total = W * int(slot_bytes)
+        send = device_bytes(ctx.shuffle_pack_fixed(int(slot_bytes)), total, dev)
+        recv = device_bytes(ctx.shuffle_recv_buffer(total), total, dev)
+        dist.all_to_all_single(recv, send, group=group)
+        ctx.shuffle_import_fixed(int(slot_bytes))
+        return int(slot_bytes)
     counts = device_i64(ctx.shuffle_count(), 2 * W, dev)
     matrix = gather_counts(counts, group)
     send_off, recv_off, recv_nrec = plan_from_counts(matrix, rank)
@@ -95,4 +108,9 @@ def shuffle(ctx, group=None):
     recv = device_bytes(ctx.shuffle_recv_buffer(int(recv_off[-1])), int(recv_off[-1]), dev)
     exchange_segments(send, send_off, recv, recv_off, group)
     ctx.shuffle_import(recv_off.astype(np.uint64), recv_nrec.astype(np.uint64))
-    return int(send_off[-1]), int(recv_off[-1])
+    return int(segment_bytes(matrix[:, :W], matrix[:, W:]).max())
+
+
+def slot_for(max_segment_bytes, headroom=1.25):
+    """A slot size for the fixed-slot shuffle from the largest exact segment seen (header included)."""
+    return (int(max_segment_bytes * headroom) + 16 + 4095) // 4096 * 4096

@@ -29,14 +29,26 @@ def main():
         want = O.run_staged(splits, R, 4)
         ctx = _native.Context(R, 1 << 24, max_keys=1 << 19, device=local_rank, stream=stream.cuda_stream,
                               world_size=world, rank=rank)
-        for it in range(2):                      # second pass re-uses the resident splits (keep_input)
+        slot = None
+        for it in range(3):                      # later passes re-use the resident splits (keep_input)
             if it == 0:
                 for i in parallel.shard_splits(len(splits), world, rank):
                     ctx.map_split(i, splits[i])
             else:
                 ctx.job_begin(keep_input=True)
             ctx.map_finish()
-            sent, received = parallel.shuffle(ctx)
+            if it < 2:                           # exact sizes first, then fixed slots (no host sync)
+                biggest = parallel.shuffle(ctx, slot_bytes=slot)
+                slot = parallel.slot_for(biggest)
+            else:                                # a slot that cannot hold the segments must be reported
+                parallel.shuffle(ctx, slot_bytes=64)
+                ctx.reduce_all()
+                try:
+                    ctx.job_sync()
+                    raise AssertionError("overflowing shuffle slot was not reported")
+                except _native.NativeError as e:
+                    assert e.code == _native.MR_ERR_OVERFLOW, e
+                continue
             ctx.reduce_all()
             got = ctx.rows()
             owned = np.array([parallel.owner_of_partition(int(p), world) == rank for p in want.part], dtype=bool)
