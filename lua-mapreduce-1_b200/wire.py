@@ -1,0 +1,160 @@
+"""The reference's text wire format for intermediate runs and results.
+
+Every run / result file is a sequence of Lua chunks, one per line:
+
+    return <key>,{<v1>,<v2>,...}\\n           job.lua:208-214 (runs), job.lua:272-273 (results)
+
+with `escape` (utils.lua:100-112): numbers through tostring (= "%.14g" in Lua 5.2), strings
+through string.format("%q") with backslash-newline rewritten to \\n; values through
+serialize_table_ipairs (utils.lua:114-120).  Files are named
+`<path>/map_results.P<part>.M<mapper>` (job.lua:208-221) and `result.P<zero-padded part>`
+(server.lua:313-321).  Writing rows in this format lets the unmodified server_final
+(server.lua:346-385: sort file names, load() every line) and finalfn consume GPU results, and
+parsing it lets GPU reducers consume runs written by reference mappers.
+Host-side text formatting only; nothing here is on the device data path.
+"""
+import os
+import re
+
+
+def lua_number(v):
+    """Lua 5.2 tostring(number): LUA_NUMBER_FMT = "%.14g" (integers print without a point)."""
+    return "%.14g" % v
+
+
+def lua_quote(s: bytes) -> bytes:
+    """string.format("%q", s) of Lua 5.2 (lstrlib.c addquoted) followed by escape()'s gsub."""
+    out = bytearray(b'"')
+    n = len(s)
+    for i, c in enumerate(s):
+        if c in (0x22, 0x5C):                      # " and \ : backslash + the character
+            out += b"\\" + bytes([c])
+        elif c == 0x0A:                            # %q gives backslash-newline; escape() makes it \n
+            out += b"\\n"
+        elif c == 0 or c < 0x20 or c == 0x7F:      # '\0' or iscntrl in the C locale
+            nxt_digit = i + 1 < n and 0x30 <= s[i + 1] <= 0x39
+            out += (b"\\%03d" if nxt_digit else b"\\%d") % c
+        else:
+            out.append(c)
+    out += b'"'
+    return bytes(out)
+
+
+def escape(v) -> bytes:
+    """utils.lua:100-112."""
+    if isinstance(v, (int, float)) and not isinstance(v, bool):
+        return lua_number(v).encode()
+    if isinstance(v, str):
+        v = v.encode("latin-1")
+    return lua_quote(bytes(v))
+
+
+def serialize_table_ipairs(values) -> bytes:
+    """utils.lua:114-120."""
+    return b"{" + b",".join(escape(v) for v in values) + b"}"
+
+
+def format_line(key, values) -> bytes:
+    return b"return " + escape(key) + b"," + serialize_table_ipairs(values) + b"\n"
+
+
+_ESC = {ord("a"): 7, ord("b"): 8, ord("f"): 12, ord("n"): 10, ord("r"): 13, ord("t"): 9, ord("v"): 11,
+        ord("\\"): 0x5C, ord('"'): 0x22, ord("'"): 0x27, 10: 10}
+
+
+def _parse_string(b, i):
+    assert b[i] == 0x22
+    out = bytearray()
+    i += 1
+    while b[i] != 0x22:
+        c = b[i]
+        if c != 0x5C:
+            out.append(c)
+            i += 1
+            continue
+        c = b[i + 1]
+        if 0x30 <= c <= 0x39:                      # \ddd, up to three decimal digits
+            j = i + 1
+            while j < i + 4 and j < len(b) and 0x30 <= b[j] <= 0x39:
+                j += 1
+            out.append(int(b[i + 1:j]))
+            i = j
+        elif c == ord("x"):
+            out.append(int(b[i + 2:i + 4], 16))
+            i += 4
+        else:
+            out.append(_ESC[c])
+            i += 2
+    return bytes(out), i + 1
+
+
+_NUM = re.compile(rb"-?(?:\d+\.?\d*(?:[eE][-+]?\d+)?|\.\d+)")
+
+
+def _parse_value(b, i):
+    if b[i] == 0x22:
+        return _parse_string(b, i)
+    m = _NUM.match(b, i)
+    assert m, f"cannot parse value at {i}: {b[i:i + 20]!r}"
+    t = m.group()
+    v = float(t)
+    return (int(v) if v.is_integer() and abs(v) < 2 ** 53 else v), m.end()
+
+
+def parse_line(line: bytes):
+    """Inverse of format_line = what load(line)() yields in utils.lua:222-224 / server.lua:381."""
+    b = line.rstrip(b"\n")
+    assert b.startswith(b"return "), b[:20]
+    key, i = _parse_value(b, 7)
+    assert b[i:i + 2] == b",{", b[i:i + 8]
+    i += 2
+    values = []
+    while b[i] != 0x7D:
+        v, i = _parse_value(b, i)
+        values.append(v)
+        if b[i] == 0x2C:
+            i += 1
+    return key, values
+
+
+def count_digits(n):
+    """server.lua count_digits: decimal digits of the largest partition id."""
+    return max(1, len(str(int(n))))
+
+
+def result_name(result_ns, part, max_part):
+    """server.lua:313-321."""
+    return "%s.P%0*d" % (result_ns, count_digits(max_part), part)
+
+
+def map_result_name(map_results_ns, part, mapper_key):
+    """job.lua:208-209."""
+    return "%s.P%d.M%s" % (map_results_ns, part, mapper_key)
+
+
+def write_results(rows, directory, result_ns="result"):
+    """Writes one `result.P<part>` file per non-empty partition (server.lua:297-324: partitions that
+    received no key do not exist), keys ascending -- the `shared` storage layout of fs.lua.
+    rows: _native.Rows.  Returns the file names in server_final's order."""
+    os.makedirs(directory, exist_ok=True)
+    parts = [p for p in range(len(rows.part_begin) - 1) if rows.part_begin[p + 1] > rows.part_begin[p]]
+    if not parts:
+        return []
+    kb = rows.key_bytes.tobytes()
+    names = []
+    for p in parts:
+        name = result_name(result_ns, p, parts[-1])
+        with open(os.path.join(directory, name), "wb") as f:
+            for i in range(int(rows.part_begin[p]), int(rows.part_begin[p + 1])):
+                f.write(format_line(kb[int(rows.key_off[i]):int(rows.key_off[i + 1])], [int(rows.count[i])]))
+        names.append(name)
+    return sorted(names)
+
+
+def read_pairs(directory, names):
+    """server_final's pair iterator (server.lua:358-383) over files in name order."""
+    for name in sorted(names):
+        with open(os.path.join(directory, name), "rb") as f:
+            for line in f.read().split(b"\n"):
+                if line:
+                    yield parse_line(line)

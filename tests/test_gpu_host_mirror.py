@@ -1,0 +1,74 @@
+"""The reference-shaped host API (server.configure/loop, worker.execute, task modules) on a GPU,
+and the reference's result wire format written from GPU rows."""
+import threading
+
+import numpy as np
+import pytest
+
+from lua_mapreduce_1_b200 import _native, corpus, mapreduce, wire
+from lua_mapreduce_1_b200.examples import WordCount
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def test_wordcount_through_server_and_worker(tmp_path, capsys):
+    splits, _ = corpus.generate(lines=[700, 650, 1, 900])
+    splits[2] = np.frombuffer(corpus.TORTURE, dtype=np.uint8)
+    paths = []
+    for i, s in enumerate(splits):
+        p = tmp_path / f"split{i}.txt"
+        p.write_bytes(s.tobytes())
+        paths.append(str(p))
+    want = O.run_staged(splits, 15, 2)
+
+    seen = []
+
+    class Final:                              # finalfn.lua:3-8, collecting instead of printing
+        init = staticmethod(lambda arg=None: None)
+
+        @staticmethod
+        def finalfn(pairs_iterator):
+            for key, values in pairs_iterator:
+                seen.append((key, values[0]))
+            return True
+
+    s = mapreduce.server.new("localhost", "wordcount-gpu")
+    s.configure({"taskfn": WordCount, "mapfn": WordCount, "partitionfn": WordCount, "reducefn": WordCount,
+                 "combinerfn": WordCount, "finalfn": Final, "init_args": {"files": paths, "num_reducers": 15}})
+    w = mapreduce.worker.new("localhost", "wordcount-gpu").configure({"max_iter": 2000, "arena_bytes": 1 << 24,
+                                                                       "max_keys": 1 << 18})
+    err = []
+    t = threading.Thread(target=lambda: err.append(None) if w.execute() is not None else err.append("x"))
+    t.start()
+    stats = s.loop()
+    t.join(60)
+    assert not t.is_alive()
+    # server_final order: partitions ascending, keys ascending (server.lua:365, utils.lua:214)
+    assert seen == list(zip(want.keys(), (int(c) for c in want.count)))
+    assert stats["map_jobs"] == 4 and stats["failed_map_jobs"] == 0
+    assert stats["red_jobs"] == len(set(want.part.tolist()))          # no job for an empty partition
+    # the module's own partitionfn (the semantic definition) agrees with the device partition ids
+    for p, k in list(zip(want.part, want.keys()))[::97]:
+        assert WordCount.partitionfn(k) == int(p)
+    w.ctx.close()
+
+
+def test_results_in_the_reference_wire_format(tmp_path):
+    splits, _ = corpus.generate(lines=[500, 400])
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    ctx = _native.Context(15, 1 << 22, max_keys=1 << 17)
+    try:
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+        rows = ctx.rows()
+    finally:
+        ctx.close()
+    names = wire.write_results(rows, str(tmp_path), "result")
+    want = O.run_staged(splits, 15, 2)
+    parts = sorted(set(want.part.tolist()))
+    assert names == [wire.result_name("result", p, parts[-1]) for p in parts]
+    got = list(wire.read_pairs(str(tmp_path), names))                  # what server_final hands to finalfn
+    assert got == [(k, [int(c)]) for k, c in zip(want.keys(), want.count)]
+    first = (tmp_path / names[0]).read_bytes().split(b"\n")[0]
+    assert first.startswith(b'return "') and first.endswith(b"}")
