@@ -45,9 +45,9 @@ struct MapParams {
 
 // per-warp shared memory
 struct __align__(16) WarpSmem {
-    uint32_t stage[(SEG + SEG_AHEAD) / 4]; // 1056 B
-    uint32_t bitmap[SEG / 32 + 4];         // 33 used
-    uint16_t pos[SEG / 2];                 // token start positions (max one per 2 bytes)
+    uint32_t stage[(SEG + SEG_AHEAD) / 4]; // 1056 B: the segment + 32 look-ahead bytes
+    uint16_t list[SEG / 2];                // token entries (pos | len << 10): short tokens from the
+                                           // front, medium tokens from the back (max one per 2 bytes)
     Key gq[64];                            // keys waiting for the global table
     unsigned long long longq[32];          // arena offsets of 16+ byte tokens
 };
@@ -109,7 +109,8 @@ template <int WARPS, int LOG2_SLOTS>
 __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
 {
     using L = MapSmemLayout<LOG2_SLOTS>;
-    constexpr uint32_t SLOTS = L::SLOTS, BUCKETS = SLOTS / WAYS;
+    constexpr uint32_t SLOTS = L::SLOTS;
+    constexpr uint32_t LIST_LAST = SEG / 2 - 1;
     extern __shared__ __align__(16) uint8_t smem[];
     unsigned long long *tkeys = (unsigned long long *)smem;
     unsigned int *tcnt = (unsigned int *)(smem + L::keys_bytes);
@@ -125,119 +126,150 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
     __syncthreads();
 
     const uint32_t lt = lanemask_lt();
-    uint32_t nq = 0; // warp-uniform fill of gq
+    uint32_t nq = 0, nlong = 0; // warp-uniform fills of gq / longq
     unsigned long long my_tokens = 0;
     const uint64_t gwarp = (uint64_t)blockIdx.x * WARPS + warp, nwarps = (uint64_t)gridDim.x * WARPS;
 
     for (uint64_t s = gwarp; s < p.nseg; s += nwarps) {
         const uint64_t base = (p.first_seg + s) * SEG;
         const uint4 *src = (const uint4 *)(p.arena + base);
-        // ---- 1. load + stage + non-space mask
-        uint4 a = ld_stream(src + 2 * lane), b = ld_stream(src + 2 * lane + 1);
+        // ---- 1. load + stage + non-space mask of the lane's 32 bytes
+        const uint4 a = ld_stream(src + 2 * lane), b = ld_stream(src + 2 * lane + 1);
         uint4 ahead = make_uint4(0, 0, 0, 0);
         if (lane < SEG_AHEAD / 16) ahead = __ldg(src + SEG / 16 + lane);
         uint32_t prev_ns = 0; // is the byte before the segment a token byte?
-        if (base != 0) prev_ns = nonspace_nibble((uint32_t)__ldg(p.arena + base - 1)) & 1u;
+        if (base != 0) {
+            const uint32_t c = __ldg(p.arena + base - 1);
+            prev_ns = !(c == 0x20u || (c - 9u) < 5u);
+        }
         uint4 *st4 = (uint4 *)ws->stage;
         st4[2 * lane] = a;
         st4[2 * lane + 1] = b;
         if (lane < SEG_AHEAD / 16) st4[SEG / 16 + lane] = ahead;
-        uint32_t m = nonspace_nibble(a.x) | nonspace_nibble(a.y) << 4 | nonspace_nibble(a.z) << 8 |
-                     nonspace_nibble(a.w) << 12 | nonspace_nibble(b.x) << 16 |
-                     nonspace_nibble(b.y) << 20 | nonspace_nibble(b.z) << 24 |
-                     nonspace_nibble(b.w) << 28;
-        ws->bitmap[lane] = m;
-        if (lane < SEG_AHEAD / 16) {
-            uint32_t am = nonspace_nibble(ahead.x) | nonspace_nibble(ahead.y) << 4 |
-                          nonspace_nibble(ahead.z) << 8 | nonspace_nibble(ahead.w) << 12;
-            am <<= 16 * lane;
-            am |= __shfl_xor_sync(0x3u, am, 1);
-            if (lane == 0) ws->bitmap[32] = am;
-        }
-        // ---- 2. token starts, scan, compaction
+        const uint32_t m = nonspace_nibble(a.x) | nonspace_nibble(a.y) << 4 | nonspace_nibble(a.z) << 8 |
+                           nonspace_nibble(a.w) << 12 | nonspace_nibble(b.x) << 16 |
+                           nonspace_nibble(b.y) << 20 | nonspace_nibble(b.z) << 24 |
+                           nonspace_nibble(b.w) << 28;
+        __syncwarp();
+        // mask of the 32 look-ahead bytes: lanes 0..7 take one word each
+        uint32_t am = 0;
+        if (lane < 8) am = nonspace_nibble(ws->stage[SEG / 4 + lane]) << (4 * lane);
+        am |= __shfl_xor_sync(0xFFFFFFFFu, am, 1);
+        am |= __shfl_xor_sync(0xFFFFFFFFu, am, 2);
+        am |= __shfl_xor_sync(0xFFFFFFFFu, am, 4);
+        am = __shfl_sync(0xFFFFFFFFu, am, 0);
+        // ---- 2. token starts, lengths and classes from the masks
         uint32_t carry = __shfl_up_sync(0xFFFFFFFFu, m >> 31, 1);
         if (lane == 0) carry = prev_ns;
-        uint32_t starts = m & ~((m << 1) | carry);
-        uint32_t cnt = __popc(starts), incl = cnt;
+        uint32_t nxt = __shfl_down_sync(0xFFFFFFFFu, m, 1);
+        if (lane == 31) nxt = am;
+        const unsigned long long w = (unsigned long long)m | ((unsigned long long)nxt << 32);
+        const uint32_t starts = m & ~((m << 1) | carry);
+        // bit i of t8: bytes i..i+7 are all token bytes (length >= 8); t16: length >= 16
+        unsigned long long t = w & (w >> 1);
+        t &= t >> 2;
+        const unsigned long long t8 = t & (t >> 4);
+        const unsigned long long t16 = t8 & (t8 >> 8);
+        const uint32_t s_long = starts & (uint32_t)t16;
+        const uint32_t s_med = starts & (uint32_t)t8 & ~(uint32_t)t16;
+        const uint32_t s_short = starts & ~(uint32_t)t8;
+        const uint32_t packed = __popc(s_short) | (__popc(s_med) << 16);
+        uint32_t incl = packed;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
             if (lane >= d) incl += v;
         }
-        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-        uint32_t o = incl - cnt;
-        while (starts) {
-            uint32_t bit = __ffs((int)starts) - 1;
-            starts &= starts - 1;
-            ws->pos[o++] = (uint16_t)(lane * 32 + bit);
+        const uint32_t totals = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        const uint32_t n_short = totals & 0xFFFFu, n_med = totals >> 16;
+        uint32_t o_s = (incl - packed) & 0xFFFFu;
+        uint32_t o_m = LIST_LAST - ((incl - packed) >> 16);
+        uint32_t st = starts & ~s_long;
+        while (st) {
+            const uint32_t bit = __ffs((int)st) - 1;
+            st &= st - 1;
+            const uint32_t len = __ffs((int)~(uint32_t)(w >> bit)) - 1; // 1..15
+            const uint16_t e = (uint16_t)((lane * 32 + bit) | (len << 10));
+            if ((s_med >> bit) & 1u) ws->list[o_m--] = e;
+            else ws->list[o_s++] = e;
         }
-        my_tokens += cnt;
+        my_tokens += __popc(starts);
+        // tokens of 16+ bytes (rare): queue their arena offsets
+        uint32_t lb = __ballot_sync(0xFFFFFFFFu, s_long != 0);
+        while (lb) {
+            const int srcl = __ffs((int)lb) - 1;
+            lb &= lb - 1;
+            const uint32_t sl = __shfl_sync(0xFFFFFFFFu, s_long, srcl);
+            const uint32_t c = __popc(sl);
+            if (lane < c) ws->longq[nlong + lane] = base + srcl * 32 + __fns(sl, 0, lane + 1);
+            nlong += c;
+            __syncwarp();
+            if (nlong > 28) { drain_long(p, ws, nlong, lane); nlong = 0; __syncwarp(); }
+        }
         const bool can_insert = *(volatile unsigned int *)&tused < FILL_LIMIT; // warp-uniform
         uint32_t inserted = 0;
         __syncwarp();
-        // ---- 3. one token per lane
-        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+        // ---- 3a. short tokens (<= 7 bytes): one per lane, CTA table
+        for (uint32_t t0 = 0; t0 < n_short; t0 += 32) {
             const uint32_t j = t0 + lane;
-            bool to_global = false, is_long = false;
+            bool to_global = false;
             Key key;
             key.k0 = 0; key.k1 = 0;
-            uint32_t pos = 0;
-            if (j < total) {
-                pos = ws->pos[j];
-                const uint32_t w = pos >> 5, sh = pos & 31;
-                const uint32_t bits = __funnelshift_r(ws->bitmap[w], ws->bitmap[w + 1], sh);
-                const uint32_t len = (uint32_t)__ffs((int)~bits) - 1u; // 0xFFFFFFFF when 32+ bytes
-                if (len > INLINE_MAX) {
-                    is_long = true;
-                } else {
-                    const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
-                    const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2];
-                    uint32_t x3 = 0, x4 = 0;
-                    if (len > 7) { x3 = ws->stage[wi + 3]; x4 = ws->stage[wi + 4]; }
-                    const int n = (int)len;
-                    const uint32_t w0 = keep_low_bytes(__funnelshift_r(x0, x1, bs), n);
-                    const uint32_t w1 = keep_low_bytes(__funnelshift_r(x1, x2, bs), n - 4);
-                    const uint32_t w2 = keep_low_bytes(__funnelshift_r(x2, x3, bs), n - 8);
-                    const uint32_t w3 = keep_low_bytes(__funnelshift_r(x3, x4, bs), n - 12);
-                    key.k0 = (uint64_t)w0 | ((uint64_t)w1 << 32);
-                    key.k1 = (uint64_t)w2 | ((uint64_t)(w3 | (len << 24)) << 32);
-                    to_global = true;
-                    if (len <= 7) {
-                        const uint32_t skh = w1 | (len << 24);
-                        const unsigned long long sk = (uint64_t)w0 | ((uint64_t)skh << 32); // bytes + length
-                        const uint32_t bucket = (w0 * 0x9E3779B1u + skh * 0x85EBCA77u) >> (32 - (LOG2_SLOTS - 2));
-                        const uint32_t baddr = tkeys_s + bucket * (WAYS * 8);
-                        const ulonglong2 q0 = lds128(baddr);
-                        int way = q0.x == sk ? 0 : q0.y == sk ? 1 : -1;
-                        if (way < 0) {
-                            const ulonglong2 q1 = lds128(baddr + 16);
-                            way = q1.x == sk ? 2 : q1.y == sk ? 3 : -1;
-                            if (way < 0 && can_insert) {
-                                const int e = q0.x == 0 ? 0 : q0.y == 0 ? 1 : q1.x == 0 ? 2 : q1.y == 0 ? 3 : -1;
-                                if (e >= 0) {
-                                    const unsigned long long old = atomicCAS(&tkeys[bucket * WAYS + e], 0ull, sk);
-                                    if (old == 0) ++inserted;
-                                    if (old == 0 || old == sk) way = e;
-                                }
-                            }
-                        }
-                        if (way >= 0) {
-                            atomicAdd(&tcnt[bucket * WAYS + way], 1u);
-                            to_global = false;
+            if (j < n_short) {
+                const uint32_t e = ws->list[j];
+                const uint32_t pos = e & 1023u, len = e >> 10;
+                const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
+                const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2];
+                const uint32_t w0 = keep_low_bytes(__funnelshift_r(x0, x1, bs), (int)len);
+                const uint32_t skh = keep_low_bytes(__funnelshift_r(x1, x2, bs), (int)len - 4) | (len << 24);
+                const unsigned long long sk = (uint64_t)w0 | ((uint64_t)skh << 32); // bytes + length
+                const uint32_t bucket = (w0 * 0x9E3779B1u + skh * 0x85EBCA77u) >> (32 - (LOG2_SLOTS - 2));
+                const uint32_t baddr = tkeys_s + bucket * (WAYS * 8);
+                const ulonglong2 q0 = lds128(baddr);
+                int way = q0.x == sk ? 0 : q0.y == sk ? 1 : -1;
+                if (way < 0) {
+                    const ulonglong2 q1 = lds128(baddr + 16);
+                    way = q1.x == sk ? 2 : q1.y == sk ? 3 : -1;
+                    if (way < 0 && can_insert) {
+                        const int e2 = q0.x == 0 ? 0 : q0.y == 0 ? 1 : q1.x == 0 ? 2 : q1.y == 0 ? 3 : -1;
+                        if (e2 >= 0) {
+                            const unsigned long long old = atomicCAS(&tkeys[bucket * WAYS + e2], 0ull, sk);
+                            if (old == 0) ++inserted;
+                            if (old == 0 || old == sk) way = e2;
                         }
                     }
                 }
+                if (way >= 0) {
+                    atomicAdd(&tcnt[bucket * WAYS + way], 1u);
+                } else {
+                    to_global = true;
+                    key.k0 = sk & LOW56;
+                    key.k1 = sk & ~LOW56;
+                }
             }
-            // queue what the CTA table did not take
             const uint32_t gm = __ballot_sync(0xFFFFFFFFu, to_global);
             if (to_global) ws->gq[nq + __popc(gm & lt)] = key;
             nq += __popc(gm);
-            const uint32_t lm = __ballot_sync(0xFFFFFFFFu, is_long);
-            if (lm) { // rare: handle immediately, one token per lane
-                if (is_long) ws->longq[__popc(lm & lt)] = base + pos;
-                __syncwarp();
-                drain_long(p, ws, __popc(lm), lane);
+            __syncwarp();
+            if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
+        }
+        // ---- 3b. medium tokens (8..15 bytes): 128-bit inline key, straight to the global queue
+        for (uint32_t t0 = 0; t0 < n_med; t0 += 32) {
+            const uint32_t j = t0 + lane;
+            if (j < n_med) {
+                const uint32_t e = ws->list[LIST_LAST - j];
+                const uint32_t pos = e & 1023u, len = e >> 10;
+                const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
+                const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2],
+                               x3 = ws->stage[wi + 3], x4 = ws->stage[wi + 4];
+                Key key;
+                key.k0 = (uint64_t)__funnelshift_r(x0, x1, bs) | ((uint64_t)__funnelshift_r(x1, x2, bs) << 32);
+                const uint32_t w2 = keep_low_bytes(__funnelshift_r(x2, x3, bs), (int)len - 8);
+                const uint32_t w3 = keep_low_bytes(__funnelshift_r(x3, x4, bs), (int)len - 12) | (len << 24);
+                key.k1 = (uint64_t)w2 | ((uint64_t)w3 << 32);
+                ws->gq[nq + (j - t0)] = key;
             }
+            nq += min(32u, n_med - t0);
             __syncwarp();
             if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
         }
@@ -245,6 +277,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         __syncwarp();
     }
     drain_keys(p, ws, 0, nq, lane);
+    drain_long(p, ws, nlong, lane);
     for (int d = 16; d; d >>= 1) my_tokens += __shfl_xor_sync(0xFFFFFFFFu, my_tokens, d);
     if (lane == 0 && my_tokens) atomicAdd(p.tokens, my_tokens);
     __syncthreads();
@@ -258,7 +291,6 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             gtable_add(p.gtab, p.gmask, p.arena, k, tcnt[i], p.err);
         }
     }
-    (void)BUCKETS;
 }
 
 } // namespace mr
