@@ -42,9 +42,17 @@ enum mr_status {
 
 /* What the task module's `native` descriptor may name.  The Lua functions stay the
  * semantic definition; a module without a descriptor is simply not accelerated. */
-enum mr_map_kind { MR_MAP_TOKENIZE_WS = 0 };          /* examples/WordCount/mapfn.lua:3-9 */
+enum mr_map_kind {
+    MR_MAP_TOKENIZE_WS = 0, /* examples/WordCount/mapfn.lua:3-9: emit(word, 1) per whitespace-separated token */
+    MR_MAP_RECORDS_U32 = 1  /* a mapfn that emits (number key, number value) records: emit, job.lua:83-97 */
+};
 enum mr_reduce_kind { MR_REDUCE_SUM_U64 = 0 };        /* examples/WordCount/reducefn.lua:1-5 */
-enum mr_partition_kind { MR_PARTITION_FNV1_LUA52 = 0 }; /* examples/WordCount/partitionfn.lua:8-16 */
+enum mr_partition_kind {
+    MR_PARTITION_FNV1_LUA52 = 0, /* examples/WordCount/partitionfn.lua:8-16 (string keys) */
+    MR_PARTITION_MOD_U32 = 1     /* partitionfn(key) = key % NUM_REDUCERS (number keys; job.lua:203-207) */
+};
+/* Supported pairs: (TOKENIZE_WS, FNV1_LUA52) and (RECORDS_U32, MOD_U32).  Number keys are ordered
+ * numerically (Lua `<`, utils.lua:214) and come back in the rows as 4 big-endian bytes. */
 
 #define MR_MAX_TOKEN_BYTES ((1u << 26) - 1)
 
@@ -112,6 +120,13 @@ int mr_job_begin(mr_ctx *ctx, int keep_input);
 int mr_map_split(mr_ctx *ctx, uint64_t split_id, const void *bytes, uint64_t n);
 /* Same with bytes already in device memory (device->device copy). */
 int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, uint64_t n);
+
+/* Map job whose output is already (key, value) number records (MR_MAP_RECORDS_U32): what emit
+ * (job.lua:83-97) would receive from a mapfn that emits numbers, n records at a time.  The values of
+ * equal keys are summed (reducefn.lua:1-5).  Host pointers: host->device copy inside the call. */
+int mr_map_records(mr_ctx *ctx, uint64_t split_id, const uint32_t *keys, const uint32_t *values, uint64_t n);
+int mr_map_records_device(mr_ctx *ctx, uint64_t split_id, const uint32_t *dev_keys,
+                          const uint32_t *dev_values, uint64_t n);
 
 /* Runs tokenise + hash-combine over every split staged since the last
  * mr_map_finish, then the partitioner on the distinct keys: job.lua:182-215

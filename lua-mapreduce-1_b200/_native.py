@@ -11,14 +11,14 @@ import numpy as np
 from . import build as _build
 
 MR_OK, MR_ERR_INVALID, MR_ERR_CUDA, MR_ERR_NOMEM, MR_ERR_OVERFLOW, MR_ERR_UNSUPPORTED, MR_ERR_END = range(7)
-MR_MAP_TOKENIZE_WS = 0
+MR_MAP_TOKENIZE_WS, MR_MAP_RECORDS_U32 = 0, 1
 MR_REDUCE_SUM_U64 = 0
-MR_PARTITION_FNV1_LUA52 = 0
+MR_PARTITION_FNV1_LUA52, MR_PARTITION_MOD_U32 = 0, 1
 
 # every symbol include/mrgpu.h declares
 EXPORTS = (
     "mr_abi_version", "mr_ctx_create", "mr_ctx_destroy", "mr_last_error", "mr_job_begin",
-    "mr_map_split", "mr_map_split_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
+    "mr_map_split", "mr_map_split_device", "mr_map_records", "mr_map_records_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
     "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
     "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
@@ -92,6 +92,8 @@ def load(build_if_missing=True):
     L.mr_job_begin.argtypes = [vp, C.c_int]
     L.mr_map_split.argtypes = [vp, u64, vp, u64]
     L.mr_map_split_device.argtypes = [vp, u64, vp, u64]
+    L.mr_map_records.argtypes = [vp, u64, vp, vp, u64]
+    L.mr_map_records_device.argtypes = [vp, u64, vp, vp, u64]
     L.mr_map_finish.argtypes = [vp]
     L.mr_reduce_all.argtypes = [vp]
     L.mr_job_sync.argtypes = [vp, C.POINTER(JobInfo)]
@@ -131,15 +133,19 @@ class Rows:
         off = self.key_off
         return [kb[int(off[i]):int(off[i + 1])] for i in range(self.n)]
 
+    def keys_u32(self):
+        """Number keys of a MR_MAP_RECORDS_U32 job (4 big-endian bytes per row)."""
+        return np.frombuffer(self.key_bytes.tobytes(), dtype=">u4").astype(np.uint32)
+
 
 class Context:
     """One per worker process per GPU (include/mrgpu.h: mr_ctx)."""
 
     def __init__(self, num_reducers, arena_bytes, max_keys=0, table_slots=0, device=0, stream=None,
-                 world_size=1, rank=0):
+                 world_size=1, rank=0, map_kind=MR_MAP_TOKENIZE_WS, partition_kind=MR_PARTITION_FNV1_LUA52):
         self._L = load()
-        cfg = Config(C.sizeof(Config), device, num_reducers, MR_MAP_TOKENIZE_WS, MR_REDUCE_SUM_U64,
-                     MR_PARTITION_FNV1_LUA52, arena_bytes, max_keys, table_slots, stream, world_size, rank)
+        cfg = Config(C.sizeof(Config), device, num_reducers, map_kind, MR_REDUCE_SUM_U64,
+                     partition_kind, arena_bytes, max_keys, table_slots, stream, world_size, rank)
         h = C.c_void_p()
         rc = self._L.mr_ctx_create(C.byref(cfg), C.byref(h))
         if rc != MR_OK:
@@ -169,6 +175,17 @@ class Context:
     def map_split_ptr(self, split_id, ptr, n, device=False):
         fn = self._L.mr_map_split_device if device else self._L.mr_map_split
         self._ck(fn(self._h, split_id, ptr, n))
+
+    def map_records(self, split_id, keys, values):
+        """keys, values: uint32 numpy arrays of equal length (host memory)."""
+        k = np.ascontiguousarray(keys, dtype=np.uint32)
+        v = np.ascontiguousarray(values, dtype=np.uint32)
+        assert k.shape == v.shape and k.ndim == 1
+        self._ck(self._L.mr_map_records(self._h, split_id, k.ctypes.data, v.ctypes.data, k.size))
+
+    def map_records_ptr(self, split_id, keys_ptr, values_ptr, n, device=False):
+        fn = self._L.mr_map_records_device if device else self._L.mr_map_records
+        self._ck(fn(self._h, split_id, keys_ptr, values_ptr, n))
 
     def map_finish(self):
         self._ck(self._L.mr_map_finish(self._h))

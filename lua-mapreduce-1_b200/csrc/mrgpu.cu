@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "map_kernel.cuh"
+#include "records_kernel.cuh"
 #include "reduce_kernels.cuh"
 
 using namespace mr;
@@ -272,6 +273,9 @@ struct mr_ctx {
     bool copies_pending = false, copy_synced = false;
     uint64_t staged_since_map = 0, auto_map_bytes = 32ull << 20;
     uint64_t remap_upto = 0;  // keep_input: segments that hold the resident splits
+    struct RecSplit { uint64_t off_k, off_v, n; };
+    std::vector<RecSplit> rec_splits; // MR_MAP_RECORDS_U32: staged record batches
+    bool rec_remap = false;
     bool map_timed = false, red_timed = false;
     mr_stats stats{};
 
@@ -393,8 +397,9 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     if (cfg->struct_size != sizeof(mr_config))
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: struct_size %u != %zu", cfg->struct_size,
                     sizeof(mr_config));
-    if (cfg->map_kind != MR_MAP_TOKENIZE_WS || cfg->reduce_kind != MR_REDUCE_SUM_U64 ||
-        cfg->partition_kind != MR_PARTITION_FNV1_LUA52)
+    const bool text_job = cfg->map_kind == MR_MAP_TOKENIZE_WS && cfg->partition_kind == MR_PARTITION_FNV1_LUA52;
+    const bool rec_job = cfg->map_kind == MR_MAP_RECORDS_U32 && cfg->partition_kind == MR_PARTITION_MOD_U32;
+    if (!(text_job || rec_job) || cfg->reduce_kind != MR_REDUCE_SUM_U64)
         return fail(nullptr, MR_ERR_UNSUPPORTED, "mr_ctx_create: unsupported map/reduce/partition kind");
     if (cfg->num_reducers == 0 || cfg->num_reducers > (1u << 24))
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: num_reducers must be in 1..2^24");
@@ -497,11 +502,14 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
         ctx->copy_synced = false;
         ctx->staged_since_map = 0;
         ctx->remap_upto = 0;
+        ctx->rec_splits.clear();
+        ctx->rec_remap = false;
     } else {
         // keep the staged splits: the next mr_map_finish maps all of them again
         ctx->remap_upto = std::max(ctx->remap_upto, ctx->mapped_segs);
         ctx->mapped_segs = 0;
-        ctx->map_dirty = ctx->any_split;
+        ctx->map_dirty = ctx->any_split && ctx->cfg.map_kind == MR_MAP_TOKENIZE_WS;
+        ctx->rec_remap = !ctx->rec_splits.empty();
         ctx->staged_since_map = 0;
     }
     CU(cudaMemsetAsync(ctx->d_gtab, 0, ctx->slots * sizeof(GEntry), ctx->stream));
@@ -540,6 +548,8 @@ static int flush_gaps(mr_ctx *ctx)
 static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKind kind)
 {
     if (!ctx) return MR_ERR_INVALID;
+    if (ctx->cfg.map_kind != MR_MAP_TOKENIZE_WS)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_split: this context maps records, use mr_map_records");
     if (n && !bytes) return fail(ctx, MR_ERR_INVALID, "mr_map_split: null bytes");
     if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
         return fail(ctx, MR_ERR_INVALID, "mr_map_split: job already reduced; call mr_job_begin");
@@ -641,6 +651,82 @@ static int run_map_round(mr_ctx *ctx)
     return MR_OK;
 }
 
+static int launch_records(mr_ctx *ctx, const mr_ctx::RecSplit &r)
+{
+    if (!r.n) return MR_OK;
+    RecordsParams p;
+    p.keys = (const uint32_t *)(ctx->d_arena + r.off_k);
+    p.vals = (const uint32_t *)(ctx->d_arena + r.off_v);
+    p.n = r.n;
+    p.gtab = ctx->d_gtab;
+    p.gmask = (uint32_t)(ctx->slots - 1);
+    p.records = &ctx->d_ctl->tokens;
+    p.err = &ctx->d_ctl->err;
+    constexpr int LOG2 = 13;
+    const size_t smem = (size_t)(1u << LOG2) * 16;
+    CU(cudaFuncSetAttribute(map_records_kernel<LOG2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (r.n + 4095) / 4096);
+    map_records_kernel<LOG2><<<std::max(grid, 1u), 1024, smem, ctx->stream>>>(p);
+    ctx->stats.launches++;
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+static int stage_records(mr_ctx *ctx, const uint32_t *keys, const uint32_t *values, uint64_t n, cudaMemcpyKind kind)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (ctx->cfg.map_kind != MR_MAP_RECORDS_U32)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_records: this context maps text splits, use mr_map_split");
+    if (n && (!keys || !values)) return fail(ctx, MR_ERR_INVALID, "mr_map_records: null pointer");
+    if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_records: job already reduced; call mr_job_begin");
+    CU(cudaSetDevice(ctx->cfg.device));
+    mr_ctx::RecSplit r;
+    r.off_k = round_up(ctx->used, 16);
+    r.off_v = r.off_k + round_up(4 * n, 16);
+    r.n = n;
+    const uint64_t end = r.off_v + round_up(4 * n, 16);
+    if (end + SEG > ctx->arena_cap)
+        return fail(ctx, MR_ERR_NOMEM, "mr_map_records: arena full (%llu > %llu bytes)", (unsigned long long)end,
+                    (unsigned long long)ctx->arena_cap);
+    cudaStream_t cs = ctx->stream;
+    if (kind == cudaMemcpyHostToDevice) {
+        if (!ctx->copy_synced) {
+            CU(cudaEventRecord(ctx->ev_job, ctx->stream));
+            CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_job, 0));
+            ctx->copy_synced = true;
+        }
+        cs = ctx->copy_stream;
+        ctx->stats.h2d_bytes += 8 * n;
+    }
+    if (n) {
+        CU(cudaMemcpyAsync(ctx->d_arena + r.off_k, keys, 4 * n, kind, cs));
+        CU(cudaMemcpyAsync(ctx->d_arena + r.off_v, values, 4 * n, kind, cs));
+    }
+    if (kind == cudaMemcpyHostToDevice) {
+        CU(cudaEventRecord(ctx->ev_copy, ctx->copy_stream));
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));
+    }
+    ctx->used = end;
+    ctx->input_bytes += 8 * n;
+    ctx->any_split = true;
+    ctx->rec_splits.push_back(r);
+    return launch_records(ctx, r); // map + combine right away, overlapping the next batch's copy
+}
+
+int mr_map_records(mr_ctx *ctx, uint64_t split_id, const uint32_t *keys, const uint32_t *values, uint64_t n)
+{
+    (void)split_id;
+    return stage_records(ctx, keys, values, n, cudaMemcpyHostToDevice);
+}
+
+int mr_map_records_device(mr_ctx *ctx, uint64_t split_id, const uint32_t *dev_keys, const uint32_t *dev_values,
+                          uint64_t n)
+{
+    (void)split_id;
+    return stage_records(ctx, dev_keys, dev_values, n, cudaMemcpyDeviceToDevice);
+}
+
 int mr_map_finish(mr_ctx *ctx)
 {
     if (!ctx) return MR_ERR_INVALID;
@@ -648,6 +734,10 @@ int mr_map_finish(mr_ctx *ctx)
         return fail(ctx, MR_ERR_INVALID, "mr_map_finish: job already reduced; call mr_job_begin");
     CU(cudaSetDevice(ctx->cfg.device));
     if (!ctx->map_timed) CU(cudaEventRecord(ctx->ev_map0, ctx->stream));
+    if (ctx->rec_remap) { // keep_input on a records context: map the resident batches again
+        for (const auto &r : ctx->rec_splits) { int rc = launch_records(ctx, r); if (rc) return rc; }
+        ctx->rec_remap = false;
+    }
     { int rc = run_map_round(ctx); if (rc) return rc; }
     CU(cudaEventRecord(ctx->ev_map1, ctx->stream));
     ctx->map_timed = true;
@@ -664,7 +754,7 @@ int launch_compact(mr_ctx *ctx)
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
     compact_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->ent, ctx->max_keys, ctx->d_ctl);
     partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 2;
     CU(cudaGetLastError());
     return MR_OK;
@@ -999,7 +1089,7 @@ int mr_shuffle_import_fixed(mr_ctx *ctx, uint64_t slot_bytes)
     import_fixed_kernel<<<W * IMPORT_CHUNKS, 256, 0, s>>>(ctx->d_recv, W, slot_bytes, ctx->ent, ctx->max_keys, ctx->d_ctl);
     ctx->bytes_base = ctx->d_recv;
     partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 3;
     CU(cudaGetLastError());
     ctx->imported = true;
@@ -1049,7 +1139,7 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
     ctl_set_n_kernel<<<1, 1, 0, s>>>(ctx->d_ctl, base);
     ctx->bytes_base = ctx->d_recv;
     partition_entries_kernel<<<grid_for(std::max<uint64_t>(base, 1), 256, ctx->sm_count * 4), 256, 0, s>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+        ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 3;
     CU(cudaGetLastError());
     ctx->imported = true;

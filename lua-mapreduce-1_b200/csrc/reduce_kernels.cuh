@@ -171,8 +171,11 @@ __global__ void __launch_bounds__(256) compact_kernel(const GEntry *gt, uint64_t
 }
 
 // dense entries -> partition id + sort item (+ which key bits vary at all)
+// partition_kind 0: the WordCount partitioner (Lua 5.2 double FNV, partitionfn.lua:8-16);
+// partition_kind 1: `key % NUM_REDUCERS` on a number key carried as 4 big-endian bytes
 __global__ void __launch_bounds__(256) partition_entries_kernel(
-    const uint8_t *bytes, uint32_t num_reducers, EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl)
+    const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind, EntryArrays ent, SortItem *items,
+    uint64_t max_keys, Ctl *ctl)
 {
     uint32_t hi_or = 0, hi_and = ~0u;
     uint64_t lo_or = 0, lo_and = ~0ull;
@@ -181,7 +184,8 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
         Key key = ent.key(idx);
-        uint32_t part = partition_of_key(key, bytes, num_reducers);
+        uint32_t part = partition_kind == 1 ? __byte_perm((uint32_t)key.k0, 0, 0x0123) % num_reducers
+                                            : partition_of_key(key, bytes, num_reducers);
         uint64_t chunk = sort_chunk(key, bytes, 0);
         ent.e[idx].pad = part;
         SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;

@@ -36,9 +36,9 @@ MAX_WORKER_RETRIES = 3   # utils.lua:48
 DEFAULT_SLEEP = 0.01
 
 NATIVE_KINDS = {
-    "map": {"tokenize_ws": _native.MR_MAP_TOKENIZE_WS},
+    "map": {"tokenize_ws": _native.MR_MAP_TOKENIZE_WS, "records_u32": _native.MR_MAP_RECORDS_U32},
     "reduce": {"sum_u64": _native.MR_REDUCE_SUM_U64},
-    "partition": {"fnv1_lua52_double": _native.MR_PARTITION_FNV1_LUA52},
+    "partition": {"fnv1_lua52_double": _native.MR_PARTITION_FNV1_LUA52, "mod_u32": _native.MR_PARTITION_MOD_U32},
 }
 
 
@@ -295,11 +295,15 @@ class worker:
         mods = params["mods"]
         desc = self._native_config(mods)
         R = int(desc["num_reducers"])
-        if self.ctx is None or self.ctx.num_reducers != R:
+        kinds = (NATIVE_KINDS["map"][desc["map"]], NATIVE_KINDS["partition"][desc["partition"]])
+        if self.ctx is None or self.ctx.num_reducers != R or self.ctx_kinds != kinds:
             if self.ctx is not None:
                 self.ctx.close()
-            self.ctx = _native.Context(R, self.arena_bytes, self.max_keys, device=self.device)
+            self.ctx = _native.Context(R, self.arena_bytes, self.max_keys, device=self.device,
+                                       map_kind=kinds[0], partition_kind=kinds[1])
+            self.ctx_kinds = kinds
         ctx = self.ctx
+        records = kinds[0] == _native.MR_MAP_RECORDS_U32
         ctx.job_begin()
         # ---- map jobs (job.lua:166-227): stage every split this worker claims
         mine = []
@@ -314,7 +318,9 @@ class worker:
             t0, c0 = time.time(), time.process_time()
             try:
                 value = job["value"]
-                if isinstance(value, (bytes, bytearray, memoryview)) or hasattr(value, "ctypes"):
+                if records:     # the map job's value is a (keys, values) pair of uint32 arrays
+                    ctx.map_records(len(mine), value[0], value[1])
+                elif isinstance(value, (bytes, bytearray, memoryview)) or hasattr(value, "ctypes"):
                     ctx.map_split(len(mine), value)
                 else:   # mapfn.lua:4: the value names a file
                     with open(value, "rb") as f:
@@ -357,6 +363,8 @@ class worker:
             try:
                 p = job["value"]["partition"]
                 rows = list(ctx.partition_cursor(p))
+                if records:     # number keys travel as 4 big-endian bytes
+                    rows = [(int.from_bytes(k, "big"), c) for k, c in rows]
                 with b.lock:
                     b.results[job["value"]["result"]] = (lambda r=rows: iter(r))
                 self._mark(job, WRITTEN, written_time=time.time(), cpu_time=time.process_time() - c0,

@@ -495,6 +495,66 @@ mro_result *mro_run_staged(const uint8_t *const *splits, const uint64_t *lens, u
     return r;
 }
 
+/* ---------------------------------------------------------------- group-by sum on number keys */
+
+/* BASELINE config 5: a job whose mapfn emits (number key, number value) pairs, whose
+ * partitionfn is `key % NUM_REDUCERS` and whose reducer is the WordCount sum
+ * (reducefn.lua:1-5).  The framework treats it like any other job: emit groups values by key
+ * (job.lua:83-97), keys are ordered with Lua `<`, which on numbers is numeric (utils.lua:126,
+ * utils.lua:214), partitions ascending (server.lua:365).  Keys are carried as 4 big-endian bytes
+ * in the rows so that byte order equals numeric order. */
+typedef struct { uint32_t key; uint32_t used; uint64_t sum; } gb_slot;
+
+static int gb_cmp(const void *x, const void *y)
+{
+    const row *a = (const row *)x, *b = (const row *)y;
+    if (a->part != b->part) return a->part < b->part ? -1 : 1;
+    return memcmp(a->ptr, b->ptr, 4);
+}
+
+mro_result *mro_groupby_u32(const uint32_t *const *keys, const uint32_t *const *vals, const uint64_t *lens,
+                            uint32_t nsplits, uint32_t num_reducers)
+{
+    uint64_t cap = 1u << 16, used = 0, records = 0;
+    gb_slot *t = (gb_slot *)calloc(cap, sizeof(gb_slot));
+    for (uint32_t s = 0; s < nsplits; ++s)
+        for (uint64_t i = 0; i < lens[s]; ++i) {
+            if ((used + 1) * 2 > cap) {
+                gb_slot *big = (gb_slot *)calloc(cap * 2, sizeof(gb_slot));
+                for (uint64_t j = 0; j < cap; ++j)
+                    if (t[j].used) {
+                        uint64_t h = (t[j].key * 0x9E3779B1u) & (cap * 2 - 1);
+                        while (big[h].used) h = (h + 1) & (cap * 2 - 1);
+                        big[h] = t[j];
+                    }
+                free(t); t = big; cap *= 2;
+            }
+            uint32_t k = keys[s][i];
+            uint64_t h = (k * 0x9E3779B1u) & (cap - 1);
+            while (t[h].used && t[h].key != k) h = (h + 1) & (cap - 1);
+            if (!t[h].used) { t[h].used = 1; t[h].key = k; ++used; }
+            t[h].sum += vals[s][i];
+            ++records;
+        }
+    row *rows = (row *)malloc((used + 1) * sizeof(row));
+    uint8_t *kb = (uint8_t *)malloc(used * 4 + 4);
+    uint64_t n = 0;
+    for (uint64_t j = 0; j < cap; ++j)
+        if (t[j].used) {
+            uint32_t k = t[j].key;
+            kb[4 * n] = (uint8_t)(k >> 24); kb[4 * n + 1] = (uint8_t)(k >> 16);
+            kb[4 * n + 2] = (uint8_t)(k >> 8); kb[4 * n + 3] = (uint8_t)k;
+            rows[n].ptr = kb + 4 * n; rows[n].len = 4; rows[n].count = t[j].sum;
+            double kd = (double)k, r = (double)num_reducers;   /* Lua: key % NUM_REDUCERS on doubles */
+            rows[n].part = (uint32_t)(kd - floor(kd / r) * r);
+            ++n;
+        }
+    qsort(rows, n, sizeof(row), gb_cmp);
+    mro_result *res = result_from_rows(rows, n, records);
+    free(rows); free(kb); free(t);
+    return res;
+}
+
 int mro_max_threads(void)
 {
 #ifdef _OPENMP

@@ -55,6 +55,9 @@ def lib():
                                     C.c_uint32]
         L.mro_run_staged.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_uint32,
                                      C.c_uint32, C.c_int]
+        L.mro_groupby_u32.restype = C.POINTER(_Result)
+        L.mro_groupby_u32.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
+                                      C.c_uint32, C.c_uint32]
         L.mro_result_free.argtypes = [C.POINTER(_Result)]
         L.mro_heap_sort_u64.argtypes = [C.POINTER(C.c_uint64), C.c_uint32]
         L.mro_merge_kat.restype = C.c_uint32
@@ -131,6 +134,18 @@ def run_staged(splits, num_reducers, nthreads=1):
     """job.lua map jobs -> sorted runs -> utils.merge_iterator reduce jobs."""
     bufs, ptrs, lens, n = _splits_args(splits)
     return _take(lib().mro_run_staged(ptrs, lens, n, num_reducers, nthreads))
+
+
+def groupby_u32(splits, num_reducers):
+    """splits: list of (keys uint32 array, values uint32 array).  Group-by-sum on number keys
+    (BASELINE config 5); key bytes in the rows are 4 big-endian bytes."""
+    ks = [np.ascontiguousarray(k, dtype=np.uint32) for k, _ in splits]
+    vs = [np.ascontiguousarray(v, dtype=np.uint32) for _, v in splits]
+    n = len(ks)
+    kp = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in ks])
+    vp = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in vs])
+    lens = (C.c_uint64 * max(n, 1))(*[a.size for a in ks])
+    return _take(lib().mro_groupby_u32(kp, vp, lens, n, num_reducers))
 
 
 def fnv_lua52(key: bytes) -> int:

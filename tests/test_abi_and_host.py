@@ -40,7 +40,7 @@ def test_bad_config_is_rejected():
     h = ctypes.c_void_p()
     cfg = _native.Config(12, 0, 10, 0, 0, 0, 1 << 20, 0, 0, None, 1, 0)   # wrong struct_size
     assert lib.mr_ctx_create(ctypes.byref(cfg), ctypes.byref(h)) == _native.MR_ERR_INVALID
-    cfg = _native.Config(ctypes.sizeof(_native.Config), 0, 10, 7, 0, 0, 1 << 20, 0, 0, None, 1, 0)
+    cfg = _native.Config(ctypes.sizeof(_native.Config), 0, 10, 7, 0, 0, 1 << 20, 0, 0, None, 1, 0)  # unknown map kind
     assert lib.mr_ctx_create(ctypes.byref(cfg), ctypes.byref(h)) == _native.MR_ERR_UNSUPPORTED
     assert b"unsupported" in lib.mr_last_error(None)
     cfg = _native.Config(ctypes.sizeof(_native.Config), 0, 0, 0, 0, 0, 1 << 20, 0, 0, None, 1, 0)

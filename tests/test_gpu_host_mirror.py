@@ -72,3 +72,34 @@ def test_results_in_the_reference_wire_format(tmp_path):
     assert got == [(k, [int(c)]) for k, c in zip(want.keys(), want.count)]
     first = (tmp_path / names[0]).read_bytes().split(b"\n")[0]
     assert first.startswith(b'return "') and first.endswith(b"}")
+
+
+def test_group_by_sum_through_server_and_worker():
+    from lua_mapreduce_1_b200.examples import GroupBySum
+    rng = np.random.default_rng(3)
+    batches = [(rng.integers(0, 5000, n).astype(np.uint32), rng.integers(0, 100, n).astype(np.uint32))
+               for n in (20000, 1, 35000)]
+    want = O.groupby_u32(batches, 7)
+    seen = []
+
+    class Final:
+        init = staticmethod(lambda arg=None: None)
+
+        @staticmethod
+        def finalfn(pairs_iterator):
+            seen.extend((k, v[0]) for k, v in pairs_iterator)
+            return True
+
+    s = mapreduce.server.new("localhost", "groupby-gpu")
+    s.configure({"taskfn": GroupBySum, "mapfn": GroupBySum, "partitionfn": GroupBySum, "reducefn": GroupBySum,
+                 "combinerfn": GroupBySum, "finalfn": Final, "init_args": {"batches": batches, "num_reducers": 7}})
+    w = mapreduce.worker.new("localhost", "groupby-gpu").configure({"max_iter": 2000, "arena_bytes": 1 << 22,
+                                                                     "max_keys": 1 << 16})
+    t = threading.Thread(target=w.execute)
+    t.start()
+    s.loop()
+    t.join(60)
+    assert not t.is_alive()
+    keys = np.frombuffer(want.key_bytes.tobytes(), ">u4").tolist()
+    assert seen == list(zip(keys, (int(c) for c in want.count)))
+    w.ctx.close()

@@ -96,3 +96,15 @@ def test_staged_equals_naive_on_ragged_splits():
     a, b = O.run_naive(splits, 10), O.run_staged(splits, 10, 3)
     assert a.same_as(b) and a.tokens == b.tokens
     assert int(a.count.sum()) == a.tokens
+
+
+def test_groupby_oracle_on_number_keys():
+    # numbers order numerically (Lua `<`), partition = key % R, values summed (reducefn.lua:1-5)
+    k = np.array([5, 3, 5, 0, 4294967295, 3, 5, 10], dtype=np.uint32)
+    v = np.array([1, 2, 3, 4, 5, 6, 7, 8], dtype=np.uint32)
+    r = O.groupby_u32([(k[:4], v[:4]), (k[4:], v[4:])], 10)
+    keys = np.frombuffer(r.key_bytes.tobytes(), ">u4")
+    assert r.part.tolist() == [0, 0, 3, 5, 5] and keys.tolist() == [0, 10, 3, 5, 4294967295]
+    assert r.count.tolist() == [4, 8, 8, 11, 5] and r.tokens == 8
+    from lua_mapreduce_1_b200.examples import GroupBySum
+    assert [GroupBySum.partitionfn(int(x)) for x in keys] == r.part.tolist()
