@@ -767,7 +767,12 @@ int launch_sort(mr_ctx *ctx)
     sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->max_keys);
     radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->d_ctl);
     ctx->stats.launches += 2;
-    for (uint32_t pass = 0; pass < MAX_PASSES; ++pass) {
+    // the sort key has 64 chunk bits plus the bits of the largest partition id: more passes than
+    // that can never be needed (which ones are needed is decided on the device)
+    uint32_t part_bits = 0;
+    while (part_bits < 32 && ((uint64_t)1 << part_bits) < ctx->cfg.num_reducers) ++part_bits;
+    const uint32_t max_passes = std::min<uint32_t>(MAX_PASSES, (64 + part_bits + RADIX_BITS - 1) / RADIX_BITS);
+    for (uint32_t pass = 0; pass < max_passes; ++pass) {
         radix_pass_kernel<<<ctx->max_tiles, SORT_THREADS, 0, s>>>(ctx->bufs, pass, ctx->d_status, ctx->max_tiles,
                                                                  ctx->d_ctl);
         ctx->stats.launches++;

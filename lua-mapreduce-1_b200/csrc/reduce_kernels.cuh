@@ -21,6 +21,7 @@ constexpr int SORT_THREADS = 512;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_ITEMS = 8;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // 4096
+constexpr int LOOKBACK = 32;
 constexpr int ROWS_THREADS = 256;
 constexpr int ROWS_ITEMS = 8;
 constexpr int ROWS_TILE = ROWS_THREADS * ROWS_ITEMS; // 2048
@@ -304,21 +305,24 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         else { it[i].lo = 0; it[i].hi = 0; it[i].val = 0; }
     }
 #pragma unroll
+    for (int i = 0; i < SORT_ITEMS; ++i) k_dig[i] = (uint16_t)extract_digit(runs, nruns, it[i].hi, it[i].lo);
+#pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
         uint64_t idx = wbase + (uint64_t)i * 32 + lane;
         bool valid = idx < n;
         uint32_t act = __ballot_sync(0xFFFFFFFFu, valid);
-        uint32_t d = 0, r = 0;
+        uint32_t r = 0;
         if (valid) {
-            d = extract_digit(runs, nruns, it[i].hi, it[i].lo);
+            const uint32_t d = k_dig[i];
             uint32_t peers = __match_any_sync(act, d);
             uint32_t leader = __ffs((int)peers) - 1;
             uint32_t old = 0;
             if (lane == leader) { old = whist[warp][d]; whist[warp][d] = old + __popc(peers); }
-            old = __shfl_sync(peers, old, leader);
+            // one shuffle for the whole warp (the same mask in every lane); each lane reads its leader
+            old = __shfl_sync(act, old, leader);
             r = old + __popc(peers & lt);
         }
-        k_dig[i] = (uint16_t)d; k_rank[i] = (uint16_t)r;
+        k_rank[i] = (uint16_t)r;
         __syncwarp();
     }
     __syncthreads();
@@ -335,17 +339,17 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         else st[(uint64_t)tile * RADIX_BINS + b] = ST_AGG | tile_count;
         __threadfence();
         if (tile > 0) {
-            // look back 8 tiles at a time: the 8 loads are independent, so a long chain of
-            // not-yet-inclusive predecessors costs one L2 round trip per 8 tiles, not per tile
+            // look back LOOKBACK tiles at a time: the loads are independent, so the inclusive
+            // prefix crosses the (co-resident) tiles in tiles / LOOKBACK serial L2 round trips
             int t = (int)tile - 1;
             bool done = false;
             while (!done) {
-                uint32_t sv[8];
+                uint32_t sv[LOOKBACK];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) sv[k] = t - k >= 0 ? st[(uint64_t)(t - k) * RADIX_BINS + b] : (2u << 30);
+                for (int k = 0; k < LOOKBACK; ++k) sv[k] = t - k >= 0 ? st[(uint64_t)(t - k) * RADIX_BINS + b] : (2u << 30);
                 int k = 0;
 #pragma unroll
-                for (; k < 8; ++k) {
+                for (; k < LOOKBACK; ++k) {
                     if ((sv[k] >> 30) == 0) break;           // not published yet: re-read from here
                     prefix += sv[k] & ST_VAL;
                     if ((sv[k] >> 30) == 2) { done = true; break; }
