@@ -144,7 +144,7 @@ __global__ void export_header_kernel(uint8_t *send, uint32_t world, unsigned lon
     unsigned long long *hdr = (unsigned long long *)(send + (unsigned long long)d * slot_bytes);
     if (16 + nrec[d] * REC_BYTES + nbytes[d] > slot_bytes) {
         atomicOr(&ctl->err, ERR_SHUFFLE_FULL);
-        hdr[0] = 0; hdr[1] = 0;
+        hdr[0] = ~0ull; hdr[1] = 0; // poison: the receiver reports the overflow too, so every rank fails alike
     } else {
         hdr[0] = nrec[d]; hdr[1] = nbytes[d];
     }
