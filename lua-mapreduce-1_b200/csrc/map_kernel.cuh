@@ -88,10 +88,21 @@ __device__ __forceinline__ uint32_t keep_low_bytes(uint32_t x, int n)
     return x & ~hi;
 }
 
+// slot of (bucket, way) in the split layout: [ways 0-1 of all buckets][ways 2-3 of all buckets]
+__device__ __forceinline__ uint32_t slot_of(uint32_t bucket, int way, uint32_t slots)
+{
+    return (way >> 1) * (slots / 2) + bucket * 2 + (way & 1);
+}
+
 __device__ __forceinline__ void drain_keys(const MapParams &p, WarpSmem *ws, uint32_t first, uint32_t n,
                                            uint32_t lane)
 {
-    if (lane < n) gtable_add(p.gtab, p.gmask, p.arena, ws->gq[first + lane], 1, p.err);
+    if (lane < n) {
+        const ulonglong2 v = *(const ulonglong2 *)&ws->gq[first + lane]; // one 16-byte load
+        Key k;
+        k.k0 = v.x; k.k1 = v.y;
+        gtable_add(p.gtab, p.gmask, p.arena, k, 1, p.err);
+    }
 }
 
 __device__ __forceinline__ void drain_long(const MapParams &p, WarpSmem *ws, uint32_t n, uint32_t lane)
@@ -224,23 +235,25 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                 const uint32_t skh = keep_low_bytes(__funnelshift_r(x1, x2, bs), (int)len - 4) | (len << 24);
                 const unsigned long long sk = (uint64_t)w0 | ((uint64_t)skh << 32); // bytes + length
                 const uint32_t bucket = (w0 * 0x9E3779B1u + skh * 0x85EBCA77u) >> (32 - (LOG2_SLOTS - 2));
-                const uint32_t baddr = tkeys_s + bucket * (WAYS * 8);
+                // ways 0-1 live in the first half of the key array, ways 2-3 in the second, so the
+                // 16-byte first probe of a bucket falls on all eight bank groups, not four
+                const uint32_t baddr = tkeys_s + bucket * 16;
                 const ulonglong2 q0 = lds128(baddr);
                 int way = q0.x == sk ? 0 : q0.y == sk ? 1 : -1;
                 if (way < 0) {
-                    const ulonglong2 q1 = lds128(baddr + 16);
+                    const ulonglong2 q1 = lds128(baddr + SLOTS * 4);
                     way = q1.x == sk ? 2 : q1.y == sk ? 3 : -1;
                     if (way < 0 && can_insert) {
                         const int e2 = q0.x == 0 ? 0 : q0.y == 0 ? 1 : q1.x == 0 ? 2 : q1.y == 0 ? 3 : -1;
                         if (e2 >= 0) {
-                            const unsigned long long old = atomicCAS(&tkeys[bucket * WAYS + e2], 0ull, sk);
+                            const unsigned long long old = atomicCAS(&tkeys[slot_of(bucket, e2, SLOTS)], 0ull, sk);
                             if (old == 0) ++inserted;
                             if (old == 0 || old == sk) way = e2;
                         }
                     }
                 }
                 if (way >= 0) {
-                    atomicAdd(&tcnt[bucket * WAYS + way], 1u);
+                    atomicAdd(&tcnt[slot_of(bucket, way, SLOTS)], 1u);
                 } else {
                     to_global = true;
                     key.k0 = sk & LOW56;
@@ -248,7 +261,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                 }
             }
             const uint32_t gm = __ballot_sync(0xFFFFFFFFu, to_global);
-            if (to_global) ws->gq[nq + __popc(gm & lt)] = key;
+            if (to_global) *(ulonglong2 *)&ws->gq[nq + __popc(gm & lt)] = make_ulonglong2(key.k0, key.k1);
             nq += __popc(gm);
             __syncwarp();
             if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
@@ -267,7 +280,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                 const uint32_t w2 = keep_low_bytes(__funnelshift_r(x2, x3, bs), (int)len - 8);
                 const uint32_t w3 = keep_low_bytes(__funnelshift_r(x3, x4, bs), (int)len - 12) | (len << 24);
                 key.k1 = (uint64_t)w2 | ((uint64_t)w3 << 32);
-                ws->gq[nq + (j - t0)] = key;
+                *(ulonglong2 *)&ws->gq[nq + (j - t0)] = make_ulonglong2(key.k0, key.k1);
             }
             nq += min(32u, n_med - t0);
             __syncwarp();
