@@ -44,14 +44,15 @@ enum mr_status {
  * semantic definition; a module without a descriptor is simply not accelerated. */
 enum mr_map_kind {
     MR_MAP_TOKENIZE_WS = 0, /* examples/WordCount/mapfn.lua:3-9: emit(word, 1) per whitespace-separated token */
-    MR_MAP_RECORDS_U32 = 1  /* a mapfn that emits (number key, number value) records: emit, job.lua:83-97 */
+    MR_MAP_RECORDS_U32 = 1, /* a mapfn that emits (number key, number value) records: emit, job.lua:83-97 */
+    MR_MAP_BIGRAM_WS = 2    /* mapfn.lua:3-9 emitting (w_i .. " " .. w_{i+1}, 1) for neighbours inside a line */
 };
 enum mr_reduce_kind { MR_REDUCE_SUM_U64 = 0 };        /* examples/WordCount/reducefn.lua:1-5 */
 enum mr_partition_kind {
     MR_PARTITION_FNV1_LUA52 = 0, /* examples/WordCount/partitionfn.lua:8-16 (string keys) */
     MR_PARTITION_MOD_U32 = 1     /* partitionfn(key) = key % NUM_REDUCERS (number keys; job.lua:203-207) */
 };
-/* Supported pairs: (TOKENIZE_WS, FNV1_LUA52) and (RECORDS_U32, MOD_U32).  Number keys are ordered
+/* Supported pairs: (TOKENIZE_WS | BIGRAM_WS, FNV1_LUA52) and (RECORDS_U32, MOD_U32).  Number keys are ordered
  * numerically (Lua `<`, utils.lua:214) and come back in the rows as 4 big-endian bytes. */
 
 #define MR_MAX_TOKEN_BYTES ((1u << 26) - 1)

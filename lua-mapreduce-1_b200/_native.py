@@ -11,7 +11,7 @@ import numpy as np
 from . import build as _build
 
 MR_OK, MR_ERR_INVALID, MR_ERR_CUDA, MR_ERR_NOMEM, MR_ERR_OVERFLOW, MR_ERR_UNSUPPORTED, MR_ERR_END = range(7)
-MR_MAP_TOKENIZE_WS, MR_MAP_RECORDS_U32 = 0, 1
+MR_MAP_TOKENIZE_WS, MR_MAP_RECORDS_U32, MR_MAP_BIGRAM_WS = 0, 1, 2
 MR_REDUCE_SUM_U64 = 0
 MR_PARTITION_FNV1_LUA52, MR_PARTITION_MOD_U32 = 0, 1
 

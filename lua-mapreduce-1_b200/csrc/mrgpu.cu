@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "map_kernel.cuh"
+#include "bigram_kernel.cuh"
 #include "records_kernel.cuh"
 #include "reduce_kernels.cuh"
 
@@ -45,11 +46,11 @@ __global__ void ctl_set_n_kernel(Ctl *ctl, unsigned long long n) { ctl->n = n; }
 // that the host->device copies of the splits run back to back on the copy engine
 struct Gap { unsigned long long off, len; };
 constexpr uint32_t MAX_GAPS = 1u << 15;
-__global__ void __launch_bounds__(256) fill_gaps_kernel(uint8_t *arena, const Gap *gaps, uint32_t ngaps)
+__global__ void __launch_bounds__(256) fill_gaps_kernel(uint8_t *arena, const Gap *gaps, uint32_t ngaps, uint8_t fill)
 {
     for (uint32_t g = blockIdx.x; g < ngaps; g += gridDim.x) {
         const Gap gp = gaps[g];
-        for (unsigned long long i = threadIdx.x; i < gp.len; i += blockDim.x) arena[gp.off + i] = 0x20;
+        for (unsigned long long i = threadIdx.x; i < gp.len; i += blockDim.x) arena[gp.off + i] = fill;
     }
 }
 
@@ -228,6 +229,7 @@ struct mr_ctx {
     uint64_t mapped_segs = 0; // segments already consumed by mr_map_finish
     uint64_t input_bytes = 0;
     bool any_split = false;
+    uint8_t *d_pool = nullptr; // bigram contexts: bytes of keys longer than 15 bytes
     Gap *h_gaps = nullptr;    // pinned
     Gap *d_gaps = nullptr;
     uint32_t ngaps = 0;
@@ -369,7 +371,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab);
+    cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab); cudaFree(ctx->d_pool);
     cudaFree(ctx->ent.e);
     for (int i = 0; i < 2; ++i) cudaFree(ctx->bufs.item[i]);
     cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv);
@@ -397,7 +399,8 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     if (cfg->struct_size != sizeof(mr_config))
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: struct_size %u != %zu", cfg->struct_size,
                     sizeof(mr_config));
-    const bool text_job = cfg->map_kind == MR_MAP_TOKENIZE_WS && cfg->partition_kind == MR_PARTITION_FNV1_LUA52;
+    const bool text_job = (cfg->map_kind == MR_MAP_TOKENIZE_WS || cfg->map_kind == MR_MAP_BIGRAM_WS) &&
+                          cfg->partition_kind == MR_PARTITION_FNV1_LUA52;
     const bool rec_job = cfg->map_kind == MR_MAP_RECORDS_U32 && cfg->partition_kind == MR_PARTITION_MOD_U32;
     if (!(text_job || rec_job) || cfg->reduce_kind != MR_REDUCE_SUM_U64)
         return fail(nullptr, MR_ERR_UNSUPPORTED, "mr_ctx_create: unsupported map/reduce/partition kind");
@@ -440,7 +443,9 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     }
     ctx->slots = slots;
     ctx->max_tiles = (uint32_t)((mk + SORT_TILE - 1) / SORT_TILE);
-    ctx->key_bytes_cap = std::min<uint64_t>(ctx->arena_cap, mk * 64) + 64;
+    // every input byte is in at most one word-count key, but in up to two bigram keys
+    const uint64_t key_space = cfg->map_kind == MR_MAP_BIGRAM_WS ? 2 * ctx->arena_cap : ctx->arena_cap;
+    ctx->key_bytes_cap = std::min<uint64_t>(key_space, mk * 64) + 64;
 
 #define CUC(call)                                                                                    \
     do {                                                                                             \
@@ -457,6 +462,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     else { CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
     CUC(dmalloc(&ctx->d_arena, ctx->arena_cap + ARENA_SLACK));
     CUC(dmalloc(&ctx->d_gtab, slots));
+    if (cfg->map_kind == MR_MAP_BIGRAM_WS) CUC(dmalloc(&ctx->d_pool, 2 * ctx->arena_cap + ARENA_SLACK));
     CUC(dmalloc(&ctx->ent.e, mk));
     for (int i = 0; i < 2; ++i) {
         CUC(dmalloc(&ctx->bufs.item[i], mk));
@@ -484,7 +490,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(cudaEventCreateWithFlags(&ctx->ev_job, cudaEventDisableTiming));
     CUC(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     if (const char *v = getenv("MRGPU_AUTO_MAP_MB")) ctx->auto_map_bytes = (uint64_t)atoll(v) << 20;
-    ctx->bytes_base = ctx->d_arena;
+    ctx->bytes_base = ctx->d_pool ? ctx->d_pool : ctx->d_arena;
     int rc = mr_job_begin(ctx, 0);
     if (rc != MR_OK) { std::string m = ctx->err; mr_ctx_destroy(ctx); return fail(nullptr, rc, "%s", m.c_str()); }
     *out = ctx;
@@ -508,7 +514,7 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
         // keep the staged splits: the next mr_map_finish maps all of them again
         ctx->remap_upto = std::max(ctx->remap_upto, ctx->mapped_segs);
         ctx->mapped_segs = 0;
-        ctx->map_dirty = ctx->any_split && ctx->cfg.map_kind == MR_MAP_TOKENIZE_WS;
+        ctx->map_dirty = ctx->any_split && ctx->cfg.map_kind != MR_MAP_RECORDS_U32;
         ctx->rec_remap = !ctx->rec_splits.empty();
         ctx->staged_since_map = 0;
     }
@@ -516,7 +522,7 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
     CU(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
     ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(ctx->d_ctl);
     CU(cudaGetLastError());
-    ctx->bytes_base = ctx->d_arena;
+    ctx->bytes_base = ctx->d_pool ? ctx->d_pool : ctx->d_arena;
     ctx->imported = false;
     ctx->shuffle_counted = false;
     ctx->state = mr_ctx::IDLE;
@@ -535,7 +541,9 @@ static int flush_gaps(mr_ctx *ctx)
 {
     if (!ctx->ngaps) return MR_OK;
     CU(cudaMemcpyAsync(ctx->d_gaps, ctx->h_gaps, ctx->ngaps * sizeof(Gap), cudaMemcpyHostToDevice, ctx->stream));
-    fill_gaps_kernel<<<std::min<uint32_t>(ctx->ngaps, 1024u), 256, 0, ctx->stream>>>(ctx->d_arena, ctx->d_gaps, ctx->ngaps);
+    // between splits: a space for the word count; a newline for bigrams (pairs never span splits)
+    const uint8_t fill = ctx->cfg.map_kind == MR_MAP_BIGRAM_WS ? 0x0A : 0x20;
+    fill_gaps_kernel<<<std::min<uint32_t>(ctx->ngaps, 1024u), 256, 0, ctx->stream>>>(ctx->d_arena, ctx->d_gaps, ctx->ngaps, fill);
     CU(cudaGetLastError());
     // the pinned list is reused by later calls: wait until the copy above has read it
     CU(cudaEventRecord(ctx->ev_gaps, ctx->stream));
@@ -548,7 +556,7 @@ static int flush_gaps(mr_ctx *ctx)
 static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKind kind)
 {
     if (!ctx) return MR_ERR_INVALID;
-    if (ctx->cfg.map_kind != MR_MAP_TOKENIZE_WS)
+    if (ctx->cfg.map_kind == MR_MAP_RECORDS_U32)
         return fail(ctx, MR_ERR_INVALID, "mr_map_split: this context maps records, use mr_map_records");
     if (n && !bytes) return fail(ctx, MR_ERR_INVALID, "mr_map_split: null bytes");
     if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
@@ -623,6 +631,31 @@ static int run_map_round(mr_ctx *ctx)
         ctx->h_gaps[ctx->ngaps].len = end + TAIL_GUARD - ctx->used;
         ctx->ngaps++;
         { int rc = flush_gaps(ctx); if (rc) return rc; }
+    }
+    if (ctx->cfg.map_kind == MR_MAP_BIGRAM_WS) {
+        BigramParams bp;
+        bp.arena = ctx->d_arena;
+        bp.begin = ctx->mapped_segs * SEG;
+        bp.end = end;
+        bp.limit = end + TAIL_GUARD;
+        bp.gtab = ctx->d_gtab;
+        bp.gmask = (uint32_t)(ctx->slots - 1);
+        bp.max_key = MR_MAX_TOKEN_BYTES;
+        bp.pool = ctx->d_pool;
+        bp.pool_used = &ctx->d_ctl->pool_used;
+        bp.pool_cap = 2 * ctx->arena_cap;
+        bp.pairs = &ctx->d_ctl->tokens;
+        bp.err = &ctx->d_ctl->err;
+        if (bp.end > bp.begin) {
+            map_bigram_kernel<<<grid_for(bp.end - bp.begin, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(bp);
+            ctx->stats.launches++;
+            CU(cudaGetLastError());
+        }
+        ctx->mapped_segs = end / SEG;
+        if (!remap_only) ctx->used = end + TAIL_GUARD;
+        ctx->map_dirty = false;
+        ctx->staged_since_map = 0;
+        return MR_OK;
     }
     MapParams p;
     p.arena = ctx->d_arena;

@@ -51,6 +51,7 @@ struct Ctl {
     unsigned long long n_out;        // rows after the segmented reduce
     unsigned long long key_bytes;    // sum of key lengths over rows
     unsigned long long tokens;
+    unsigned long long pool_used;    // bytes of the key pool in use (bigram keys longer than 15 bytes)
     unsigned int nruns[MAX_PASSES];
     DigitRun runs[MAX_PASSES][8];
     unsigned int tickets[MAX_PASSES];

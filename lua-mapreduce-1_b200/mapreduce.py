@@ -36,7 +36,8 @@ MAX_WORKER_RETRIES = 3   # utils.lua:48
 DEFAULT_SLEEP = 0.01
 
 NATIVE_KINDS = {
-    "map": {"tokenize_ws": _native.MR_MAP_TOKENIZE_WS, "records_u32": _native.MR_MAP_RECORDS_U32},
+    "map": {"tokenize_ws": _native.MR_MAP_TOKENIZE_WS, "records_u32": _native.MR_MAP_RECORDS_U32,
+            "bigram_ws": _native.MR_MAP_BIGRAM_WS},
     "reduce": {"sum_u64": _native.MR_REDUCE_SUM_U64},
     "partition": {"fnv1_lua52_double": _native.MR_PARTITION_FNV1_LUA52, "mod_u32": _native.MR_PARTITION_MOD_U32},
 }

@@ -495,6 +495,61 @@ mro_result *mro_run_staged(const uint8_t *const *splits, const uint64_t *lens, u
     return r;
 }
 
+/* ---------------------------------------------------------------- bigram count */
+
+/* BASELINE config 4: the WordCount job with a mapfn that emits word pairs,
+ *     for line in io.lines(value) do
+ *       local prev
+ *       for w in line:gmatch("[^%s]+") do if prev then emit(prev .. " " .. w, 1) end; prev = w end
+ *     end
+ * i.e. mapfn.lua:4-8 with the key `w_i .. " " .. w_{i+1}` inside one line (io.lines cuts at '\n'
+ * only; '\r' stays in the line and is whitespace for %s).  Everything downstream is the WordCount
+ * path: emit + sum (job.lua:83-97, reducefn.lua:1-5), partitionfn.lua:8-16, Lua string order. */
+mro_result *mro_run_bigram(const uint8_t *const *splits, const uint64_t *lens, uint32_t nsplits,
+                           uint32_t num_reducers)
+{
+    ktable t;
+    kt_init(&t, 1u << 16);
+    uint64_t pairs = 0, cap = 1u << 20, used = 0, nblocks = 0, blocks_cap = 64;
+    uint8_t **blocks = (uint8_t **)malloc(blocks_cap * sizeof(uint8_t *)); /* key bytes live in blocks */
+    uint8_t *cur = (uint8_t *)malloc(cap);
+    blocks[nblocks++] = cur;
+    for (uint32_t s = 0; s < nsplits; ++s) {
+        const uint8_t *b = splits[s];
+        uint64_t n = lens[s], i = 0;
+        const uint8_t *prev = NULL;
+        uint64_t prev_len = 0;
+        while (i < n) {
+            while (i < n && mro_is_space(b[i])) { if (b[i] == '\n') prev = NULL; ++i; }
+            uint64_t st = i;
+            while (i < n && !mro_is_space(b[i])) ++i;
+            if (i == st) break;
+            if (prev) {
+                uint64_t klen = prev_len + 1 + (i - st);
+                if (used + klen > cap) {
+                    if (nblocks == blocks_cap) { blocks_cap *= 2; blocks = (uint8_t **)realloc(blocks, blocks_cap * sizeof(uint8_t *)); }
+                    cap = klen > (1u << 20) ? klen : (1u << 20);
+                    cur = (uint8_t *)malloc(cap); used = 0; blocks[nblocks++] = cur;
+                }
+                uint8_t *k = cur + used;
+                memcpy(k, prev, prev_len); k[prev_len] = ' '; memcpy(k + prev_len + 1, b + st, i - st);
+                uint64_t before = t.used;
+                kt_add(&t, k, (uint32_t)klen, 1);
+                if (t.used != before) used += klen; /* keep the bytes only for a new key */
+                ++pairs;
+            }
+            prev = b + st; prev_len = i - st;
+        }
+    }
+    row *rows = rows_from_table(&t, num_reducers);
+    qsort(rows, t.used, sizeof(row), row_cmp_part_key);
+    mro_result *r = result_from_rows(rows, t.used, pairs);
+    free(rows); free(t.slots);
+    for (uint64_t j = 0; j < nblocks; ++j) free(blocks[j]);
+    free(blocks);
+    return r;
+}
+
 /* ---------------------------------------------------------------- group-by sum on number keys */
 
 /* BASELINE config 5: a job whose mapfn emits (number key, number value) pairs, whose

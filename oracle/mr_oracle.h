@@ -29,6 +29,8 @@ mro_result *mro_run_naive(const uint8_t *const *splits, const uint64_t *lens, ui
                           uint32_t num_reducers);
 mro_result *mro_run_staged(const uint8_t *const *splits, const uint64_t *lens, uint32_t nsplits,
                            uint32_t num_reducers, int nthreads);
+mro_result *mro_run_bigram(const uint8_t *const *splits, const uint64_t *lens, uint32_t nsplits,
+                           uint32_t num_reducers);
 mro_result *mro_groupby_u32(const uint32_t *const *keys, const uint32_t *const *vals, const uint64_t *lens,
                             uint32_t nsplits, uint32_t num_reducers);
 void mro_result_free(mro_result *r);

@@ -49,8 +49,9 @@ def lib():
         L.mro_key_cmp.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]
         L.mro_is_space.restype = C.c_int
         L.mro_is_space.argtypes = [C.c_ubyte]
-        for f in (L.mro_run_naive, L.mro_run_staged):
+        for f in (L.mro_run_naive, L.mro_run_staged, L.mro_run_bigram):
             f.restype = C.POINTER(_Result)
+        L.mro_run_bigram.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_uint32, C.c_uint32]
         L.mro_run_naive.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_uint32,
                                     C.c_uint32]
         L.mro_run_staged.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_uint32,
@@ -134,6 +135,12 @@ def run_staged(splits, num_reducers, nthreads=1):
     """job.lua map jobs -> sorted runs -> utils.merge_iterator reduce jobs."""
     bufs, ptrs, lens, n = _splits_args(splits)
     return _take(lib().mro_run_staged(ptrs, lens, n, num_reducers, nthreads))
+
+
+def run_bigram(splits, num_reducers):
+    """Bigram count (BASELINE config 4): keys `w_i .. " " .. w_{i+1}` inside a line; .tokens = pairs emitted."""
+    bufs, ptrs, lens, n = _splits_args(splits)
+    return _take(lib().mro_run_bigram(ptrs, lens, n, num_reducers))
 
 
 def groupby_u32(splits, num_reducers):

@@ -108,3 +108,18 @@ def test_groupby_oracle_on_number_keys():
     assert r.count.tolist() == [4, 8, 8, 11, 5] and r.tokens == 8
     from lua_mapreduce_1_b200.examples import GroupBySum
     assert [GroupBySum.partitionfn(int(x)) for x in keys] == r.part.tolist()
+
+
+def test_bigram_oracle_against_python_restatement():
+    import collections
+    from lua_mapreduce_1_b200 import corpus
+    splits = [b"a b  c\td\r\ne f\n\ng\nh i", b"x y", corpus.TORTURE, corpus.generate_split(3, 300)[0].tobytes()]
+    want = collections.Counter()
+    for s in splits:
+        for line in s.split(b"\n"):              # io.lines cuts at "\n" only
+            w = line.split()
+            for a, b in zip(w, w[1:]):
+                want[a + b" " + b] += 1
+    r = O.run_bigram(splits, 10)
+    assert r.as_dict() == dict(want) and r.tokens == sum(want.values())
+    assert r.keys() == [k for _, k in sorted((O.partition(k, 10), k) for k in want)]
