@@ -797,6 +797,7 @@ int launch_sort(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
     CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
+    CU(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
     sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->max_keys);
     radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->d_ctl);
     ctx->stats.launches += 2;
@@ -806,8 +807,8 @@ int launch_sort(mr_ctx *ctx)
     while (part_bits < 32 && ((uint64_t)1 << part_bits) < ctx->cfg.num_reducers) ++part_bits;
     const uint32_t max_passes = std::min<uint32_t>(MAX_PASSES, (64 + part_bits + RADIX_BITS - 1) / RADIX_BITS);
     for (uint32_t pass = 0; pass < max_passes; ++pass) {
-        radix_pass_kernel<<<ctx->max_tiles, SORT_THREADS, 0, s>>>(ctx->bufs, pass, ctx->d_status, ctx->max_tiles,
-                                                                 ctx->d_ctl);
+        radix_pass_kernel<<<ctx->max_tiles, SORT_THREADS, sizeof(SortSmem), s>>>(ctx->bufs, pass, ctx->d_status,
+                                                                                ctx->max_tiles, ctx->d_ctl);
         ctx->stats.launches++;
     }
     uint64_t tie_cap = 1; while (tie_cap < ctx->max_keys) tie_cap <<= 1;
@@ -1011,6 +1012,10 @@ int mr_result_next(mr_result *res, const char **key, uint64_t *klen, uint64_t *c
 }
 
 void mr_result_release(mr_result *res) { delete res; }
+
+#ifdef MRGPU_SORT_TIMING
+extern "C" const long long *mr_debug_stamps(mr_ctx *ctx) { return ctx->h_ctl->dbg; }
+#endif
 
 int mr_stats_get(mr_ctx *ctx, mr_stats *out)
 {

@@ -56,6 +56,7 @@ struct Ctl {
     DigitRun runs[MAX_PASSES][8];
     unsigned int tickets[MAX_PASSES];
     unsigned int ghist[MAX_PASSES][RADIX_BINS];
+    long long dbg[16];               // MRGPU_SORT_TIMING builds: clock64 stamps of one tile
 };
 
 // Dense entries: the occupied slots of the global table copied side by side, 32 bytes each
@@ -270,34 +271,45 @@ struct SortBufs {
     SortItem *item[2];
 };
 
-// One LSD pass (stable): tile-local ranking by warp-level digit matching, tile offsets
-// by decoupled look-back over per-tile digit counts.
+// One LSD pass (stable).  Per tile of 4096 items: digits, warp-local ranks from ballot-built
+// peer masks, per-bin tile counts published for a decoupled look-back (tile id = block index: a
+// tile only ever waits for lower-numbered tiles, and blocks of a grid are dispatched in index
+// order), items reordered by digit in shared memory so that the global scatter writes runs of
+// consecutive 16-byte items instead of one 32-byte sector per item.
+struct __align__(16) SortSmem {
+    SortItem sorted[SORT_TILE];                 // 64 KB: the tile in digit order
+    unsigned int whist[SORT_WARPS][RADIX_BINS]; // per-warp digit counts -> exclusive offsets
+    unsigned int bin_base[RADIX_BINS];          // global start of the tile's items of each digit
+    unsigned int tile_excl[RADIX_BINS];         // start of each digit inside the tile
+    unsigned int scan_tmp[2][RADIX_BINS / 32];
+    unsigned char dig[SORT_TILE];               // digit of sorted[i]
+    DigitRun runs[8];
+    unsigned int nruns;
+};
+
+#ifdef MRGPU_SORT_TIMING
+#define STAMP(k) do { if (blockIdx.x == 64 && pass == 1 && threadIdx.x == 0) ctl->dbg[k] = clock64(); } while (0)
+#else
+#define STAMP(k) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs, uint32_t pass,
                                                                   uint32_t *status, uint32_t max_tiles,
                                                                   Ctl *ctl)
 {
+    extern __shared__ __align__(16) uint8_t sort_smem_raw[];
+    SortSmem &sm = *(SortSmem *)sort_smem_raw;
+    STAMP(0);
     if (pass >= ctl->npasses) return;
     const uint64_t n = ctl->n;
-    __shared__ uint32_t s_tile;
-    __shared__ unsigned int whist[SORT_WARPS][RADIX_BINS];
-    __shared__ unsigned int bin_base[RADIX_BINS];
-    __shared__ unsigned int scan_tmp[RADIX_BINS / 32];
-    __shared__ DigitRun runs[8];
-    __shared__ unsigned int s_nruns;
-    if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->tickets[pass], 1u);
-    if (threadIdx.x < 8) runs[threadIdx.x] = ctl->runs[pass][threadIdx.x];
-    if (threadIdx.x == 8) s_nruns = ctl->nruns[pass];
-    for (uint32_t i = threadIdx.x; i < SORT_WARPS * RADIX_BINS; i += SORT_THREADS) (&whist[0][0])[i] = 0;
-    __syncthreads();
-    const uint32_t tile = s_tile;
+    const uint32_t tile = blockIdx.x;
     if ((uint64_t)tile * SORT_TILE >= n) return;
     const SortItem *src = bufs.item[pass & 1];
     SortItem *dst = bufs.item[(pass & 1) ^ 1];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt = lanemask_lt();
-    const uint32_t nruns = s_nruns;
 
+    // item loads first: their latency overlaps the set-up below
     SortItem it[SORT_ITEMS];
-    uint16_t k_rank[SORT_ITEMS], k_dig[SORT_ITEMS];
     const uint64_t wbase = (uint64_t)tile * SORT_TILE + (uint64_t)warp * (32 * SORT_ITEMS);
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
@@ -305,40 +317,60 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
         if (idx < n) it[i] = src[idx];
         else { it[i].lo = 0; it[i].hi = 0; it[i].val = 0; }
     }
+    if (threadIdx.x < 8) sm.runs[threadIdx.x] = ctl->runs[pass][threadIdx.x];
+    if (threadIdx.x == 8) sm.nruns = ctl->nruns[pass];
+    for (uint32_t i = threadIdx.x; i < SORT_WARPS * RADIX_BINS; i += SORT_THREADS) (&sm.whist[0][0])[i] = 0;
+    __syncthreads();
+    STAMP(1);
+    const uint32_t nruns = sm.nruns;
+
+    uint16_t k_rank[SORT_ITEMS];
+    uint8_t k_dig[SORT_ITEMS];
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) k_dig[i] = (uint16_t)extract_digit(runs, nruns, it[i].hi, it[i].lo);
+    for (int i = 0; i < SORT_ITEMS; ++i) k_dig[i] = (uint8_t)extract_digit(sm.runs, nruns, it[i].hi, it[i].lo);
+    STAMP(2);
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
-        uint64_t idx = wbase + (uint64_t)i * 32 + lane;
-        bool valid = idx < n;
-        uint32_t act = __ballot_sync(0xFFFFFFFFu, valid);
+        const bool valid = wbase + (uint64_t)i * 32 + lane < n;
+        const uint32_t act = __ballot_sync(0xFFFFFFFFu, valid);
+        const uint32_t d = k_dig[i];
+        // lanes holding the same digit: eight ballots (one per digit bit), all independent
+        uint32_t peers = act;
+#pragma unroll
+        for (int bit = 0; bit < RADIX_BITS; ++bit) {
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, (d >> bit) & 1u);
+            peers &= ((d >> bit) & 1u) ? bal : ~bal;
+        }
         uint32_t r = 0;
         if (valid) {
-            const uint32_t d = k_dig[i];
-            uint32_t peers = __match_any_sync(act, d);
-            uint32_t leader = __ffs((int)peers) - 1;
+            const uint32_t leader = __ffs((int)peers) - 1;
             uint32_t old = 0;
-            if (lane == leader) { old = whist[warp][d]; whist[warp][d] = old + __popc(peers); }
-            // one shuffle for the whole warp (the same mask in every lane); each lane reads its leader
-            old = __shfl_sync(act, old, leader);
+            if (lane == leader) { old = sm.whist[warp][d]; sm.whist[warp][d] = old + __popc(peers); }
+            old = __shfl_sync(act, old, leader); // one shuffle for the warp; each lane reads its leader
             r = old + __popc(peers & lt);
         }
         k_rank[i] = (uint16_t)r;
         __syncwarp();
     }
+    STAMP(3);
     __syncthreads();
+    STAMP(4);
     // thread b < 256 owns bin b: per-warp exclusive offsets, tile count, look-back
-    unsigned int prefix = 0, g = 0, incl = 0;
+    unsigned int prefix = 0, g = 0, incl = 0, tcount = 0, tincl = 0;
     if (threadIdx.x < RADIX_BINS) {
         const uint32_t b = threadIdx.x;
+        unsigned int c[SORT_WARPS];
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w) c[w] = sm.whist[w][b];
         unsigned int run = 0;
 #pragma unroll
-        for (int w = 0; w < SORT_WARPS; ++w) { unsigned int c = whist[w][b]; whist[w][b] = run; run += c; }
-        const unsigned int tile_count = run;
+        for (int w = 0; w < SORT_WARPS; ++w) { sm.whist[w][b] = run; run += c[w]; }
+        tcount = run;
+        // the status word carries its own flag, so no fence is needed around it
         volatile uint32_t *st = status + ((uint64_t)pass * max_tiles) * RADIX_BINS;
-        if (tile == 0) st[(uint64_t)tile * RADIX_BINS + b] = ST_INC | tile_count;
-        else st[(uint64_t)tile * RADIX_BINS + b] = ST_AGG | tile_count;
-        __threadfence();
+        st[(uint64_t)tile * RADIX_BINS + b] = (tile == 0 ? ST_INC : ST_AGG) | tcount;
+        g = ctl->ghist[pass][b];
+        STAMP(5);
         if (tile > 0) {
             // look back LOOKBACK tiles at a time: the loads are independent, so the inclusive
             // prefix crosses the (co-resident) tiles in tiles / LOOKBACK serial L2 round trips
@@ -357,31 +389,48 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
                 }
                 t -= k;
             }
-            st[(uint64_t)tile * RADIX_BINS + b] = ST_INC | (prefix + tile_count);
+            st[(uint64_t)tile * RADIX_BINS + b] = ST_INC | (prefix + tcount);
         }
-        // exclusive scan of the global histogram = start of every bin
-        g = ctl->ghist[pass][b];
-        incl = g;
+        STAMP(6);
+        // two exclusive scans over the bins: global histogram (bin starts) and tile counts
+        incl = g; tincl = tcount;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
-        if (lane == 31) scan_tmp[warp] = incl;
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d), tv = __shfl_up_sync(0xFFFFFFFFu, tincl, d);
+            if (lane >= d) { incl += v; tincl += tv; }
+        }
+        if (lane == 31) { sm.scan_tmp[0][warp] = incl; sm.scan_tmp[1][warp] = tincl; }
     }
     __syncthreads();
     if (threadIdx.x < RADIX_BINS) {
-        unsigned int wsum = 0;
-        for (uint32_t w = 0; w < warp; ++w) wsum += scan_tmp[w];
-        bin_base[threadIdx.x] = wsum + incl - g + prefix;
+        unsigned int wsum = 0, twsum = 0;
+        for (uint32_t w = 0; w < warp; ++w) { wsum += sm.scan_tmp[0][w]; twsum += sm.scan_tmp[1][w]; }
+        sm.bin_base[threadIdx.x] = wsum + incl - g + prefix;
+        sm.tile_excl[threadIdx.x] = twsum + tincl - tcount;
     }
     __syncthreads();
+    STAMP(7);
+    // reorder by digit in shared memory, then write runs of consecutive items
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
-        uint64_t idx = wbase + (uint64_t)i * 32 + lane;
-        if (idx < n) {
-            uint32_t d = k_dig[i];
-            uint64_t o = (uint64_t)bin_base[d] + whist[warp][d] + k_rank[i];
-            dst[o] = it[i];
+        if (wbase + (uint64_t)i * 32 + lane < n) {
+            const uint32_t d = k_dig[i];
+            const uint32_t q = sm.tile_excl[d] + sm.whist[warp][d] + k_rank[i];
+            sm.sorted[q] = it[i];
+            sm.dig[q] = (unsigned char)d;
         }
     }
+    __syncthreads();
+    const uint64_t tile_n = n - (uint64_t)tile * SORT_TILE < SORT_TILE ? n - (uint64_t)tile * SORT_TILE : SORT_TILE;
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; ++i) {
+        const uint32_t q = (uint32_t)i * SORT_THREADS + threadIdx.x;
+        if (q < tile_n) {
+            const uint32_t d = sm.dig[q];
+            dst[(uint64_t)sm.bin_base[d] + (q - sm.tile_excl[d])] = sm.sorted[q];
+        }
+    }
+    STAMP(8);
 }
 
 // ------------------------------------------------------------------ ties beyond 7 bytes
@@ -590,13 +639,10 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
                                                            RowArrays rows, uint32_t num_reducers,
                                                            unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl)
 {
-    __shared__ uint32_t s_tile;
     __shared__ unsigned int wh[ROWS_THREADS / 32];
     __shared__ unsigned long long wb[ROWS_THREADS / 32];
     __shared__ unsigned long long s_prefix_h, s_prefix_b;
-    if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->rows_ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
+    const uint32_t tile = blockIdx.x; // tiles wait only for lower-numbered ones (in-order block dispatch)
     const uint64_t n = ctl->n;
     if (n == 0) {
         if (tile == 0) {
