@@ -41,14 +41,26 @@ struct MapParams {
     uint32_t max_token;
     unsigned long long *tokens; // running token count
     unsigned int *err;
+    long long *dbg;             // MRGPU_MAP_TIMING builds: per-phase cycles of one warp
 };
+
+#ifdef MRGPU_MAP_TIMING
+#define MT_DECL long long mt_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, mt_t = clock64(), mt_n
+#define MT(k) do { mt_n = clock64(); mt_acc[k] += mt_n - mt_t; mt_t = mt_n; } while (0)
+#define MT_END do { if (blockIdx.x == 7 && warp == 5 && lane == 0) for (int q = 0; q < 8; ++q) p.dbg[q] = mt_acc[q]; } while (0)
+#else
+#define MT_DECL do { } while (0)
+#define MT(k) do { } while (0)
+#define MT_END do { } while (0)
+#endif
 
 // per-warp shared memory
 struct __align__(16) WarpSmem {
     uint32_t stage[(SEG + SEG_AHEAD) / 4]; // 1056 B: the segment + 32 look-ahead bytes
     uint16_t list[SEG / 2];                // token entries (pos | len << 10): short tokens from the
                                            // front, medium tokens from the back (max one per 2 bytes)
-    Key gq[64];                            // keys waiting for the global table
+    Key gq[96];                            // keys waiting for the global table: < 64 after a drain
+                                           // (32 left + 32 re-queued at most), + 32 per iteration
     unsigned long long longq[32];          // arena offsets of 16+ byte tokens
 };
 
@@ -100,9 +112,43 @@ __device__ __forceinline__ void drain_keys(const MapParams &p, WarpSmem *ws, uin
     if (lane < n) {
         const ulonglong2 v = *(const ulonglong2 *)&ws->gq[first + lane]; // one 16-byte load
         Key k;
-        k.k0 = v.x; k.k1 = v.y;
+        k.k0 = v.x; k.k1 = v.y & ~(0xFull << 60); // a re-queued key still carries its probe distance
         gtable_add(p.gtab, p.gmask, p.arena, k, 1, p.err);
     }
+}
+
+// Asynchronous insertion into the global table.  A queued key carries its probe distance in
+// bits 60..63 of k1 (free for inline keys, whose length uses bits 56..59).  probe_issue starts the
+// 16-byte load of slot (home + distance); probe_try, called a few hundred instructions later, finishes
+// the insertion if that slot holds the key or is empty, and otherwise reports "try the next slot",
+// upon which the caller simply re-queues the key with distance + 1: no drain ever waits for memory.
+// A stale loaded value is harmless: an empty slot is claimed with compare-and-swap, which returns
+// the current content, and a slot's key never changes once set.
+constexpr unsigned long long QDIST_MASK = 0xFull << 60;
+
+__device__ __forceinline__ void probe_issue(const MapParams &p, const Key &qkey, uint32_t &slot, ulonglong2 &v)
+{
+    Key key = qkey;
+    key.k1 &= ~QDIST_MASK;
+    slot = (hash_key(key) + (uint32_t)(qkey.k1 >> 60)) & p.gmask;
+    v = __ldcg((const ulonglong2 *)&p.gtab[slot]);
+}
+
+// returns true when the key has been counted
+__device__ __forceinline__ bool probe_try(const MapParams &p, const Key &qkey, uint32_t slot, ulonglong2 v)
+{
+    Key key = qkey, cur;
+    key.k1 &= ~QDIST_MASK;
+    cur.k0 = v.x; cur.k1 = v.y;
+    if (cur.k1 == 0) {
+        cur = cas128(&p.gtab[slot], key);
+        if (cur.k1 == 0) cur = key; // the slot is ours
+    }
+    if (cur.k0 == key.k0 && cur.k1 == key.k1) {
+        atomicAdd(&p.gtab[slot].cnt, 1ull);
+        return true;
+    }
+    return false;
 }
 
 __device__ __forceinline__ void drain_long(const MapParams &p, WarpSmem *ws, uint32_t n, uint32_t lane)
@@ -138,10 +184,40 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
 
     const uint32_t lt = lanemask_lt();
     uint32_t nq = 0, nlong = 0; // warp-uniform fills of gq / longq
+    // one batch of 32 keys whose slot loads are in flight (lane i holds key i)
+    bool pending = false;
+    Key pkey;
+    pkey.k0 = 0; pkey.k1 = 0;
+    uint32_t pslot = 0;
+    ulonglong2 pv = make_ulonglong2(0, 0);
+    // take the newest 32 queued keys, finish the batch in flight (re-queueing what needs another
+    // probe), then put the new batch in flight
+    auto drain32 = [&]() {
+        nq -= 32;
+        const ulonglong2 kv = *(const ulonglong2 *)&ws->gq[nq + lane];
+        __syncwarp();
+        if (pending) {
+            bool again = !probe_try(p, pkey, pslot, pv);
+            if (again && (pkey.k1 >> 60) == 15) { // very long probe chain: finish it synchronously
+                Key k = pkey;
+                k.k1 &= ~QDIST_MASK;
+                gtable_add(p.gtab, p.gmask, p.arena, k, 1, p.err);
+                again = false;
+            }
+            const uint32_t am = __ballot_sync(0xFFFFFFFFu, again);
+            if (again) *(ulonglong2 *)&ws->gq[nq + __popc(am & lt)] = make_ulonglong2(pkey.k0, pkey.k1 + (1ull << 60));
+            nq += __popc(am);
+        }
+        pkey.k0 = kv.x; pkey.k1 = kv.y;
+        probe_issue(p, pkey, pslot, pv);
+        pending = true;
+        __syncwarp();
+    };
     unsigned long long my_tokens = 0;
     const uint64_t gwarp = (uint64_t)blockIdx.x * WARPS + warp, nwarps = (uint64_t)gridDim.x * WARPS;
-
+    MT_DECL;
     for (uint64_t s = gwarp; s < p.nseg; s += nwarps) {
+        MT(7);
         const uint64_t base = (p.first_seg + s) * SEG;
         const uint4 *src = (const uint4 *)(p.arena + base);
         // ---- 1. load + stage + non-space mask of the lane's 32 bytes
@@ -162,6 +238,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                            nonspace_nibble(b.y) << 20 | nonspace_nibble(b.z) << 24 |
                            nonspace_nibble(b.w) << 28;
         __syncwarp();
+        MT(0); // loads + staging + mask
         // mask of the 32 look-ahead bytes: lanes 0..7 take one word each
         uint32_t am = 0;
         if (lane < 8) am = nonspace_nibble(ws->stage[SEG / 4 + lane]) << (4 * lane);
@@ -220,6 +297,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         const bool can_insert = *(volatile unsigned int *)&tused < FILL_LIMIT; // warp-uniform
         uint32_t inserted = 0;
         __syncwarp();
+        MT(1); // starts, classes, scan, lists
         // ---- 3a. short tokens (<= 7 bytes): one per lane, CTA table
         for (uint32_t t0 = 0; t0 < n_short; t0 += 32) {
             const uint32_t j = t0 + lane;
@@ -264,7 +342,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             if (to_global) *(ulonglong2 *)&ws->gq[nq + __popc(gm & lt)] = make_ulonglong2(key.k0, key.k1);
             nq += __popc(gm);
             __syncwarp();
-            if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
+            MT(2); // short tokens: key + CTA table
+            if (nq >= 32) { drain32(); while (nq >= 64) drain32(); MT(4); }
         }
         // ---- 3b. medium tokens (8..15 bytes): 128-bit inline key, straight to the global queue
         for (uint32_t t0 = 0; t0 < n_med; t0 += 32) {
@@ -284,13 +363,21 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             }
             nq += min(32u, n_med - t0);
             __syncwarp();
-            if (nq >= 32) { nq -= 32; drain_keys(p, ws, nq, 32, lane); __syncwarp(); }
+            MT(3); // medium tokens: key build + queue
+            if (nq >= 32) { drain32(); while (nq >= 64) drain32(); MT(4); }
         }
         if (inserted) atomicAdd(&tused, inserted);
         __syncwarp();
     }
-    drain_keys(p, ws, 0, nq, lane);
+    if (pending && !probe_try(p, pkey, pslot, pv)) { // the batch in flight, then the rest, synchronously
+        Key k = pkey;
+        k.k1 &= ~QDIST_MASK;
+        gtable_add(p.gtab, p.gmask, p.arena, k, 1, p.err);
+    }
+    for (uint32_t q0 = 0; q0 < nq; q0 += 32) drain_keys(p, ws, q0, min(32u, nq - q0), lane);
     drain_long(p, ws, nlong, lane);
+    MT(5);
+    MT_END;
     for (int d = 16; d; d >>= 1) my_tokens += __shfl_xor_sync(0xFFFFFFFFu, my_tokens, d);
     if (lane == 0 && my_tokens) atomicAdd(p.tokens, my_tokens);
     __syncthreads();

@@ -666,6 +666,7 @@ static int run_map_round(mr_ctx *ctx)
     p.max_token = MR_MAX_TOKEN_BYTES;
     p.tokens = &ctx->d_ctl->tokens;
     p.err = &ctx->d_ctl->err;
+    p.dbg = ctx->d_ctl->dbg;
     if (p.nseg) {
         cudaError_t e;
         switch (ctx->map_variant) {
@@ -1013,7 +1014,7 @@ int mr_result_next(mr_result *res, const char **key, uint64_t *klen, uint64_t *c
 
 void mr_result_release(mr_result *res) { delete res; }
 
-#ifdef MRGPU_SORT_TIMING
+#if defined(MRGPU_SORT_TIMING) || defined(MRGPU_MAP_TIMING)
 extern "C" const long long *mr_debug_stamps(mr_ctx *ctx) { return ctx->h_ctl->dbg; }
 #endif
 
