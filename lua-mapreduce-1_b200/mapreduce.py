@@ -305,7 +305,19 @@ class worker:
             self.ctx_kinds = kinds
         ctx = self.ctx
         records = kinds[0] == _native.MR_MAP_RECORDS_U32
-        ctx.job_begin()
+        # Map affinity across iterations (task.lua:279-293: in iteration > 1 a worker prefers the map
+        # jobs it ran before): when the waiting map jobs are exactly the ones whose splits this
+        # worker still holds in HBM, the splits are not staged again (mr_job_begin(keep_input)).
+        def signature(j):
+            v = j["value"]
+            return (j["_id"], v if isinstance(v, (str, bytes)) else id(v))
+
+        with b.lock:
+            wanted = [signature(j) for j in b.map_jobs]
+        resident = (b.task["iteration"] > 1 and getattr(self, "_resident", None) == (id(ctx), wanted)
+                    and len(wanted) > 0)
+        ctx.job_begin(keep_input=resident)
+        self.kept_input = resident
         # ---- map jobs (job.lua:166-227): stage every split this worker claims
         mine = []
         while True:
@@ -319,7 +331,9 @@ class worker:
             t0, c0 = time.time(), time.process_time()
             try:
                 value = job["value"]
-                if records:     # the map job's value is a (keys, values) pair of uint32 arrays
+                if resident:    # the split is already in HBM from the previous iteration
+                    pass
+                elif records:   # the map job's value is a (keys, values) pair of uint32 arrays
                     ctx.map_records(len(mine), value[0], value[1])
                 elif isinstance(value, (bytes, bytearray, memoryview)) or hasattr(value, "ctypes"):
                     ctx.map_split(len(mine), value)
@@ -342,6 +356,7 @@ class worker:
             self._mark(job, WRITTEN, written_time=time.time(), cpu_time=time.process_time() - c0,
                        real_time=time.time() - t0)
         self.last_info = info
+        self._resident = (id(ctx), wanted) if len(mine) == len(wanted) else None
         # ---- wait for the reduce phase, publish one reduce job per non-empty partition
         with b.lock:
             while b.task["status"] == TASK_MAP:

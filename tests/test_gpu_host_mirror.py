@@ -103,3 +103,39 @@ def test_group_by_sum_through_server_and_worker():
     keys = np.frombuffer(want.key_bytes.tobytes(), ">u4").tolist()
     assert seen == list(zip(keys, (int(c) for c in want.count)))
     w.ctx.close()
+
+
+def test_loop_iterations_keep_the_splits_resident(tmp_path):
+    # finalfn returning "loop" (server.lua:386-402) starts another iteration; the worker then finds
+    # the same map jobs and maps the splits it already holds in HBM (map affinity, task.lua:279-293)
+    splits, _ = corpus.generate(lines=[400, 300])
+    paths = []
+    for i, s_ in enumerate(splits):
+        p = tmp_path / f"s{i}.txt"
+        p.write_bytes(s_.tobytes())
+        paths.append(str(p))
+    want = O.run_staged(splits, 15, 2)
+    runs = []
+
+    class Final:
+        init = staticmethod(lambda arg=None: None)
+
+        @staticmethod
+        def finalfn(pairs_iterator):
+            runs.append([(k, v[0]) for k, v in pairs_iterator])
+            return "loop" if len(runs) < 3 else True
+
+    s = mapreduce.server.new("localhost", "loop-gpu")
+    s.configure({"taskfn": WordCount, "mapfn": WordCount, "partitionfn": WordCount, "reducefn": WordCount,
+                 "combinerfn": WordCount, "finalfn": Final, "init_args": {"files": paths, "num_reducers": 15}})
+    w = mapreduce.worker.new("localhost", "loop-gpu").configure({"max_iter": 2000, "max_tasks": 3,
+                                                                  "arena_bytes": 1 << 22, "max_keys": 1 << 17})
+    t = threading.Thread(target=w.execute)
+    t.start()
+    stats = s.loop()
+    t.join(60)
+    assert not t.is_alive() and stats["iteration"] == 3
+    expect = list(zip(want.keys(), (int(c) for c in want.count)))
+    assert runs == [expect, expect, expect]
+    assert w.kept_input is True and int(w.ctx.stats().h2d_bytes) == 0     # last iteration copied nothing
+    w.ctx.close()
