@@ -47,7 +47,12 @@ enum mr_map_kind {
     MR_MAP_RECORDS_U32 = 1, /* a mapfn that emits (number key, number value) records: emit, job.lua:83-97 */
     MR_MAP_BIGRAM_WS = 2    /* mapfn.lua:3-9 emitting (w_i .. " " .. w_{i+1}, 1) for neighbours inside a line */
 };
-enum mr_reduce_kind { MR_REDUCE_SUM_U64 = 0 };        /* examples/WordCount/reducefn.lua:1-5 */
+enum mr_reduce_kind {       /* reducefn = combinerfn; all associative, commutative, idempotent (job.lua:104-106) */
+    MR_REDUCE_SUM_U64 = 0,  /* examples/WordCount/reducefn.lua:1-5: emit(sum of values) */
+    MR_REDUCE_MIN_U64 = 1,  /* emit(math.min(unpack(values)))   -- records jobs only */
+    MR_REDUCE_MAX_U64 = 2,  /* emit(math.max(unpack(values)))   -- records jobs only */
+    MR_REDUCE_COUNT = 3     /* emit(number of values): a mapfn emitting (key, 1) with the sum reducer */
+};
 enum mr_partition_kind {
     MR_PARTITION_FNV1_LUA52 = 0, /* examples/WordCount/partitionfn.lua:8-16 (string keys) */
     MR_PARTITION_MOD_U32 = 1     /* partitionfn(key) = key % NUM_REDUCERS (number keys; job.lua:203-207) */

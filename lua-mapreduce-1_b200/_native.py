@@ -12,7 +12,7 @@ from . import build as _build
 
 MR_OK, MR_ERR_INVALID, MR_ERR_CUDA, MR_ERR_NOMEM, MR_ERR_OVERFLOW, MR_ERR_UNSUPPORTED, MR_ERR_END = range(7)
 MR_MAP_TOKENIZE_WS, MR_MAP_RECORDS_U32, MR_MAP_BIGRAM_WS = 0, 1, 2
-MR_REDUCE_SUM_U64 = 0
+MR_REDUCE_SUM_U64, MR_REDUCE_MIN_U64, MR_REDUCE_MAX_U64, MR_REDUCE_COUNT = 0, 1, 2, 3
 MR_PARTITION_FNV1_LUA52, MR_PARTITION_MOD_U32 = 0, 1
 
 # every symbol include/mrgpu.h declares
@@ -142,9 +142,10 @@ class Context:
     """One per worker process per GPU (include/mrgpu.h: mr_ctx)."""
 
     def __init__(self, num_reducers, arena_bytes, max_keys=0, table_slots=0, device=0, stream=None,
-                 world_size=1, rank=0, map_kind=MR_MAP_TOKENIZE_WS, partition_kind=MR_PARTITION_FNV1_LUA52):
+                 world_size=1, rank=0, map_kind=MR_MAP_TOKENIZE_WS, partition_kind=MR_PARTITION_FNV1_LUA52,
+                 reduce_kind=MR_REDUCE_SUM_U64):
         self._L = load()
-        cfg = Config(C.sizeof(Config), device, num_reducers, map_kind, MR_REDUCE_SUM_U64,
+        cfg = Config(C.sizeof(Config), device, num_reducers, map_kind, reduce_kind,
                      partition_kind, arena_bytes, max_keys, table_slots, stream, world_size, rank)
         h = C.c_void_p()
         rc = self._L.mr_ctx_create(C.byref(cfg), C.byref(h))

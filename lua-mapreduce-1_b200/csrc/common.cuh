@@ -211,6 +211,28 @@ __device__ inline uint32_t partition_of_key(const Key &k, const uint8_t *bytes, 
     return f.partition(num_reducers);
 }
 
+// ---------------------------------------------------------------- reducers
+// What is done with the values of one key (the task module's reducefn/combinerfn; all of them are
+// associative, commutative and idempotent in the sense of job.lua:104-106).  Tables are cleared to
+// zero, so every running value is kept in a form whose identity is 0: a sum as it is, a maximum as it
+// is, a minimum as its bitwise complement (then "min" is a max of complements).
+enum ReduceOp : uint32_t { OP_SUM = 0, OP_MIN = 1, OP_MAX = 2, OP_COUNT = 3 };
+
+__device__ __forceinline__ unsigned long long op_encode(uint32_t op, unsigned long long v)
+{
+    return op == OP_COUNT ? 1ull : (op == OP_MIN ? ~v : v);
+}
+__host__ __device__ __forceinline__ unsigned long long op_decode(uint32_t op, unsigned long long x)
+{
+    return op == OP_MIN ? ~x : x;
+}
+// merge an encoded value into a running encoded value
+__device__ __forceinline__ void op_apply(unsigned long long *addr, unsigned long long x, uint32_t op)
+{
+    if (op == OP_SUM || op == OP_COUNT) atomicAdd(addr, x);
+    else atomicMax(addr, x);
+}
+
 // ---------------------------------------------------------------- global table
 // Open addressing, linear probing, 32-byte slots {k0, k1, count, -}.  A key is claimed
 // with ONE 128-bit compare-and-swap on (k0, k1) and never changes afterwards; counts
@@ -235,7 +257,7 @@ __device__ __forceinline__ Key cas128(GEntry *slot, const Key &desired)
 }
 
 __device__ inline void gtable_add(GEntry *gt, uint32_t gmask, const uint8_t *bytes, const Key &key,
-                                  uint64_t n, unsigned int *err)
+                                  uint64_t n, unsigned int *err, uint32_t op = OP_SUM)
 {
     uint32_t slot = hash_key(key) & gmask;
     for (uint32_t probes = 0; probes < GT_MAX_PROBES; ++probes) {
@@ -247,7 +269,7 @@ __device__ inline void gtable_add(GEntry *gt, uint32_t gmask, const uint8_t *byt
             if (cur.k1 == 0) cur = key; // the slot is ours
         }
         if (same_key(cur, key, bytes)) {
-            atomicAdd(&gt[slot].cnt, (unsigned long long)n);
+            op_apply(&gt[slot].cnt, (unsigned long long)n, op);
             return;
         }
         slot = (slot + 1) & gmask;

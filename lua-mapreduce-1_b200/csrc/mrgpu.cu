@@ -402,7 +402,8 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     const bool text_job = (cfg->map_kind == MR_MAP_TOKENIZE_WS || cfg->map_kind == MR_MAP_BIGRAM_WS) &&
                           cfg->partition_kind == MR_PARTITION_FNV1_LUA52;
     const bool rec_job = cfg->map_kind == MR_MAP_RECORDS_U32 && cfg->partition_kind == MR_PARTITION_MOD_U32;
-    if (!(text_job || rec_job) || cfg->reduce_kind != MR_REDUCE_SUM_U64)
+    const bool red_ok = cfg->reduce_kind == MR_REDUCE_SUM_U64 || (rec_job && cfg->reduce_kind <= MR_REDUCE_COUNT);
+    if (!(text_job || rec_job) || !red_ok)
         return fail(nullptr, MR_ERR_UNSUPPORTED, "mr_ctx_create: unsupported map/reduce/partition kind");
     if (cfg->num_reducers == 0 || cfg->num_reducers > (1u << 24))
         return fail(nullptr, MR_ERR_INVALID, "mr_ctx_create: num_reducers must be in 1..2^24");
@@ -696,6 +697,7 @@ static int launch_records(mr_ctx *ctx, const mr_ctx::RecSplit &r)
     p.gmask = (uint32_t)(ctx->slots - 1);
     p.records = &ctx->d_ctl->tokens;
     p.err = &ctx->d_ctl->err;
+    p.op = ctx->cfg.reduce_kind;
     constexpr int LOG2 = 13;
     const size_t smem = (size_t)(1u << LOG2) * 16;
     CU(cudaFuncSetAttribute(map_records_kernel<LOG2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -828,8 +830,12 @@ int launch_rows(mr_ctx *ctx)
     CU(cudaMemsetAsync(ctx->rows_st.heads, 0, 3ull * ctx->rows_tiles * 8, s));
     CU(cudaMemsetAsync(&ctx->d_ctl->rows_ticket, 0, sizeof(unsigned int), s));
     rows_kernel<<<ctx->rows_tiles, ROWS_THREADS, 0, s>>>(ctx->bufs, ctx->ent, ctx->bytes_base, ctx->rows,
-                                                        ctx->cfg.num_reducers, ctx->key_bytes_cap - 64,
-                                                        ctx->rows_st, ctx->d_ctl);
+                                                        ctx->cfg.num_reducers, ctx->cfg.reduce_kind,
+                                                        ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl);
+    if (ctx->cfg.reduce_kind == MR_REDUCE_MIN_U64) {
+        rows_decode_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->rows, ctx->cfg.reduce_kind, ctx->d_ctl);
+        ctx->stats.launches += 1;
+    }
     ctx->stats.launches += 1;
     CU(cudaGetLastError());
     return MR_OK;

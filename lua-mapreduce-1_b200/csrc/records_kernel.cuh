@@ -20,6 +20,7 @@ struct RecordsParams {
     uint32_t gmask;
     unsigned long long *records; // running record count
     unsigned int *err;
+    uint32_t op;                 // ReduceOp
 };
 
 __device__ __forceinline__ Key key_of_u32(uint32_t k)
@@ -58,15 +59,16 @@ __global__ void __launch_bounds__(1024, 1) map_records_kernel(RecordsParams p)
             if (cur == 0) cur = atomicCAS(&bk[q], 0ull, sk) == 0 ? sk : *(volatile unsigned long long *)&bk[q];
             if (cur == sk) { way = q; break; }
         }
-        if (way >= 0) atomicAdd(&tsum[bucket * 4 + way], (unsigned long long)v);
-        else gtable_add(p.gtab, p.gmask, nullptr, key_of_u32(k), v, p.err);
+        const unsigned long long x = op_encode(p.op, v);
+        if (way >= 0) op_apply(&tsum[bucket * 4 + way], x, p.op);
+        else gtable_add(p.gtab, p.gmask, nullptr, key_of_u32(k), x, p.err, p.op);
     }
     for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d);
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(p.records, mine);
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < SLOTS; i += blockDim.x) {
         const unsigned long long sk = tkeys[i];
-        if (sk) gtable_add(p.gtab, p.gmask, nullptr, key_of_u32((uint32_t)sk), tsum[i], p.err);
+        if (sk) gtable_add(p.gtab, p.gmask, nullptr, key_of_u32((uint32_t)sk), tsum[i], p.err, p.op);
     }
 }
 

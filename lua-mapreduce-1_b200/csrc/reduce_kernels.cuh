@@ -636,7 +636,7 @@ __device__ __forceinline__ void write_key_bytes(uint8_t *dst, const Key &key, ui
 // across tiles with decoupled look-back; equal neighbours add their counts into the row
 // (the segmented reduce; integer adds, so the order of the atomics does not matter).
 __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, EntryArrays ent, const uint8_t *bytes,
-                                                           RowArrays rows, uint32_t num_reducers,
+                                                           RowArrays rows, uint32_t num_reducers, uint32_t op,
                                                            unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl)
 {
     __shared__ unsigned int wh[ROWS_THREADS / 32];
@@ -768,7 +768,7 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
         const bool next_known = j + 1 < ROWS_ITEMS;
         const bool next_head = next_known && (pos + 1 >= n || ((headmask >> (j + 1)) & 1u));
         if (head && next_head) rows.count[o - 1] = cnt[j];
-        else atomicAdd(&rows.count[o - 1], cnt[j]);
+        else op_apply(&rows.count[o - 1], cnt[j], op);
         if (pos == n - 1) { // totals and sentinels
             ctl->n_out = o;
             ctl->key_bytes = boff;
@@ -788,6 +788,15 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
             }
         }
     }
+}
+
+// rows of a MIN job hold complements until here (common.cuh, ReduceOp)
+__global__ void __launch_bounds__(256) rows_decode_kernel(RowArrays rows, uint32_t op, const Ctl *ctl)
+{
+    const uint64_t n = ctl->n_out;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        rows.count[i] = op_decode(op, rows.count[i]);
 }
 
 } // namespace mr

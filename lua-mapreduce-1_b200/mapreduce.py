@@ -38,7 +38,8 @@ DEFAULT_SLEEP = 0.01
 NATIVE_KINDS = {
     "map": {"tokenize_ws": _native.MR_MAP_TOKENIZE_WS, "records_u32": _native.MR_MAP_RECORDS_U32,
             "bigram_ws": _native.MR_MAP_BIGRAM_WS},
-    "reduce": {"sum_u64": _native.MR_REDUCE_SUM_U64},
+    "reduce": {"sum_u64": _native.MR_REDUCE_SUM_U64, "min_u64": _native.MR_REDUCE_MIN_U64,
+               "max_u64": _native.MR_REDUCE_MAX_U64, "count": _native.MR_REDUCE_COUNT},
     "partition": {"fnv1_lua52_double": _native.MR_PARTITION_FNV1_LUA52, "mod_u32": _native.MR_PARTITION_MOD_U32},
 }
 
@@ -296,12 +297,13 @@ class worker:
         mods = params["mods"]
         desc = self._native_config(mods)
         R = int(desc["num_reducers"])
-        kinds = (NATIVE_KINDS["map"][desc["map"]], NATIVE_KINDS["partition"][desc["partition"]])
+        kinds = (NATIVE_KINDS["map"][desc["map"]], NATIVE_KINDS["partition"][desc["partition"]],
+                 NATIVE_KINDS["reduce"][desc["reduce"]])
         if self.ctx is None or self.ctx.num_reducers != R or self.ctx_kinds != kinds:
             if self.ctx is not None:
                 self.ctx.close()
             self.ctx = _native.Context(R, self.arena_bytes, self.max_keys, device=self.device,
-                                       map_kind=kinds[0], partition_kind=kinds[1])
+                                       map_kind=kinds[0], partition_kind=kinds[1], reduce_kind=kinds[2])
             self.ctx_kinds = kinds
         ctx = self.ctx
         records = kinds[0] == _native.MR_MAP_RECORDS_U32

@@ -567,8 +567,9 @@ static int gb_cmp(const void *x, const void *y)
     return memcmp(a->ptr, b->ptr, 4);
 }
 
+/* op: 0 sum (reducefn.lua:1-5), 1 min, 2 max, 3 count of values */
 mro_result *mro_groupby_u32(const uint32_t *const *keys, const uint32_t *const *vals, const uint64_t *lens,
-                            uint32_t nsplits, uint32_t num_reducers)
+                            uint32_t nsplits, uint32_t num_reducers, int op)
 {
     uint64_t cap = 1u << 16, used = 0, records = 0;
     gb_slot *t = (gb_slot *)calloc(cap, sizeof(gb_slot));
@@ -587,8 +588,12 @@ mro_result *mro_groupby_u32(const uint32_t *const *keys, const uint32_t *const *
             uint32_t k = keys[s][i];
             uint64_t h = (k * 0x9E3779B1u) & (cap - 1);
             while (t[h].used && t[h].key != k) h = (h + 1) & (cap - 1);
-            if (!t[h].used) { t[h].used = 1; t[h].key = k; ++used; }
-            t[h].sum += vals[s][i];
+            uint64_t v = vals[s][i];
+            if (!t[h].used) { t[h].used = 1; t[h].key = k; ++used; t[h].sum = op == 1 ? v : (op == 2 ? v : 0); }
+            if (op == 0) t[h].sum += v;
+            else if (op == 1) t[h].sum = v < t[h].sum ? v : t[h].sum;
+            else if (op == 2) t[h].sum = v > t[h].sum ? v : t[h].sum;
+            else t[h].sum += 1;
             ++records;
         }
     row *rows = (row *)malloc((used + 1) * sizeof(row));

@@ -32,7 +32,7 @@ mro_result *mro_run_staged(const uint8_t *const *splits, const uint64_t *lens, u
 mro_result *mro_run_bigram(const uint8_t *const *splits, const uint64_t *lens, uint32_t nsplits,
                            uint32_t num_reducers);
 mro_result *mro_groupby_u32(const uint32_t *const *keys, const uint32_t *const *vals, const uint64_t *lens,
-                            uint32_t nsplits, uint32_t num_reducers);
+                            uint32_t nsplits, uint32_t num_reducers, int op);
 void mro_result_free(mro_result *r);
 
 void mro_heap_sort_u64(uint64_t *v, uint32_t n);

@@ -58,7 +58,7 @@ def lib():
                                      C.c_uint32, C.c_int]
         L.mro_groupby_u32.restype = C.POINTER(_Result)
         L.mro_groupby_u32.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
-                                      C.c_uint32, C.c_uint32]
+                                      C.c_uint32, C.c_uint32, C.c_int]
         L.mro_result_free.argtypes = [C.POINTER(_Result)]
         L.mro_heap_sort_u64.argtypes = [C.POINTER(C.c_uint64), C.c_uint32]
         L.mro_merge_kat.restype = C.c_uint32
@@ -143,7 +143,7 @@ def run_bigram(splits, num_reducers):
     return _take(lib().mro_run_bigram(ptrs, lens, n, num_reducers))
 
 
-def groupby_u32(splits, num_reducers):
+def groupby_u32(splits, num_reducers, op=0):
     """splits: list of (keys uint32 array, values uint32 array).  Group-by-sum on number keys
     (BASELINE config 5); key bytes in the rows are 4 big-endian bytes."""
     ks = [np.ascontiguousarray(k, dtype=np.uint32) for k, _ in splits]
@@ -152,7 +152,7 @@ def groupby_u32(splits, num_reducers):
     kp = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in ks])
     vp = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in vs])
     lens = (C.c_uint64 * max(n, 1))(*[a.size for a in ks])
-    return _take(lib().mro_groupby_u32(kp, vp, lens, n, num_reducers))
+    return _take(lib().mro_groupby_u32(kp, vp, lens, n, num_reducers, op))
 
 
 def fnv_lua52(key: bytes) -> int:

@@ -61,6 +61,25 @@ def main():
             dist.all_reduce(tot)
             assert int(tot.item()) == want.tokens
         ctx.close()
+    # number keys with a MIN reducer: the owner really merges (the same key arrives from several ranks)
+    rng = np.random.default_rng(17)
+    batches = [(rng.integers(0, 20000, 50000).astype(np.uint32), rng.integers(0, 2**32, 50000, dtype=np.uint64).astype(np.uint32))
+               for _ in range(2 * world + 1)]
+    for kind, op in ((_native.MR_REDUCE_MIN_U64, 1), (_native.MR_REDUCE_SUM_U64, 0)):
+        want = O.groupby_u32(batches, 10, op)
+        ctx = _native.Context(10, 1 << 24, max_keys=1 << 18, device=local_rank, stream=stream.cuda_stream,
+                              world_size=world, rank=rank, map_kind=_native.MR_MAP_RECORDS_U32,
+                              partition_kind=_native.MR_PARTITION_MOD_U32, reduce_kind=kind)
+        for i in parallel.shard_splits(len(batches), world, rank):
+            ctx.map_records(i, batches[i][0], batches[i][1])
+        ctx.map_finish()
+        parallel.shuffle(ctx)
+        ctx.reduce_all()
+        got = ctx.rows()
+        owned = np.array([parallel.owner_of_partition(int(p), world) == rank for p in want.part], dtype=bool)
+        assert got.n == int(owned.sum()) and np.array_equal(got.count, want.count[owned]), (rank, kind)
+        assert np.array_equal(got.keys_u32(), np.frombuffer(want.key_bytes.tobytes(), ">u4")[owned])
+        ctx.close()
     dist.barrier()
     dist.destroy_process_group()
     print(f"rank {rank}/{world}: multi-GPU parity ok")

@@ -91,3 +91,33 @@ def test_wrong_entry_point_is_refused():
     with pytest.raises(_native.NativeError) as e:       # records with the string partitioner: not built
         _native.Context(10, 1 << 20, map_kind=_native.MR_MAP_RECORDS_U32)
     assert e.value.code == _native.MR_ERR_UNSUPPORTED
+
+
+@pytest.mark.parametrize("kind,op", [(_native.MR_REDUCE_MIN_U64, 1), (_native.MR_REDUCE_MAX_U64, 2),
+                                     (_native.MR_REDUCE_COUNT, 3), (_native.MR_REDUCE_SUM_U64, 0)])
+def test_other_reducers(kind, op):
+    # f-3: min / max / count besides sum, same key order and partitioning
+    n = 400_000
+    keys, vals = skewed(n, 11, distinct=30_000)
+    vals = (vals * np.uint32(4_000_003)).astype(np.uint32)          # spread over the whole uint32 range
+    vals[::1000] = 0
+    vals[1::1000] = 0xFFFFFFFF
+    want = O.groupby_u32([(keys, vals)], 10, op)
+    ctx = ctx_for(10, n, reduce_kind=kind)
+    try:
+        for i, (a, b) in enumerate(zip(np.array_split(keys, 3), np.array_split(vals, 3))):
+            ctx.map_records(i, a, b)
+        got = ctx.rows()
+        assert_rows_equal(got, want, f"reduce kind {kind}")
+        ctx.job_begin(keep_input=True)
+        assert_rows_equal(ctx.rows(), want, f"reduce kind {kind}, keep_input")
+    finally:
+        ctx.close()
+    if op == 3:
+        assert int(got.count.sum()) == n
+
+
+def test_reducers_other_than_sum_need_a_records_job():
+    with pytest.raises(_native.NativeError) as e:
+        _native.Context(10, 1 << 20, reduce_kind=_native.MR_REDUCE_MAX_U64)
+    assert e.value.code == _native.MR_ERR_UNSUPPORTED
