@@ -192,6 +192,27 @@ int mr_shuffle_pack(mr_ctx *ctx, const uint64_t *counts, mr_shuffle_plan *plan);
  * MR_ERR_OVERFLOW (rerun the job with a larger slot or the exact-size path above). */
 int mr_shuffle_pack_fixed(mr_ctx *ctx, uint64_t slot_bytes, const uint8_t **send_base);
 int mr_shuffle_import_fixed(mr_ctx *ctx, uint64_t slot_bytes);
+
+/* The library's own transport for that all-to-all, for a host that has no collective library of
+ * its own (the reference's Lua worker: its shuffle medium is GridFS, job.lua:208-221 and
+ * utils.lua:176-186; here it is NCCL over NVLink).  libnccl.so.2 is opened at run time
+ * (override the path with MRGPU_NCCL_LIB); nothing else in the library needs it.
+ *   mr_nccl_unique_id  rank 0 makes the 128-byte rendezvous blob; the host hands it to the other
+ *                      ranks through its control plane (the task document every worker already
+ *                      polls, task.lua:96-116).
+ *   mr_nccl_init       collective over cfg.world_size contexts (one per process and GPU);
+ *                      cfg.rank is the NCCL rank.  Once per context.
+ *   mr_shuffle_nccl    after mr_map_finish: pack -> grouped ncclSend/ncclRecv of world_size slots
+ *                      -> import, all on the context's stream.  slot_bytes = 0 sizes the slots from
+ *                      this job (largest segment of any rank + 25 %, one all-reduce and one host
+ *                      synchronisation) and reports the size through *slot_used (may be NULL) so
+ *                      that later jobs of the same shape pass it back and run with no host
+ *                      synchronisation at all; overflow then surfaces as MR_ERR_OVERFLOW from
+ *                      mr_job_sync, as with mr_shuffle_pack_fixed. */
+#define MR_NCCL_ID_BYTES 128
+int mr_nccl_unique_id(uint8_t *id /* [MR_NCCL_ID_BYTES] */);
+int mr_nccl_init(mr_ctx *ctx, const uint8_t *id /* [MR_NCCL_ID_BYTES] */);
+int mr_shuffle_nccl(mr_ctx *ctx, uint64_t slot_bytes, uint64_t *slot_used);
 /* Reserve room for `bytes` incoming bytes; returns the device pointer to receive into. */
 int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr);
 /* recv_off: host array [world_size+1] of byte offsets per source inside the receive

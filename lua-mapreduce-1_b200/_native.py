@@ -22,6 +22,7 @@ EXPORTS = (
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
     "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
     "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
+    "mr_nccl_unique_id", "mr_nccl_init", "mr_shuffle_nccl",
     "mr_stats_get", "mr_partition_of", "mr_count_tokens_static",
 )
 
@@ -107,6 +108,9 @@ def load(build_if_missing=True):
     L.mr_shuffle_pack.argtypes = [vp, C.POINTER(u64), C.POINTER(ShufflePlan)]
     L.mr_shuffle_pack_fixed.argtypes = [vp, u64, C.POINTER(vp)]
     L.mr_shuffle_import_fixed.argtypes = [vp, u64]
+    L.mr_nccl_unique_id.argtypes = [C.c_char_p]
+    L.mr_nccl_init.argtypes = [vp, C.c_char_p]
+    L.mr_shuffle_nccl.argtypes = [vp, u64, C.POINTER(u64)]
     L.mr_shuffle_recv_buffer.argtypes = [vp, u64, C.POINTER(vp)]
     L.mr_shuffle_import.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
@@ -261,6 +265,18 @@ class Context:
     def shuffle_import_fixed(self, slot_bytes):
         self._ck(self._L.mr_shuffle_import_fixed(self._h, slot_bytes))
 
+    def nccl_init(self, unique_id):
+        """Collective: joins the library's own NCCL communicator (mr_nccl_init)."""
+        if len(unique_id) != NCCL_ID_BYTES:
+            raise ValueError("unique_id must be %d bytes" % NCCL_ID_BYTES)
+        self._ck(self._L.mr_nccl_init(self._h, bytes(unique_id)))
+
+    def shuffle_nccl(self, slot_bytes=0):
+        """pack -> all-to-all -> import inside the library; returns the slot size used."""
+        used = C.c_uint64(0)
+        self._ck(self._L.mr_shuffle_nccl(self._h, int(slot_bytes), C.byref(used)))
+        return used.value
+
     def shuffle_recv_buffer(self, nbytes):
         p = C.c_void_p()
         self._ck(self._L.mr_shuffle_recv_buffer(self._h, nbytes, C.byref(p)))
@@ -278,6 +294,19 @@ def partition_of(key: bytes, num_reducers: int) -> int:
 
 
 STATIC_MAX_BYTES = 128 * 1024
+NCCL_ID_BYTES = 128
+
+
+def nccl_unique_id():
+    """mr_nccl_unique_id: the rendezvous blob rank 0 hands to the other ranks."""
+    buf = C.create_string_buffer(NCCL_ID_BYTES)
+    L = load()
+    rc = L.mr_nccl_unique_id(buf)
+    if rc != MR_OK:
+        raise NativeError(rc, (L.mr_last_error(None) or b"").decode())
+    return buf.raw
+
+
 TOKEN_COUNT_DTYPE = np.dtype([("key", "S15"), ("len", np.uint8), ("count", np.uint64)])
 
 

@@ -2,6 +2,7 @@
 
   libmrgpu.so     CUDA kernels + C ABI (include/mrgpu.h), nvcc for sm_100a only
   libmrcorpus.so  synthetic corpus generator (host C)
+  examples/c_host/wordcount_host   a worker written in C against include/mrgpu.h alone
 """
 import os
 import shutil
@@ -12,6 +13,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_GPU = os.path.join(HERE, "libmrgpu.so")
 LIB_CORPUS = os.path.join(HERE, "libmrcorpus.so")
+C_HOST = os.path.join(HERE, "examples", "c_host", "wordcount_host")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -60,8 +62,18 @@ def build_corpus(force=False):
     return LIB_CORPUS
 
 
+def build_c_host(force=False):
+    """The C worker links libmrgpu.so by relative rpath, so the pair travels together."""
+    src = C_HOST + ".c"
+    if not force and not _newer(C_HOST, [src, LIB_GPU, os.path.join(ROOT, "include", "mrgpu.h")]):
+        return C_HOST
+    subprocess.check_call(["gcc", "-O2", "-std=gnu11", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", C_HOST, src,
+                           "-L", HERE, "-lmrgpu", "-Wl,-rpath,$ORIGIN/../.."])
+    return C_HOST
+
+
 def build_all(force=False, verbose=False):
-    return build_gpu(force, verbose), build_corpus(force)
+    return build_gpu(force, verbose), build_corpus(force), build_c_host(force)
 
 
 if __name__ == "__main__":

@@ -4,6 +4,7 @@
 #include "mrgpu.h"
 
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <cmath>
@@ -11,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -262,6 +264,7 @@ struct mr_ctx {
     std::vector<uint64_t> send_off, send_nrec;
     bool imported = false;
     bool shuffle_counted = false;
+    void *nccl_comm = nullptr; // mr_nccl_init: communicator of the library's own transport
 
     // state
     enum { IDLE, MAPPED, REDUCED, SYNCED } state = IDLE;
@@ -341,6 +344,7 @@ cudaError_t launch_map(mr_ctx *ctx, const MapParams &p)
 
 int run_general_ties(mr_ctx *ctx, uint32_t nt);
 int launch_rows(mr_ctx *ctx);
+void nccl_release(mr_ctx *ctx);
 
 } // namespace
 
@@ -371,6 +375,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    nccl_release(ctx);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab); cudaFree(ctx->d_pool);
     cudaFree(ctx->ent.e);
     for (int i = 0; i < 2; ++i) cudaFree(ctx->bufs.item[i]);
@@ -483,7 +488,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(cudaMallocHost((void **)&ctx->h_stage, (MAX_WORLD + 1) * 8));
     CUC(cudaMallocHost((void **)&ctx->h_gaps, (MAX_GAPS + 1) * sizeof(Gap)));
     CUC(dmalloc(&ctx->d_gaps, MAX_GAPS + 1));
-    CUC(dmalloc(&ctx->d_shuf, 5ull * cfg->world_size + 1));
+    CUC(dmalloc(&ctx->d_shuf, 5ull * cfg->world_size + 2)); // last word: largest segment (mr_shuffle_nccl)
     CUC(cudaEventCreate(&ctx->ev_map0)); CUC(cudaEventCreate(&ctx->ev_map1));
     CUC(cudaEventCreate(&ctx->ev_red0)); CUC(cudaEventCreate(&ctx->ev_red1));
     CUC(cudaEventCreateWithFlags(&ctx->ev_gaps, cudaEventDisableTiming));
@@ -1196,3 +1201,157 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
     return MR_OK;
 }
 
+
+// ------------------------------------------------- the library's own transport (NCCL)
+// A host without torch.distributed (the reference's Lua worker) still needs the all-to-all
+// between mr_shuffle_pack_fixed and mr_shuffle_import_fixed.  libnccl.so.2 is opened at run
+// time (no link-time dependency; the copy a host process already loaded is reused) and only
+// the point-to-point and all-reduce calls are bound.
+namespace {
+
+struct NcclId { char internal[MR_NCCL_ID_BYTES]; };
+typedef void *NcclComm;
+enum { NCCL_UINT8 = 1, NCCL_UINT64 = 5, NCCL_MAX = 2 }; // ncclDataType_t / ncclRedOp_t values of NCCL 2.x
+
+struct NcclApi {
+    void *lib = nullptr;
+    int (*GetUniqueId)(NcclId *) = nullptr;
+    int (*CommInitRank)(NcclComm *, int, NcclId, int) = nullptr;
+    int (*CommDestroy)(NcclComm) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void *, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*Recv)(void *, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    std::string why;
+};
+
+NcclApi g_nccl;
+std::once_flag g_nccl_once;
+
+void nccl_open()
+{
+    const char *names[] = { getenv("MRGPU_NCCL_LIB"), "libnccl.so.2", "libnccl.so" };
+    for (const char *n : names) {
+        if (!n || !*n) continue;
+        g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.lib) break;
+        g_nccl.why = dlerror();
+    }
+    if (!g_nccl.lib) return;
+    struct { const char *name; void **slot; } syms[] = {
+        { "ncclGetUniqueId", (void **)&g_nccl.GetUniqueId },   { "ncclCommInitRank", (void **)&g_nccl.CommInitRank },
+        { "ncclCommDestroy", (void **)&g_nccl.CommDestroy },   { "ncclGroupStart", (void **)&g_nccl.GroupStart },
+        { "ncclGroupEnd", (void **)&g_nccl.GroupEnd },         { "ncclSend", (void **)&g_nccl.Send },
+        { "ncclRecv", (void **)&g_nccl.Recv },                 { "ncclAllReduce", (void **)&g_nccl.AllReduce },
+        { "ncclGetErrorString", (void **)&g_nccl.GetErrorString },
+    };
+    for (auto &sy : syms) {
+        *sy.slot = dlsym(g_nccl.lib, sy.name);
+        if (!*sy.slot) {
+            g_nccl.why = std::string("libnccl lacks ") + sy.name;
+            g_nccl.lib = nullptr;
+            return;
+        }
+    }
+}
+
+const NcclApi *nccl_api()
+{
+    std::call_once(g_nccl_once, nccl_open);
+    return g_nccl.lib ? &g_nccl : nullptr;
+}
+
+#define NC(call)                                                                                   \
+    do {                                                                                           \
+        int r_ = (call);                                                                           \
+        if (r_ != 0)                                                                               \
+            return fail(ctx, MR_ERR_CUDA, "%s failed: %s", #call, g_nccl.GetErrorString(r_));     \
+    } while (0)
+
+void nccl_release(mr_ctx *ctx)
+{
+    if (ctx->nccl_comm && g_nccl.lib) g_nccl.CommDestroy((NcclComm)ctx->nccl_comm);
+    ctx->nccl_comm = nullptr;
+}
+
+// largest outgoing slot of this rank: header + records + long-key bytes, rounded as the packer does
+__global__ void segment_max_kernel(const unsigned long long *nrec, const unsigned long long *nbytes, uint32_t W,
+                                   unsigned long long *out)
+{
+    unsigned long long m = 0;
+    for (uint32_t d = threadIdx.x; d < W; d += 32) {
+        unsigned long long b = 16 + nrec[d] * REC_BYTES + nbytes[d];
+        m = max(m, (b + 15) / 16 * 16);
+    }
+    for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(~0u, m, o));
+    if (threadIdx.x == 0) *out = m;
+}
+
+} // namespace
+
+int mr_nccl_unique_id(uint8_t *id)
+{
+    mr_ctx *ctx = nullptr;
+    if (!id) return MR_ERR_INVALID;
+    const NcclApi *api = nccl_api();
+    if (!api) return fail(ctx, MR_ERR_CUDA, "libnccl.so.2 not loadable: %s", g_nccl.why.c_str());
+    NcclId nid;
+    NC(api->GetUniqueId(&nid));
+    memcpy(id, nid.internal, MR_NCCL_ID_BYTES);
+    return MR_OK;
+}
+
+int mr_nccl_init(mr_ctx *ctx, const uint8_t *id)
+{
+    if (!ctx || !id) return MR_ERR_INVALID;
+    const NcclApi *api = nccl_api();
+    if (!api) return fail(ctx, MR_ERR_CUDA, "libnccl.so.2 not loadable: %s", g_nccl.why.c_str());
+    if (ctx->nccl_comm) return fail(ctx, MR_ERR_INVALID, "mr_nccl_init: context already has a communicator");
+    CU(cudaSetDevice(ctx->cfg.device));
+    NcclId nid;
+    memcpy(nid.internal, id, MR_NCCL_ID_BYTES);
+    NcclComm comm = nullptr;
+    NC(api->CommInitRank(&comm, (int)ctx->cfg.world_size, nid, (int)ctx->cfg.rank));
+    ctx->nccl_comm = comm;
+    return MR_OK;
+}
+
+int mr_shuffle_nccl(mr_ctx *ctx, uint64_t slot_bytes, uint64_t *slot_used)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (!ctx->nccl_comm) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_nccl: call mr_nccl_init first");
+    const NcclApi *api = nccl_api();
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    NcclComm comm = (NcclComm)ctx->nccl_comm;
+    if (slot_bytes == 0) {
+        // size the slots from this job: largest segment over all ranks, plus a quarter (one host sync)
+        const uint64_t *dc;
+        if (!ctx->shuffle_counted) { int rc = mr_shuffle_count(ctx, &dc); if (rc) return rc; }
+        unsigned long long *d_max = ctx->d_shuf + 5ull * W + 1;
+        segment_max_kernel<<<1, 32, 0, s>>>(ctx->d_shuf, ctx->d_shuf + W, W, d_max);
+        ctx->stats.launches++;
+        NC(api->AllReduce(d_max, d_max, 1, NCCL_UINT64, NCCL_MAX, comm, s));
+        CU(cudaMemcpyAsync(ctx->h_stage, d_max, 8, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        const uint64_t m = ctx->h_stage[0];
+        slot_bytes = round_up(m + m / 4 + 16, 4096);
+    }
+    const uint8_t *send = nullptr;
+    void *recv = nullptr;
+    int rc = mr_shuffle_pack_fixed(ctx, slot_bytes, &send);
+    if (rc) return rc;
+    rc = mr_shuffle_recv_buffer(ctx, (uint64_t)W * slot_bytes, &recv);
+    if (rc) return rc;
+    NC(api->GroupStart());
+    for (uint32_t p = 0; p < W; ++p) {
+        NC(api->Send(send + (uint64_t)p * slot_bytes, slot_bytes, NCCL_UINT8, (int)p, comm, s));
+        NC(api->Recv((uint8_t *)recv + (uint64_t)p * slot_bytes, slot_bytes, NCCL_UINT8, (int)p, comm, s));
+    }
+    NC(api->GroupEnd());
+    if (slot_used) *slot_used = slot_bytes;
+    return mr_shuffle_import_fixed(ctx, slot_bytes);
+}

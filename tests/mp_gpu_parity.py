@@ -80,6 +80,41 @@ def main():
         assert got.n == int(owned.sum()) and np.array_equal(got.count, want.count[owned]), (rank, kind)
         assert np.array_equal(got.keys_u32(), np.frombuffer(want.key_bytes.tobytes(), ">u4")[owned])
         ctx.close()
+    # the library's own transport (mr_nccl_init / mr_shuffle_nccl): torch only carries the rendezvous
+    # blob here, as the host's control plane would; the all-to-all runs inside libmrgpu.so
+    blob = [_native.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(blob, src=0)
+    splits, _ = corpus.generate(lines=[1500, 1700, 1, 0, 900, 2500, 640], threads=4)
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    want = O.run_staged(splits, 10, 4)
+    ctx = _native.Context(10, 1 << 24, max_keys=1 << 19, device=local_rank, stream=stream.cuda_stream,
+                          world_size=world, rank=rank)
+    ctx.nccl_init(blob[0])
+    slot = 0
+    for it in range(3):
+        if it == 0:
+            for i in parallel.shard_splits(len(splits), world, rank):
+                ctx.map_split(i, splits[i])
+        else:
+            ctx.job_begin(keep_input=True)
+        ctx.map_finish()
+        used = ctx.shuffle_nccl(slot if it < 2 else 64)   # sized from the job, then re-used, then too small
+        ctx.reduce_all()
+        if it == 2:
+            try:
+                ctx.job_sync()
+                raise AssertionError("overflowing slot was not reported by the native transport")
+            except _native.NativeError as e:
+                assert e.code == _native.MR_ERR_OVERFLOW, e
+            continue
+        assert used >= 4096 and used % 4096 == 0 and (it == 0 or used == slot), (it, used, slot)
+        slot = used
+        got = ctx.rows()
+        owned = np.array([parallel.owner_of_partition(int(p), world) == rank for p in want.part], dtype=bool)
+        assert got.n == int(owned.sum()), (rank, got.n, int(owned.sum()))
+        assert got.keys() == [k for k, o in zip(want.keys(), owned) if o], f"rank {rank}: native transport keys differ"
+        assert np.array_equal(got.part, want.part[owned]) and np.array_equal(got.count, want.count[owned])
+    ctx.close()
     dist.barrier()
     dist.destroy_process_group()
     print(f"rank {rank}/{world}: multi-GPU parity ok")

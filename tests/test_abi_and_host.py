@@ -35,6 +35,22 @@ def test_no_gpu_fails_loudly():
     assert "no CPU path" in str(e.value)
 
 
+def test_c_worker_builds_against_the_header_alone(tmp_path):
+    # examples/c_host: gcc + include/mrgpu.h + libmrgpu.so, nothing else; without a GPU the
+    # worker must stop with the library's own error text, not fall back to anything
+    import subprocess
+    from lua_mapreduce_1_b200 import build as B
+    exe = B.build_c_host()
+    p = subprocess.run([exe], capture_output=True, text=True)
+    assert p.returncode == 2 and "usage" in p.stderr
+    if not _has_gpu():
+        f = tmp_path / "a.txt"
+        f.write_text("a b a")
+        p = subprocess.run([exe, "0", "1", "10", str(tmp_path / "id"), str(tmp_path), str(f)],
+                           capture_output=True, text=True)
+        assert p.returncode == 1 and "mr_ctx_create" in p.stderr and "no CPU path" in p.stderr
+
+
 def test_bad_config_is_rejected():
     lib = _native.load()
     h = ctypes.c_void_p()

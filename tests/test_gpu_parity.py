@@ -223,6 +223,31 @@ def test_config2_full_size_exact():
         ctx.close()
 
 
+def test_native_transport_single_rank():
+    # mr_nccl_init / mr_shuffle_nccl with a world of one: the slot goes to this rank itself
+    splits, tok = corpus.generate(lines=[700, 1, 0, 1300])
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    want = O.run_naive(splits, 10)
+    ctx = _native.Context(10, 1 << 22, max_keys=1 << 17)
+    try:
+        with pytest.raises(_native.NativeError):
+            ctx.shuffle_nccl()                       # no communicator yet
+        ctx.nccl_init(_native.nccl_unique_id())
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+        ctx.map_finish()
+        slot = ctx.shuffle_nccl()
+        ctx.reduce_all()
+        assert_rows_equal(ctx.rows(), want, "native transport")
+        ctx.job_begin(keep_input=True)
+        ctx.map_finish()
+        assert ctx.shuffle_nccl(slot) == slot        # no host synchronisation this time
+        ctx.reduce_all()
+        assert_rows_equal(ctx.rows(), want, "native transport, fixed slot")
+    finally:
+        ctx.close()
+
+
 def test_multi_gpu_shuffle_parity():
     # all visible GPUs (>= 2), one rank each, nccl all-to-all; skipped on a single-GPU box
     import os
