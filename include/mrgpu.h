@@ -121,8 +121,11 @@ int mr_job_begin(mr_ctx *ctx, int keep_input);
 /* Map job for one split: replaces the closure of job.lua:166-227 for
  * MR_MAP_TOKENIZE_WS, i.e. mapfn.lua:3-9 + emit (job.lua:83-97).  The bytes are
  * the content of the file the reference's taskfn names (taskfn.lua:8-11); they
- * are staged into the HBM arena (host pointer: host->device copy inside the
- * call).  Tokens never span splits. */
+ * are staged into the HBM arena by a host->device copy the call queues.  A
+ * pageable buffer may be reused as soon as the call returns; a page-locked
+ * (pinned) buffer is read by the copy engine asynchronously and must stay
+ * unchanged until mr_map_finish has returned and the stream has caught up
+ * (mr_job_sync, or any later result call).  Tokens never span splits. */
 int mr_map_split(mr_ctx *ctx, uint64_t split_id, const void *bytes, uint64_t n);
 /* Same with bytes already in device memory (device->device copy). */
 int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, uint64_t n);

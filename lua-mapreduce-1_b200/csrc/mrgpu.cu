@@ -234,7 +234,8 @@ struct mr_ctx {
     uint8_t *d_pool = nullptr; // bigram contexts: bytes of keys longer than 15 bytes
     Gap *h_gaps = nullptr;    // pinned
     Gap *d_gaps = nullptr;
-    uint32_t ngaps = 0;
+    uint32_t ngaps = 0;       // gaps collected since the last flush, at h_gaps[gap_base ..]
+    uint32_t gap_base = 0;    // the pinned list is a ring: earlier flushes may still be reading below this
 
     // tables and entries
     GEntry *d_gtab = nullptr;
@@ -546,16 +547,33 @@ static int run_map_round(mr_ctx *ctx);
 static int flush_gaps(mr_ctx *ctx)
 {
     if (!ctx->ngaps) return MR_OK;
-    CU(cudaMemcpyAsync(ctx->d_gaps, ctx->h_gaps, ctx->ngaps * sizeof(Gap), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_gaps, ctx->h_gaps + ctx->gap_base, ctx->ngaps * sizeof(Gap), cudaMemcpyHostToDevice, ctx->stream));
     // between splits: a space for the word count; a newline for bigrams (pairs never span splits)
     const uint8_t fill = ctx->cfg.map_kind == MR_MAP_BIGRAM_WS ? 0x0A : 0x20;
     fill_gaps_kernel<<<std::min<uint32_t>(ctx->ngaps, 1024u), 256, 0, ctx->stream>>>(ctx->d_arena, ctx->d_gaps, ctx->ngaps, fill);
     CU(cudaGetLastError());
-    // the pinned list is reused by later calls: wait until the copy above has read it
-    CU(cudaEventRecord(ctx->ev_gaps, ctx->stream));
+    CU(cudaEventRecord(ctx->ev_gaps, ctx->stream)); // marks the last read of the pinned list so far
     ctx->gaps_pending = true;
     ctx->stats.launches++;
+    ctx->gap_base += ctx->ngaps;
     ctx->ngaps = 0;
+    return MR_OK;
+}
+
+// Appends to the pinned gap list.  The host never waits for a flush in the steady state (a wait
+// here would drain the copy queue once per map round); only when the ring is used up does it
+// wait for the flushes behind it and start over at the front.
+static int gap_push(mr_ctx *ctx, uint64_t off, uint64_t len)
+{
+    if (ctx->gap_base + ctx->ngaps == MAX_GAPS) {
+        int rc = flush_gaps(ctx);
+        if (rc) return rc;
+        if (ctx->gaps_pending) { CU(cudaEventSynchronize(ctx->ev_gaps)); ctx->gaps_pending = false; }
+        ctx->gap_base = 0;
+    }
+    Gap &g = ctx->h_gaps[ctx->gap_base + ctx->ngaps++];
+    g.off = off;
+    g.len = len;
     return MR_OK;
 }
 
@@ -573,13 +591,7 @@ static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKin
     if (off + n + SEG > ctx->arena_cap)
         return fail(ctx, MR_ERR_NOMEM, "mr_map_split: arena full (%llu + %llu > %llu bytes)",
                     (unsigned long long)off, (unsigned long long)n, (unsigned long long)ctx->arena_cap);
-    if (ctx->gaps_pending) { CU(cudaEventSynchronize(ctx->ev_gaps)); ctx->gaps_pending = false; }
-    if (off > ctx->used) {
-        if (ctx->ngaps == MAX_GAPS) { int rc = flush_gaps(ctx); if (rc) return rc; }
-        ctx->h_gaps[ctx->ngaps].off = ctx->used;
-        ctx->h_gaps[ctx->ngaps].len = off - ctx->used;
-        ctx->ngaps++;
-    }
+    if (off > ctx->used) { int rc = gap_push(ctx, ctx->used, off - ctx->used); if (rc) return rc; }
     if (kind == cudaMemcpyHostToDevice) {
         // host->device copies run on their own stream so that they overlap the map rounds
         if (!ctx->copy_synced) {
@@ -631,11 +643,7 @@ static int run_map_round(mr_ctx *ctx)
     } else {
         // pad the tail with spaces up to a whole segment plus the look-ahead window
         end = round_up(std::max<uint64_t>(ctx->used, 1), SEG);
-        if (ctx->gaps_pending) { CU(cudaEventSynchronize(ctx->ev_gaps)); ctx->gaps_pending = false; }
-        if (ctx->ngaps == MAX_GAPS) { int rc = flush_gaps(ctx); if (rc) return rc; }
-        ctx->h_gaps[ctx->ngaps].off = ctx->used;
-        ctx->h_gaps[ctx->ngaps].len = end + TAIL_GUARD - ctx->used;
-        ctx->ngaps++;
+        { int rc = gap_push(ctx, ctx->used, end + TAIL_GUARD - ctx->used); if (rc) return rc; }
         { int rc = flush_gaps(ctx); if (rc) return rc; }
     }
     if (ctx->cfg.map_kind == MR_MAP_BIGRAM_WS) {

@@ -157,6 +157,24 @@ def test_incremental_map_finish_and_keep_input():
         ctx.close()
 
 
+def test_more_splits_than_the_gap_list_holds():
+    # the pinned list of inter-split gaps is a ring of 32768 entries that the host only waits on
+    # when it wraps: 70,000 tiny splits wrap it twice inside one job, a second job wraps it again
+    words = [b"w%d" % (i % 257) for i in range(70000)]
+    splits = [w + b" tail" if i % 3 else w for i, w in enumerate(words)]
+    want = O.run_naive(splits, 10)
+    ctx = _native.Context(10, 1 << 23, max_keys=1 << 16)
+    try:
+        for rep in range(2):
+            ctx.job_begin()
+            for i, s in enumerate(splits):
+                ctx.map_split(i, s)
+            ctx.reduce_all()
+            assert_rows_equal(ctx.rows(), want, f"job {rep}")
+    finally:
+        ctx.close()
+
+
 def test_partition_cursor_matches_rows():
     splits, _ = corpus.generate(lines=[800, 800])
     ctx = _native.Context(15, 1 << 21, max_keys=1 << 17)
