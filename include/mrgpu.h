@@ -216,6 +216,37 @@ int mr_shuffle_import_fixed(mr_ctx *ctx, uint64_t slot_bytes);
 int mr_nccl_unique_id(uint8_t *id /* [MR_NCCL_ID_BYTES] */);
 int mr_nccl_init(mr_ctx *ctx, const uint8_t *id /* [MR_NCCL_ID_BYTES] */);
 int mr_shuffle_nccl(mr_ctx *ctx, uint64_t slot_bytes, uint64_t *slot_used);
+
+/* Peer-to-peer shuffle for ranks of one NVLink domain: no staging buffer, no collective call.  Every
+ * rank owns a receive window in its HBM; the other ranks map it (CUDA IPC between processes, peer
+ * access between contexts of one process) and their pack kernel stores the records straight into
+ * the owner's slots over NVLink, then raises a flag there; the owner waits on its flags inside the
+ * kernel that indexes the window, and sorts/reduces the records where they lie.  Same seam as above
+ * (job.lua:208-221 write, job.lua:253-260 read).
+ *   mr_p2p_setup   allocates this rank's window for slots of slot_bytes (multiple of 32; two
+ *                  buffers of world_size slots, alternating per job) and fills *mine.
+ *   (the host exchanges the 128-byte mr_peer_info blobs: every rank needs all of them, in rank order)
+ *   mr_p2p_attach  maps every rank's window.  Collective in effect: call it on every rank after
+ *                  every rank's mr_p2p_setup, and call neither while a shuffle is in flight.
+ *   mr_shuffle_p2p after mr_map_finish, instead of the other shuffle calls; asynchronous, no host
+ *                  synchronisation.  A segment larger than the slot surfaces as MR_ERR_OVERFLOW from
+ *                  mr_job_sync on the sender and the owner (set the windows up again with larger
+ *                  slots); a rank that never delivers surfaces as MR_ERR_CUDA after 20 s.
+ * Fails with MR_ERR_UNSUPPORTED where the devices cannot map each other's memory; mr_shuffle_nccl
+ * is the transport for that case. */
+typedef struct mr_peer_info {
+    uint64_t pid;           /* process that owns the window */
+    uint64_t dev_ptr;       /* its address there (used by contexts of the same process) */
+    uint64_t win_bytes;
+    uint64_t slot_bytes;
+    int32_t device;
+    uint32_t rank;
+    uint8_t ipc_handle[64]; /* cudaIpcMemHandle_t */
+    uint8_t reserved[24];
+} mr_peer_info;
+int mr_p2p_setup(mr_ctx *ctx, uint64_t slot_bytes, mr_peer_info *mine);
+int mr_p2p_attach(mr_ctx *ctx, const mr_peer_info *all /* [world_size] */);
+int mr_shuffle_p2p(mr_ctx *ctx);
 /* Reserve room for `bytes` incoming bytes; returns the device pointer to receive into. */
 int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr);
 /* recv_off: host array [world_size+1] of byte offsets per source inside the receive

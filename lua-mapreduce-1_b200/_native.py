@@ -23,6 +23,7 @@ EXPORTS = (
     "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
     "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
     "mr_nccl_unique_id", "mr_nccl_init", "mr_shuffle_nccl",
+    "mr_p2p_setup", "mr_p2p_attach", "mr_shuffle_p2p",
     "mr_stats_get", "mr_partition_of", "mr_count_tokens_static",
 )
 
@@ -111,6 +112,9 @@ def load(build_if_missing=True):
     L.mr_nccl_unique_id.argtypes = [C.c_char_p]
     L.mr_nccl_init.argtypes = [vp, C.c_char_p]
     L.mr_shuffle_nccl.argtypes = [vp, u64, C.POINTER(u64)]
+    L.mr_p2p_setup.argtypes = [vp, u64, C.c_char_p]
+    L.mr_p2p_attach.argtypes = [vp, C.c_char_p]
+    L.mr_shuffle_p2p.argtypes = [vp]
     L.mr_shuffle_recv_buffer.argtypes = [vp, u64, C.POINTER(vp)]
     L.mr_shuffle_import.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
@@ -277,6 +281,22 @@ class Context:
         self._ck(self._L.mr_shuffle_nccl(self._h, int(slot_bytes), C.byref(used)))
         return used.value
 
+    def p2p_setup(self, slot_bytes):
+        """Allocates this rank's receive window; returns the 128-byte mr_peer_info blob for the peers."""
+        blob = C.create_string_buffer(PEER_INFO_BYTES)
+        self._ck(self._L.mr_p2p_setup(self._h, int(slot_bytes), blob))
+        return blob.raw
+
+    def p2p_attach(self, blobs):
+        """blobs: the mr_peer_info of every rank, in rank order."""
+        if len(blobs) != self.world_size or any(len(b) != PEER_INFO_BYTES for b in blobs):
+            raise ValueError("need one %d-byte blob per rank" % PEER_INFO_BYTES)
+        self._ck(self._L.mr_p2p_attach(self._h, b"".join(blobs)))
+
+    def shuffle_p2p(self):
+        """pack straight into the owners' windows -> flags -> index in place; asynchronous."""
+        self._ck(self._L.mr_shuffle_p2p(self._h))
+
     def shuffle_recv_buffer(self, nbytes):
         p = C.c_void_p()
         self._ck(self._L.mr_shuffle_recv_buffer(self._h, nbytes, C.byref(p)))
@@ -295,6 +315,7 @@ def partition_of(key: bytes, num_reducers: int) -> int:
 
 STATIC_MAX_BYTES = 128 * 1024
 NCCL_ID_BYTES = 128
+PEER_INFO_BYTES = 128
 
 
 def nccl_unique_id():

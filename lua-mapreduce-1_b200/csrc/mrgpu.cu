@@ -5,6 +5,7 @@
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cmath>
@@ -20,6 +21,7 @@
 #include "bigram_kernel.cuh"
 #include "records_kernel.cuh"
 #include "reduce_kernels.cuh"
+#include "p2p_kernels.cuh"
 
 using namespace mr;
 
@@ -54,6 +56,17 @@ __global__ void __launch_bounds__(256) fill_gaps_kernel(uint8_t *arena, const Ga
         const Gap gp = gaps[g];
         for (unsigned long long i = threadIdx.x; i < gp.len; i += blockDim.x) arena[gp.off + i] = fill;
     }
+}
+
+// what the owner's side of a shuffle starts from: counters of the reduce side cleared, token
+// count, error bits and key pool of the map side kept
+__global__ void ctl_owner_reset_kernel(Ctl *ctl)
+{
+    ctl->n = 0;
+    ctl->or_lo = 0; ctl->and_lo = ~0ull; ctl->or_hi = 0; ctl->and_hi = ~0u;
+    ctl->npasses = 0;
+    ctl->n_tie = 0; ctl->tie_overflow = 0; ctl->tie_small = 0; ctl->rows_ticket = 0;
+    ctl->n_out = 0; ctl->key_bytes = 0;
 }
 
 constexpr uint32_t MAX_WORLD = 1024;
@@ -267,6 +280,18 @@ struct mr_ctx {
     bool shuffle_counted = false;
     void *nccl_comm = nullptr; // mr_nccl_init: communicator of the library's own transport
 
+    // peer-to-peer shuffle (mr_p2p_setup / mr_p2p_attach / mr_shuffle_p2p), layout in p2p_kernels.cuh
+    GEntry *ent_own = nullptr;          // the context's own entry array (ent.e points into the window after a p2p shuffle)
+    uint8_t *p2p_win = nullptr;         // this rank's window
+    uint64_t p2p_slot = 0, p2p_win_bytes = 0;
+    std::vector<uint8_t *> p2p_peer;    // every rank's window as mapped in this process
+    std::vector<char> p2p_ipc;          // 1: opened with cudaIpcOpenMemHandle (to be closed)
+    uint8_t **d_p2p_buf = nullptr;      // device [2][world]: the peers' buffers per parity
+    uint8_t **d_p2p_win = nullptr;      // device [world]
+    unsigned int *d_p2p_done = nullptr;
+    uint64_t p2p_epoch = 0;
+    bool p2p_attached = false;
+
     // state
     enum { IDLE, MAPPED, REDUCED, SYNCED } state = IDLE;
     bool map_dirty = false; // splits staged since the last mr_map_finish
@@ -346,6 +371,7 @@ cudaError_t launch_map(mr_ctx *ctx, const MapParams &p)
 int run_general_ties(mr_ctx *ctx, uint32_t nt);
 int launch_rows(mr_ctx *ctx);
 void nccl_release(mr_ctx *ctx);
+void p2p_release(mr_ctx *ctx);
 
 } // namespace
 
@@ -377,8 +403,9 @@ void mr_ctx_destroy(mr_ctx *ctx)
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     nccl_release(ctx);
+    p2p_release(ctx);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab); cudaFree(ctx->d_pool);
-    cudaFree(ctx->ent.e);
+    cudaFree(ctx->ent_own);
     for (int i = 0; i < 2; ++i) cudaFree(ctx->bufs.item[i]);
     cudaFree(ctx->d_status); cudaFree(ctx->d_ties); cudaFree(ctx->d_posv);
     cudaFree(ctx->rows_st.heads);
@@ -471,6 +498,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->d_gtab, slots));
     if (cfg->map_kind == MR_MAP_BIGRAM_WS) CUC(dmalloc(&ctx->d_pool, 2 * ctx->arena_cap + ARENA_SLACK));
     CUC(dmalloc(&ctx->ent.e, mk));
+    ctx->ent_own = ctx->ent.e;
     for (int i = 0; i < 2; ++i) {
         CUC(dmalloc(&ctx->bufs.item[i], mk));
     }
@@ -530,6 +558,7 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
     ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(ctx->d_ctl);
     CU(cudaGetLastError());
     ctx->bytes_base = ctx->d_pool ? ctx->d_pool : ctx->d_arena;
+    ctx->ent.e = ctx->ent_own;
     ctx->imported = false;
     ctx->shuffle_counted = false;
     ctx->state = mr_ctx::IDLE;
@@ -796,15 +825,21 @@ int mr_map_finish(mr_ctx *ctx)
 
 namespace {
 
-// table -> entries (+ partition, sort keys).  Idempotent guard: done once per job.
-int launch_compact(mr_ctx *ctx)
+// table -> entries with partition ids, plus sort items (tally == false) or per-owner tallies for
+// the peer-to-peer shuffle (tally == true); one read of the table either way
+int launch_compact(mr_ctx *ctx, bool tally = false)
 {
     const uint64_t tiles = (ctx->slots + 256 * COMPACT_ITEMS - 1) / (256 * COMPACT_ITEMS);
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
-    compact_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_gtab, ctx->slots, ctx->ent, ctx->max_keys, ctx->d_ctl);
-    partition_entries_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
-        ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent, ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
-    ctx->stats.launches += 2;
+    if (tally)
+        compact_partition_kernel<1><<<grid, 256, 0, ctx->stream>>>(
+            ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
+            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->cfg.world_size, ctx->d_shuf, ctx->d_shuf + ctx->cfg.world_size);
+    else
+        compact_partition_kernel<0><<<grid, 256, 0, ctx->stream>>>(
+            ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
+            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, 1, nullptr, nullptr);
+    ctx->stats.launches += 1;
     CU(cudaGetLastError());
     return MR_OK;
 }
@@ -883,6 +918,9 @@ int check_device_err(mr_ctx *ctx, unsigned err)
                     (unsigned long long)ctx->slots);
     if (err & ERR_SHUFFLE_FULL)
         return fail(ctx, MR_ERR_OVERFLOW, "a shuffle segment does not fit the fixed slot: use a larger slot_bytes or the exact-size path");
+    if (err & ERR_PEER_TIMEOUT)
+        return fail(ctx, MR_ERR_CUDA, "peer-to-peer shuffle: a rank did not deliver its records within %llu s",
+                    P2P_TIMEOUT_NS / 1000000000ull);
     if (err & ERR_KEYS_FULL)
         return fail(ctx, MR_ERR_NOMEM, "more distinct keys (or key bytes) than max_keys=%llu allows",
                     (unsigned long long)ctx->max_keys);
@@ -1362,4 +1400,155 @@ int mr_shuffle_nccl(mr_ctx *ctx, uint64_t slot_bytes, uint64_t *slot_used)
     NC(api->GroupEnd());
     if (slot_used) *slot_used = slot_bytes;
     return mr_shuffle_import_fixed(ctx, slot_bytes);
+}
+
+// ------------------------------------------------- peer-to-peer shuffle (p2p_kernels.cuh)
+namespace {
+
+void p2p_release(mr_ctx *ctx)
+{
+    for (size_t r = 0; r < ctx->p2p_peer.size(); ++r)
+        if (ctx->p2p_ipc[r] && ctx->p2p_peer[r]) cudaIpcCloseMemHandle(ctx->p2p_peer[r]);
+    ctx->p2p_peer.clear();
+    ctx->p2p_ipc.clear();
+    cudaFree(ctx->p2p_win); ctx->p2p_win = nullptr;
+    cudaFree(ctx->d_p2p_buf); ctx->d_p2p_buf = nullptr;
+    cudaFree(ctx->d_p2p_win); ctx->d_p2p_win = nullptr;
+    cudaFree(ctx->d_p2p_done); ctx->d_p2p_done = nullptr;
+    ctx->p2p_attached = false;
+    ctx->p2p_slot = 0;
+}
+
+} // namespace
+
+static_assert(sizeof(mr_peer_info) == 128, "mr_peer_info is part of the ABI");
+static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(((mr_peer_info *)0)->ipc_handle), "IPC handle size");
+
+int mr_p2p_setup(mr_ctx *ctx, uint64_t slot_bytes, mr_peer_info *mine)
+{
+    if (!ctx || !mine) return MR_ERR_INVALID;
+    if (slot_bytes < 64 || slot_bytes % 32) return fail(ctx, MR_ERR_INVALID, "mr_p2p_setup: slot_bytes must be a multiple of 32, >= 64");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    if (2ull * W * slot_bytes + ARENA_SLACK >= MAX_BYTE_SPACE) return fail(ctx, MR_ERR_NOMEM, "mr_p2p_setup: window too large");
+    CU(cudaStreamSynchronize(ctx->stream));
+    p2p_release(ctx);
+    ctx->p2p_slot = slot_bytes;
+    ctx->p2p_win_bytes = P2P_FLAG_BYTES + 2ull * W * slot_bytes + 256;
+    CU(cudaMalloc((void **)&ctx->p2p_win, ctx->p2p_win_bytes));
+    CU(cudaMemset(ctx->p2p_win, 0, P2P_FLAG_BYTES)); // flags: no epoch seen yet
+    CU(dmalloc(&ctx->d_p2p_buf, 2ull * W));
+    CU(dmalloc(&ctx->d_p2p_win, W));
+    CU(dmalloc(&ctx->d_p2p_done, 1));
+    CU(cudaMemset(ctx->d_p2p_done, 0, sizeof(unsigned int)));
+    ctx->p2p_epoch = 0;
+    memset(mine, 0, sizeof *mine);
+    mine->pid = (uint64_t)getpid();
+    mine->dev_ptr = (uint64_t)(uintptr_t)ctx->p2p_win;
+    mine->win_bytes = ctx->p2p_win_bytes;
+    mine->slot_bytes = slot_bytes;
+    mine->device = ctx->cfg.device;
+    mine->rank = ctx->cfg.rank;
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, ctx->p2p_win));
+    memcpy(mine->ipc_handle, &h, sizeof h);
+    return MR_OK;
+}
+
+int mr_p2p_attach(mr_ctx *ctx, const mr_peer_info *all)
+{
+    if (!ctx || !all) return MR_ERR_INVALID;
+    if (!ctx->p2p_win) return fail(ctx, MR_ERR_INVALID, "mr_p2p_attach: call mr_p2p_setup first");
+    if (ctx->p2p_attached) return fail(ctx, MR_ERR_INVALID, "mr_p2p_attach: already attached (mr_p2p_setup starts over)");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->cfg.world_size;
+    ctx->p2p_peer.assign(W, nullptr);
+    ctx->p2p_ipc.assign(W, 0);
+    for (uint32_t r = 0; r < W; ++r) {
+        const mr_peer_info &pi = all[r];
+        if (pi.rank != r) return fail(ctx, MR_ERR_INVALID, "mr_p2p_attach: entry %u describes rank %u", r, pi.rank);
+        if (pi.slot_bytes != ctx->p2p_slot)
+            return fail(ctx, MR_ERR_INVALID, "mr_p2p_attach: rank %u uses slot_bytes %llu, this rank %llu", r,
+                        (unsigned long long)pi.slot_bytes, (unsigned long long)ctx->p2p_slot);
+        if (r == ctx->cfg.rank) {
+            if (pi.dev_ptr != (uint64_t)(uintptr_t)ctx->p2p_win) return fail(ctx, MR_ERR_INVALID, "mr_p2p_attach: entry %u is not this context's window", r);
+            ctx->p2p_peer[r] = ctx->p2p_win;
+        } else if (pi.pid == (uint64_t)getpid()) {
+            // another context of this process: the pointer is valid here, the device must be reachable
+            if (pi.device != ctx->cfg.device) {
+                int can = 0;
+                CU(cudaDeviceCanAccessPeer(&can, ctx->cfg.device, pi.device));
+                if (!can) return fail(ctx, MR_ERR_UNSUPPORTED, "mr_p2p_attach: device %d cannot reach device %d", ctx->cfg.device, pi.device);
+                cudaError_t e = cudaDeviceEnablePeerAccess(pi.device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else if (e != cudaSuccess) return fail(ctx, MR_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d): %s", pi.device, cudaGetErrorString(e));
+            }
+            ctx->p2p_peer[r] = (uint8_t *)(uintptr_t)pi.dev_ptr;
+        } else {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, pi.ipc_handle, sizeof h);
+            void *ptr = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return fail(ctx, MR_ERR_UNSUPPORTED, "mr_p2p_attach: cannot map the window of rank %u (%s); use mr_shuffle_nccl", r, cudaGetErrorString(e));
+            }
+            ctx->p2p_peer[r] = (uint8_t *)ptr;
+            ctx->p2p_ipc[r] = 1;
+        }
+    }
+    std::vector<uint8_t *> tab(3ull * W);
+    for (uint32_t r = 0; r < W; ++r) {
+        tab[r] = ctx->p2p_peer[r] + P2P_FLAG_BYTES;                                          // parity 0
+        tab[W + r] = ctx->p2p_peer[r] + P2P_FLAG_BYTES + (uint64_t)W * ctx->p2p_slot;        // parity 1
+        tab[2ull * W + r] = ctx->p2p_peer[r];
+    }
+    CU(cudaMemcpy(ctx->d_p2p_buf, tab.data(), 2ull * W * sizeof(uint8_t *), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(ctx->d_p2p_win, tab.data() + 2ull * W, W * sizeof(uint8_t *), cudaMemcpyHostToDevice));
+    ctx->p2p_attached = true;
+    return MR_OK;
+}
+
+int mr_shuffle_p2p(mr_ctx *ctx)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    if (!ctx->p2p_attached) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_p2p: call mr_p2p_setup and mr_p2p_attach first");
+    if (ctx->state != mr_ctx::MAPPED || ctx->imported || ctx->shuffle_counted)
+        return fail(ctx, MR_ERR_INVALID, "mr_shuffle_p2p: call after mr_map_finish, once per job");
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (ctx->map_dirty) { int rc = mr_map_finish(ctx); if (rc) return rc; }
+    const uint32_t W = ctx->cfg.world_size;
+    cudaStream_t s = ctx->stream;
+    // sender: table -> entries with partition ids and tallies per owner (one kernel), then headers
+    // and records into the owners' slots and the flags (one kernel)
+    CU(cudaMemsetAsync(ctx->d_shuf, 0, (5ull * W + 1) * 8, s));
+    int rc = launch_compact(ctx, true);
+    if (rc) return rc;
+    unsigned long long *nrec = ctx->d_shuf, *nbytes = ctx->d_shuf + W, *rec_cur = ctx->d_shuf + 2 * W,
+                       *byte_cur = ctx->d_shuf + 3 * W;
+    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
+    const uint64_t epoch = ++ctx->p2p_epoch;
+    const uint32_t parity = (uint32_t)(epoch & 1);
+    P2PParams p;
+    p.peer_buf = ctx->d_p2p_buf + (uint64_t)parity * W;
+    p.peer_win = ctx->d_p2p_win;
+    p.world = W;
+    p.rank = ctx->cfg.rank;
+    p.slot_bytes = ctx->p2p_slot;
+    p.epoch = epoch;
+    p2p_scatter_kernel<<<g, 256, 0, s>>>(p, ctx->ent, ctx->bytes_base, nrec, nbytes, rec_cur, byte_cur, ctx->d_p2p_done,
+                                         ctx->max_keys, ctx->d_ctl);
+    // owner: a fresh control block (token count and errors kept), then index the window in place
+    uint8_t *mybuf = ctx->p2p_win + P2P_FLAG_BYTES + (uint64_t)parity * W * ctx->p2p_slot;
+    ctl_owner_reset_kernel<<<1, 1, 0, s>>>(ctx->d_ctl);
+    const uint32_t chunks = std::max<uint32_t>(1, std::min<uint32_t>(P2P_MAX_CHUNKS, (uint32_t)ctx->sm_count * 4 / W));
+    p2p_index_kernel<<<W * chunks, 256, 0, s>>>(mybuf, (const unsigned long long *)ctx->p2p_win, W, chunks, ctx->p2p_slot, epoch,
+                                                ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+    ctx->stats.launches += 3;
+    CU(cudaGetLastError());
+    ctx->ent.e = (GEntry *)mybuf;
+    ctx->bytes_base = mybuf;
+    ctx->imported = true;
+    ctx->shuffle_counted = true;
+    return MR_OK;
 }

@@ -173,6 +173,92 @@ __global__ void __launch_bounds__(256) compact_kernel(const GEntry *gt, uint64_t
     }
 }
 
+// table slots -> dense entries WITH their partition ids, in one read of the table.  A tile's
+// occupied slots are first packed side by side in shared memory, so that the partitioner (a
+// byte loop per key) runs on full warps although only a fraction of the slots is occupied.
+//   MODE 0  also builds the sort items and the varying-bit masks (single rank, exact shuffle)
+//   MODE 1  also tallies records / long-key bytes per owner rank (peer-to-peer shuffle)
+constexpr uint32_t TALLY_MAX_WORLD = 1024;
+template <int MODE>
+__global__ void __launch_bounds__(256) compact_partition_kernel(
+    const GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind,
+    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, uint32_t world, unsigned long long *nrec,
+    unsigned long long *nbytes)
+{
+    constexpr int ITEMS = COMPACT_ITEMS;
+    __shared__ ulonglong4 s_ent[256 * ITEMS];
+    __shared__ unsigned int wsum[8];
+    __shared__ unsigned long long s_base;
+    __shared__ unsigned int s_rec[MODE == 1 ? TALLY_MAX_WORLD : 1];
+    __shared__ unsigned long long s_bytes[MODE == 1 ? TALLY_MAX_WORLD : 1];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t tile_slots = 256 * ITEMS;
+    const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
+    uint32_t hi_or = 0, hi_and = ~0u;
+    uint64_t lo_or = 0, lo_and = ~0ull;
+    bool any = false;
+    if (MODE == 1) {
+        for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
+        __syncthreads();
+    }
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        ulonglong4 e[ITEMS];
+        uint32_t nocc = 0;
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
+            e[i] = make_ulonglong4(0, 0, 0, 0);
+            if (slot < nslots) e[i] = ld256(&gt[slot]);
+            nocc += e[i].y != 0;
+        }
+        uint32_t incl = nocc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        uint32_t woff = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { uint32_t c = wsum[w]; if (w < (int)warp) woff += c; total += c; }
+        if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n, (unsigned long long)total);
+        uint32_t pos = woff + incl - nocc;
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (e[i].y != 0) s_ent[pos++] = e[i];
+        __syncthreads();
+        const unsigned long long base = total ? s_base : 0;
+        for (uint32_t t = threadIdx.x; t < total; t += 256) {
+            const uint64_t idx = base + t;
+            if (idx >= max_keys) { atomicOr(&ctl->err, ERR_KEYS_FULL); continue; }
+            ulonglong4 v = s_ent[t];
+            Key key; key.k0 = v.x; key.k1 = v.y;
+            const uint32_t part = partition_kind == 1 ? __byte_perm((uint32_t)key.k0, 0, 0x0123) % num_reducers
+                                                      : partition_of_key(key, bytes, num_reducers);
+            v.w = part;
+            ((ulonglong4 *)ent.e)[idx] = v;
+            if (MODE == 0) {
+                const uint64_t chunk = sort_chunk(key, bytes, 0);
+                SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
+                items[idx] = it;
+                hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
+                any = true;
+            } else {
+                const uint32_t d = part % world;
+                atomicAdd(&s_rec[d], 1u);
+                if (key_is_long(key)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(key));
+            }
+        }
+        __syncthreads();
+    }
+    if (MODE == 0) {
+        orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
+    } else {
+        for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) {
+            if (s_rec[d]) atomicAdd(&nrec[d], (unsigned long long)s_rec[d]);
+            if (s_bytes[d]) atomicAdd(&nbytes[d], s_bytes[d]);
+        }
+    }
+}
+
 // dense entries -> partition id + sort item (+ which key bits vary at all)
 // partition_kind 0: the WordCount partitioner (Lua 5.2 double FNV, partitionfn.lua:8-16);
 // partition_kind 1: `key % NUM_REDUCERS` on a number key carried as 4 big-endian bytes

@@ -111,6 +111,24 @@ def shuffle(ctx, group=None, slot_bytes=None):
     return int(segment_bytes(matrix[:, :W], matrix[:, W:]).max())
 
 
+def p2p_slot_for(max_segment_bytes, headroom=1.25):
+    """Slot size for the peer-to-peer shuffle from the largest exact segment seen: its records are
+    32 bytes where the packed segments have 24, its header 32 where they have 16."""
+    return (int(max_segment_bytes * headroom * 4 / 3) + 32 + 4095) // 4096 * 4096
+
+
+def p2p_connect(ctx, slot_bytes, group=None):
+    """Collective: every rank sets up its receive window and maps everybody else's (the 128-byte
+    blobs travel through the process group, which stands for the host's control plane).  Raises
+    NativeError(MR_ERR_UNSUPPORTED) where peers cannot map each other's memory."""
+    mine = ctx.p2p_setup(int(slot_bytes))
+    blobs = [None] * ctx.world_size
+    dist.all_gather_object(blobs, mine, group=group)
+    ctx.p2p_attach(blobs)
+    dist.barrier(group=group)     # nobody signals into a window that is not there yet
+    return int(slot_bytes)
+
+
 def slot_for(max_segment_bytes, headroom=1.25):
     """A slot size for the fixed-slot shuffle from the largest exact segment seen (header included)."""
     return (int(max_segment_bytes * headroom) + 16 + 4095) // 4096 * 4096

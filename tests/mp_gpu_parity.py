@@ -115,6 +115,40 @@ def main():
         assert got.keys() == [k for k, o in zip(want.keys(), owned) if o], f"rank {rank}: native transport keys differ"
         assert np.array_equal(got.part, want.part[owned]) and np.array_equal(got.count, want.count[owned])
     ctx.close()
+    # peer-to-peer shuffle: records stored straight into the owners' windows (CUDA IPC), flags, no
+    # collective call in the data path; five jobs so that both buffers of the window are re-used
+    ctx = _native.Context(10, 1 << 24, max_keys=1 << 19, device=local_rank, stream=stream.cuda_stream,
+                          world_size=world, rank=rank)
+    for i in parallel.shard_splits(len(splits), world, rank):
+        ctx.map_split(i, splits[i])
+    ctx.map_finish()
+    biggest = parallel.shuffle(ctx)                       # exact sizes once, to size the slots
+    ctx.reduce_all(); ctx.job_sync()
+    parallel.p2p_connect(ctx, parallel.p2p_slot_for(biggest))
+    owned = np.array([parallel.owner_of_partition(int(p), world) == rank for p in want.part], dtype=bool)
+    wk = [k for k, o in zip(want.keys(), owned) if o]
+    for it in range(5):
+        ctx.job_begin(keep_input=True)
+        ctx.map_finish()
+        ctx.shuffle_p2p()
+        ctx.reduce_all()
+        got = ctx.rows()
+        assert got.n == int(owned.sum()), (rank, it, got.n, int(owned.sum()))
+        assert got.keys() == wk, f"rank {rank}: p2p keys differ in job {it}"
+        assert np.array_equal(got.part, want.part[owned]) and np.array_equal(got.count, want.count[owned])
+    dist.barrier()
+    parallel.p2p_connect(ctx, 64)                         # slots that cannot hold the segments
+    ctx.job_begin(keep_input=True)
+    ctx.map_finish()
+    ctx.shuffle_p2p()
+    ctx.reduce_all()
+    try:
+        ctx.job_sync()
+        raise AssertionError("overflowing p2p slot was not reported")
+    except _native.NativeError as e:
+        assert e.code == _native.MR_ERR_OVERFLOW, e
+    dist.barrier()
+    ctx.close()
     dist.barrier()
     dist.destroy_process_group()
     print(f"rank {rank}/{world}: multi-GPU parity ok")

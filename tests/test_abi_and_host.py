@@ -14,7 +14,7 @@ from lua_mapreduce_1_b200 import _native, corpus, mapreduce
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "mrgpu.h")).read()
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
-    declared = set(re.findall(r"\b(mr_[a-z_]+)\s*\(", hdr))
+    declared = set(re.findall(r"\b(mr_[a-z0-9_]+)\s*\(", hdr))
     assert declared == set(_native.EXPORTS)
     lib = _native.load()
     for name in declared:

@@ -266,6 +266,75 @@ def test_native_transport_single_rank():
         ctx.close()
 
 
+def test_p2p_shuffle_single_rank():
+    # the peer-to-peer shuffle with a world of one: the window is this context's own memory
+    splits, tok = corpus.generate(lines=[900, 1, 0, 1100])
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    want = O.run_naive(splits, 10)
+    ctx = _native.Context(10, 1 << 22, max_keys=1 << 17)
+    try:
+        for i, s in enumerate(splits):
+            ctx.map_split(i, s)
+        ctx.map_finish()
+        with pytest.raises(_native.NativeError):
+            ctx.shuffle_p2p()                        # no window yet
+        ctx.p2p_attach([ctx.p2p_setup(4 << 20)])
+        for it in range(3):
+            if it:
+                ctx.job_begin(keep_input=True)
+                ctx.map_finish()
+            ctx.shuffle_p2p()
+            ctx.reduce_all()
+            assert_rows_equal(ctx.rows(), want, f"p2p job {it}")
+        list(ctx.partition_cursor(3))                # cursors read the rows, not the window
+        ctx.p2p_attach([ctx.p2p_setup(64)])          # too small: reported, not written past the slot
+        ctx.job_begin(keep_input=True)
+        ctx.map_finish()
+        ctx.shuffle_p2p()
+        ctx.reduce_all()
+        with pytest.raises(_native.NativeError) as e:
+            ctx.job_sync()
+        assert e.value.code == _native.MR_ERR_OVERFLOW
+    finally:
+        ctx.close()
+
+
+def test_p2p_shuffle_two_contexts_in_one_process():
+    # one process driving two GPUs: the windows are reached through peer access, not IPC
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    splits, tok = corpus.generate(lines=[800, 1200, 1, 0, 950, 700, 1300])
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    want = O.run_naive(splits, 10)
+    ctxs = [_native.Context(10, 1 << 22, max_keys=1 << 17, device=r, world_size=2, rank=r) for r in range(2)]
+    try:
+        blobs = [c.p2p_setup(4 << 20) for c in ctxs]
+        for c in ctxs:
+            c.p2p_attach(blobs)
+        for it in range(3):
+            for r, c in enumerate(ctxs):
+                if it == 0:
+                    for i in range(r, len(splits), 2):
+                        c.map_split(i, splits[i])
+                else:
+                    c.job_begin(keep_input=True)
+                c.map_finish()
+            for c in ctxs:
+                c.shuffle_p2p()                      # asynchronous: neither call waits for the other rank
+            for c in ctxs:
+                c.reduce_all()
+            keys = want.keys()
+            for r, c in enumerate(ctxs):
+                got = c.rows()
+                owned = (want.part % 2) == r
+                assert got.keys() == [k for k, o in zip(keys, owned) if o], (it, r)
+                assert np.array_equal(got.count, want.count[owned]) and np.array_equal(got.part, want.part[owned])
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 def test_multi_gpu_shuffle_parity():
     # all visible GPUs (>= 2), one rank each, nccl all-to-all; skipped on a single-GPU box
     import os
