@@ -36,6 +36,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scale", type=int, default=1, help="corpus scale per rank (1 = config 2 shape)")
+    ap.add_argument("--shuffle", default="auto", choices=["auto", "p2p", "nccl"],
+                    help="N>1: peer-to-peer windows (auto: where the GPUs can map each other) or NCCL all-to-all")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -181,7 +183,21 @@ def main():
         for i, t in enumerate(pinned):
             ctx.map_split_ptr(i, t.data_ptr(), t.numel())
 
-    shuffle_slot = [None]   # None: exact-size shuffle (one host sync); then fixed slots, no sync
+    # first job: exact-size shuffle (one host sync) that measures the segments; after it either the
+    # peer-to-peer windows or fixed NCCL slots, neither with any host synchronisation
+    shuffle_slot = [None]
+    shuffle_kind = ["nccl all-to-all, exact sizes"]
+    biggest_seen = [0]
+
+    def do_shuffle():
+        if shuffle_kind[0].startswith("p2p"):
+            ctx.shuffle_p2p()
+            return
+        biggest = parallel.shuffle(ctx, slot_bytes=shuffle_slot[0])
+        if shuffle_slot[0] is None:
+            biggest_seen[0] = biggest
+            shuffle_slot[0] = parallel.slot_for(biggest)
+            shuffle_kind[0] = f"one nccl all-to-all (fixed {shuffle_slot[0]}-byte slots)"
 
     def job(resident):
         ctx.job_begin(keep_input=resident)
@@ -189,9 +205,7 @@ def main():
             stage_all()
         ctx.map_finish()
         if world > 1:
-            biggest = parallel.shuffle(ctx, slot_bytes=shuffle_slot[0])
-            if shuffle_slot[0] is None:
-                shuffle_slot[0] = parallel.slot_for(biggest)
+            do_shuffle()
         ctx.reduce_all()
 
     def barrier():
@@ -208,6 +222,15 @@ def main():
     if world > 1:
         dist.all_reduce(tot)
     tokens_total, bytes_total, rows_total, keybytes_total = [int(x) for x in tot.cpu()]
+    if world > 1 and args.shuffle != "nccl":
+        try:
+            slot = parallel.p2p_connect(ctx, parallel.p2p_slot_for(biggest_seen[0]))
+            shuffle_kind[0] = f"p2p: records stored straight into the owners' windows over NVLink ({slot}-byte slots), flags, no collective"
+        except _native.NativeError as e:
+            if args.shuffle == "p2p":
+                raise
+            if rank == 0:
+                print(f"[bench] peer-to-peer windows unavailable ({e}); using NCCL", file=sys.stderr)
 
     # ---- device-resident steps
     for _ in range(args.warmup):
@@ -227,7 +250,7 @@ def main():
         ctx.map_finish()
         ev[s][1].record()
         if world > 1:
-            parallel.shuffle(ctx, slot_bytes=shuffle_slot[0])
+            do_shuffle()
         ctx.reduce_all()
         ev[s][2].record()
         launches += int(ctx.stats().launches)
@@ -316,7 +339,7 @@ def main():
         "config": {"workload": f"config2 x{args.scale}: synthetic Europarl-shaped word count, {nper} splits/rank, R={R}",
                    "tokens": tokens_total, "input_bytes": bytes_total, "distinct_keys": rows_total,
                    "partitions": R, "seed": hex(SEED), "parallelism": f"splits sharded over {world} rank(s), "
-                   "owner = partition mod ranks, one all-to-all" + (f" (fixed {shuffle_slot[0]}-byte slots)" if world > 1 else ""),
+                   "owner = partition mod ranks" + (f", shuffle = {shuffle_kind[0]}" if world > 1 else ""),
                    "l2": "input per rank (294 MB) is larger than L2 (126 MB); no flush between steps"},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }))

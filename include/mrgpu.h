@@ -247,6 +247,24 @@ typedef struct mr_peer_info {
 int mr_p2p_setup(mr_ctx *ctx, uint64_t slot_bytes, mr_peer_info *mine);
 int mr_p2p_attach(mr_ctx *ctx, const mr_peer_info *all /* [world_size] */);
 int mr_shuffle_p2p(mr_ctx *ctx);
+
+/* Which rank reduces a key.  Default: partition mod world_size -- every result.P<p> lives on one
+ * rank, as one reduce job owns one partition in the reference (server.lua:316-324); with 10
+ * partitions on 8 ranks two ranks then carry twice the others' share.  mr_shuffle_set_owners
+ * replaces that by world_size-1 splitters (partition, sort word), ascending: rank r reduces the
+ * keys whose (partition, sort word) lies in [splitter r-1, splitter r), i.e. a contiguous range of
+ * the job's output order "partition ascending, then key ascending".  result.P<p> is then the
+ * concatenation, in rank order, of the slices mr_reduce_partition(p) returns on each rank (most of
+ * them empty).  The sort word of a key is its first 7 bytes, big-endian, in the top 56 bits and
+ * min(length, 8) in the low byte; keys equal in it stay together.  Every rank must install the
+ * same splitters (n = 0 returns to the default), between jobs.
+ *   mr_row_sort_word  (partition, sort word) of row `row` of the finished job on this rank: the
+ *                     host picks splitters at equal shares of a first job's rows
+ *                     (lua-mapreduce-1_b200/parallel.py: balance_owners).
+ *   mr_owner_of       the owner rank of a key under the installed splitters, on the host. */
+int mr_shuffle_set_owners(mr_ctx *ctx, uint32_t n, const uint32_t *part, const uint64_t *word);
+int mr_row_sort_word(mr_ctx *ctx, uint64_t row, uint32_t *part, uint64_t *word);
+int mr_owner_of(const mr_ctx *ctx, const void *key, uint64_t klen, uint32_t *owner);
 /* Reserve room for `bytes` incoming bytes; returns the device pointer to receive into. */
 int mr_shuffle_recv_buffer(mr_ctx *ctx, uint64_t bytes, void **dev_ptr);
 /* recv_off: host array [world_size+1] of byte offsets per source inside the receive

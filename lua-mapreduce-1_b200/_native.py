@@ -24,6 +24,7 @@ EXPORTS = (
     "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
     "mr_nccl_unique_id", "mr_nccl_init", "mr_shuffle_nccl",
     "mr_p2p_setup", "mr_p2p_attach", "mr_shuffle_p2p",
+    "mr_shuffle_set_owners", "mr_row_sort_word", "mr_owner_of",
     "mr_stats_get", "mr_partition_of", "mr_count_tokens_static",
 )
 
@@ -115,6 +116,9 @@ def load(build_if_missing=True):
     L.mr_p2p_setup.argtypes = [vp, u64, C.c_char_p]
     L.mr_p2p_attach.argtypes = [vp, C.c_char_p]
     L.mr_shuffle_p2p.argtypes = [vp]
+    L.mr_shuffle_set_owners.argtypes = [vp, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(u64)]
+    L.mr_row_sort_word.argtypes = [vp, u64, C.POINTER(C.c_uint32), C.POINTER(u64)]
+    L.mr_owner_of.argtypes = [vp, C.c_char_p, u64, C.POINTER(C.c_uint32)]
     L.mr_shuffle_recv_buffer.argtypes = [vp, u64, C.POINTER(vp)]
     L.mr_shuffle_import.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.mr_stats_get.argtypes = [vp, C.POINTER(Stats)]
@@ -224,6 +228,13 @@ class Context:
                                        out.part_begin.ctypes.data))
         return out
 
+    def rows_part_begin(self):
+        """part_begin of the finished job: rows of partition p are [part_begin[p], part_begin[p+1])."""
+        self.job_sync()
+        pb = np.empty(self.num_reducers + 1, np.uint64)
+        self._ck(self._L.mr_rows_fetch(self._h, None, None, None, None, pb.ctypes.data))
+        return pb
+
     def partition_cursor(self, part):
         """Iterates (key bytes, count) of one partition, keys ascending (result.P<part>)."""
         h = C.c_void_p()
@@ -280,6 +291,25 @@ class Context:
         used = C.c_uint64(0)
         self._ck(self._L.mr_shuffle_nccl(self._h, int(slot_bytes), C.byref(used)))
         return used.value
+
+    def set_owners(self, splitters):
+        """splitters: ascending list of (partition, sort word), world_size - 1 of them, or empty for
+        the default (owner = partition mod world_size).  Every rank installs the same list."""
+        n = len(splitters)
+        parts = (C.c_uint32 * max(n, 1))(*[int(p) for p, _ in splitters])
+        words = (C.c_uint64 * max(n, 1))(*[int(w) for _, w in splitters])
+        self._ck(self._L.mr_shuffle_set_owners(self._h, n, parts, words))
+
+    def row_sort_word(self, row):
+        """(partition, sort word) of one row of the finished job."""
+        p, w = C.c_uint32(), C.c_uint64()
+        self._ck(self._L.mr_row_sort_word(self._h, int(row), C.byref(p), C.byref(w)))
+        return int(p.value), int(w.value)
+
+    def owner_of(self, key):
+        o = C.c_uint32()
+        self._ck(self._L.mr_owner_of(self._h, bytes(key), len(key), C.byref(o)))
+        return int(o.value)
 
     def p2p_setup(self, slot_bytes):
         """Allocates this rank's receive window; returns the 128-byte mr_peer_info blob for the peers."""

@@ -165,6 +165,33 @@ __device__ inline uint64_t sort_chunk(const Key &k, const uint8_t *bytes, uint32
     return (bswap64(w) & ~0xFFull) | (rem < 8 ? rem : 8);
 }
 
+// ---------------------------------------------------------------- owner rank of a key
+// Which rank reduces a key.  Without splitters: partition mod world (every result.P<p> lives on
+// one rank, as one reduce job owns one partition in the reference, server.lua:316-324).  With
+// world-1 splitters (part, sort word of round 0), ascending: rank = number of splitters <= the
+// key's (part, word) -- contiguous ranges of the global order "partition, then key", so that the
+// ranks hold equal shares whatever the partition count, each result.P<p> being the concatenation
+// of at most a few ranks' slices in rank order.  Keys equal in (part, word) stay together.
+struct OwnerMap {
+    const unsigned long long *word; // [n] splitter sort words
+    const uint32_t *part;           // [n] splitter partitions
+    uint32_t n;                     // 0 or world - 1
+    uint32_t world;
+};
+
+__device__ __forceinline__ uint32_t owner_of(const OwnerMap &m, uint32_t part, uint64_t w /* sort_chunk(key, bytes, 0) */)
+{
+    if (m.n == 0) return part % m.world;
+    uint32_t lo = 0, hi = m.n; // first splitter greater than (part, w)
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        const uint32_t sp = m.part[mid];
+        const bool le = sp < part || (sp == part && m.word[mid] <= w);
+        if (le) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
 // ---------------------------------------------------------------- partitioner
 // examples/WordCount/partitionfn.lua:10-15.  Lua 5.2 numbers are IEEE binary64 and
 // `a % b = a - floor(a/b)*b`: h * prime can reach 2^57, so the product is rounded to 53

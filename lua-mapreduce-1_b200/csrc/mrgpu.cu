@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) export_count_kernel(EntryArrays ent, uint
     const uint64_t n = ctl->n;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        uint32_t d = ent.part(i) % world;
+        uint32_t d = ent.owner(i);
         atomicAdd(&s_rec[d], 1u);
         Key k = ent.key(i);
         if (key_is_long(k)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(k));
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
     for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
     __syncthreads();
     for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-        uint32_t d = ent.part(i) % world;
+        uint32_t d = ent.owner(i);
         atomicAdd(&s_rec[d], 1u);
         Key k = ent.key(i);
         if (key_is_long(k)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(k));
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
     }
     __syncthreads();
     for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-        uint32_t d = ent.part(i) % world;
+        uint32_t d = ent.owner(i);
         Key k = ent.key(i);
         uint8_t *seg = send + seg_off[d];
         unsigned long long r = s_rec_base[d] + atomicAdd(&s_rec[d], 1u);
@@ -292,6 +292,18 @@ struct mr_ctx {
     uint64_t p2p_epoch = 0;
     bool p2p_attached = false;
 
+    // owner ranks by key range (mr_shuffle_set_owners); none: owner = partition mod world_size
+    unsigned long long *d_split_word = nullptr;
+    uint32_t *d_split_part = nullptr;
+    std::vector<uint64_t> split_word;
+    std::vector<uint32_t> split_part;
+    OwnerMap owners() const
+    {
+        OwnerMap m;
+        m.word = d_split_word; m.part = d_split_part; m.n = (uint32_t)split_word.size(); m.world = cfg.world_size;
+        return m;
+    }
+
     // state
     enum { IDLE, MAPPED, REDUCED, SYNCED } state = IDLE;
     bool map_dirty = false; // splits staged since the last mr_map_finish
@@ -404,6 +416,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     nccl_release(ctx);
     p2p_release(ctx);
+    cudaFree(ctx->d_split_word); cudaFree(ctx->d_split_part);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_gtab); cudaFree(ctx->d_pool);
     cudaFree(ctx->ent_own);
     for (int i = 0; i < 2; ++i) cudaFree(ctx->bufs.item[i]);
@@ -518,6 +531,8 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(cudaMallocHost((void **)&ctx->h_gaps, (MAX_GAPS + 1) * sizeof(Gap)));
     CUC(dmalloc(&ctx->d_gaps, MAX_GAPS + 1));
     CUC(dmalloc(&ctx->d_shuf, 5ull * cfg->world_size + 2)); // last word: largest segment (mr_shuffle_nccl)
+    CUC(dmalloc(&ctx->d_split_word, cfg->world_size));
+    CUC(dmalloc(&ctx->d_split_part, cfg->world_size));
     CUC(cudaEventCreate(&ctx->ev_map0)); CUC(cudaEventCreate(&ctx->ev_map1));
     CUC(cudaEventCreate(&ctx->ev_red0)); CUC(cudaEventCreate(&ctx->ev_red1));
     CUC(cudaEventCreateWithFlags(&ctx->ev_gaps, cudaEventDisableTiming));
@@ -834,11 +849,11 @@ int launch_compact(mr_ctx *ctx, bool tally = false)
     if (tally)
         compact_partition_kernel<1><<<grid, 256, 0, ctx->stream>>>(
             ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
-            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->cfg.world_size, ctx->d_shuf, ctx->d_shuf + ctx->cfg.world_size);
+            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners(), ctx->d_shuf, ctx->d_shuf + ctx->cfg.world_size);
     else
         compact_partition_kernel<0><<<grid, 256, 0, ctx->stream>>>(
             ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
-            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, 1, nullptr, nullptr);
+            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners(), nullptr, nullptr);
     ctx->stats.launches += 1;
     CU(cudaGetLastError());
     return MR_OK;
@@ -1550,5 +1565,79 @@ int mr_shuffle_p2p(mr_ctx *ctx)
     ctx->bytes_base = mybuf;
     ctx->imported = true;
     ctx->shuffle_counted = true;
+    return MR_OK;
+}
+
+// ------------------------------------------------- owner ranks by key range
+namespace {
+
+// sort word of round 0 on the host: same value as sort_chunk(key, bytes, 0) in common.cuh
+uint64_t host_sort_word(const uint8_t *key, uint64_t len)
+{
+    uint64_t w = 0;
+    for (uint64_t i = 0; i < 7; ++i) w = (w << 8) | (i < len ? key[i] : 0);
+    return (w << 8) | (len < 8 ? len : 8);
+}
+
+} // namespace
+
+int mr_shuffle_set_owners(mr_ctx *ctx, uint32_t n, const uint32_t *part, const uint64_t *word)
+{
+    if (!ctx) return MR_ERR_INVALID;
+    const uint32_t W = ctx->cfg.world_size;
+    if (n != 0 && n != W - 1) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_set_owners: need 0 or world_size-1 = %u splitters, got %u", W - 1, n);
+    if (n && (!part || !word)) return MR_ERR_INVALID;
+    for (uint32_t i = 1; i < n; ++i)
+        if (part[i] < part[i - 1] || (part[i] == part[i - 1] && word[i] < word[i - 1]))
+            return fail(ctx, MR_ERR_INVALID, "mr_shuffle_set_owners: splitters must ascend");
+    if (ctx->state == mr_ctx::MAPPED && (ctx->shuffle_counted || ctx->imported))
+        return fail(ctx, MR_ERR_INVALID, "mr_shuffle_set_owners: a shuffle is under way");
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaStreamSynchronize(ctx->stream)); // earlier jobs may still read the old splitters
+    ctx->split_part.assign(part, part + n);
+    ctx->split_word.assign(word, word + n);
+    if (n) {
+        CU(cudaMemcpy(ctx->d_split_part, part, n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(ctx->d_split_word, word, n * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    }
+    return MR_OK;
+}
+
+int mr_owner_of(const mr_ctx *ctx, const void *key, uint64_t klen, uint32_t *owner)
+{
+    if (!ctx || !owner || (klen && !key)) return MR_ERR_INVALID;
+    uint32_t part;
+    if (ctx->cfg.partition_kind == MR_PARTITION_MOD_U32) { // number keys travel as 4 big-endian bytes
+        if (klen != 4) return MR_ERR_INVALID;
+        const uint8_t *b = (const uint8_t *)key;
+        part = ((uint32_t)b[0] << 24 | (uint32_t)b[1] << 16 | (uint32_t)b[2] << 8 | b[3]) % ctx->cfg.num_reducers;
+    } else {
+        part = mr_partition_of(key, klen, ctx->cfg.num_reducers);
+    }
+    if (ctx->split_word.empty()) { *owner = part % ctx->cfg.world_size; return MR_OK; }
+    const uint64_t w = host_sort_word((const uint8_t *)key, klen);
+    uint32_t r = 0;
+    while (r < ctx->split_word.size() &&
+           (ctx->split_part[r] < part || (ctx->split_part[r] == part && ctx->split_word[r] <= w))) ++r;
+    *owner = r;
+    return MR_OK;
+}
+
+int mr_row_sort_word(mr_ctx *ctx, uint64_t row, uint32_t *part, uint64_t *word)
+{
+    if (!ctx || !part || !word) return MR_ERR_INVALID;
+    if (ctx->state != mr_ctx::SYNCED) { int rc = mr_job_sync(ctx, nullptr); if (rc) return rc; }
+    if (row >= ctx->info.n_keys) return fail(ctx, MR_ERR_INVALID, "mr_row_sort_word: row %llu of %llu", (unsigned long long)row,
+                                             (unsigned long long)ctx->info.n_keys);
+    CU(cudaSetDevice(ctx->cfg.device));
+    uint64_t off[2];
+    uint8_t kb[8] = { 0 };
+    CU(cudaMemcpyAsync(off, ctx->rows.key_off + row, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(part, ctx->rows.part + row, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint64_t len = off[1] - off[0];
+    if (len) CU(cudaMemcpyAsync(kb, ctx->rows.key_bytes + off[0], len < 7 ? len : 7, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    *word = host_sort_word(kb, len);
     return MR_OK;
 }

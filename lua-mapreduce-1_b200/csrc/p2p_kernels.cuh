@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(256) p2p_scatter_kernel(P2PParams p, EntryArra
         for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
         __syncthreads();
         for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-            const uint32_t d = ent.part(i) % p.world;
+            const uint32_t d = ent.owner(i);
             atomicAdd(&s_rec[d], 1u);
             const Key k = ent.key(i);
             if (key_is_long(k)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(k));
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(256) p2p_scatter_kernel(P2PParams p, EntryArra
         for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
             const ulonglong4 e = ld256(&ent.e[i]);
             Key k; k.k0 = e.x; k.k1 = e.y;
-            const uint32_t d = (uint32_t)e.w % p.world;
+            const uint32_t d = (uint32_t)(e.w >> 32);
             const unsigned long long slot_at = (unsigned long long)p.rank * p.slot_bytes; // offset in the owner's buffer
             uint8_t *slot = p.peer_buf[d] + slot_at;
             const unsigned long long r = s_rec_base[d] + atomicAdd(&s_rec[d], 1u);

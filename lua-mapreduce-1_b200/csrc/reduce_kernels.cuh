@@ -71,6 +71,7 @@ struct EntryArrays {
     }
     __device__ __forceinline__ unsigned long long cnt(uint64_t i) const { return e[i].cnt; }
     __device__ __forceinline__ uint32_t part(uint64_t i) const { return (uint32_t)e[i].pad; }
+    __device__ __forceinline__ uint32_t owner(uint64_t i) const { return (uint32_t)(e[i].pad >> 32); } // set by compact_partition_kernel
 };
 
 // one 256-bit load (sm_100: ld.global.v4.u64), e.g. a whole table entry = one 32-byte sector
@@ -120,58 +121,9 @@ __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t 
     }
 }
 
-// table slots -> dense entries.  Order of entries is arbitrary.  One atomic per 1024-slot
-// tile reserves the output range (a per-warp atomic on one address costs ~1.4 ns each).
+// One atomic per 1024-slot tile reserves the output range (a per-warp atomic on one address
+// costs ~1.4 ns each).
 constexpr int COMPACT_ITEMS = 4;
-__global__ void __launch_bounds__(256) compact_kernel(const GEntry *gt, uint64_t nslots, EntryArrays ent,
-                                                      uint64_t max_keys, Ctl *ctl)
-{
-    __shared__ unsigned int wsum[8];
-    __shared__ unsigned long long s_base;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint64_t tile_slots = 256 * COMPACT_ITEMS;
-    const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
-    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        Key key[COMPACT_ITEMS];
-        uint32_t nocc = 0;
-#pragma unroll
-        for (int i = 0; i < COMPACT_ITEMS; ++i) {
-            uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
-            key[i].k0 = 0; key[i].k1 = 0;
-            if (slot < nslots) {
-                ulonglong2 v = __ldcg((const ulonglong2 *)&gt[slot]);
-                key[i].k0 = v.x; key[i].k1 = v.y;
-            }
-            nocc += key[i].k1 != 0;
-        }
-        uint32_t incl = nocc;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
-        if (lane == 31) wsum[warp] = incl;
-        __syncthreads();
-        uint32_t woff = 0, total = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) { uint32_t c = wsum[w]; if (w < (int)warp) woff += c; total += c; }
-        if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n, (unsigned long long)total);
-        __syncthreads();
-        if (total) {
-            uint64_t idx = s_base + woff + incl - nocc;
-#pragma unroll
-            for (int i = 0; i < COMPACT_ITEMS; ++i) {
-                if (key[i].k1 == 0) continue;
-                uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
-                if (idx < max_keys) {
-                    GEntry ge; ge.k0 = key[i].k0; ge.k1 = key[i].k1; ge.cnt = __ldcg(&gt[slot].cnt); ge.pad = 0;
-                    ((ulonglong4 *)ent.e)[idx] = *(ulonglong4 *)&ge;
-                } else {
-                    atomicOr(&ctl->err, ERR_KEYS_FULL);
-                }
-                ++idx;
-            }
-        }
-        __syncthreads();
-    }
-}
 
 // table slots -> dense entries WITH their partition ids, in one read of the table.  A tile's
 // occupied slots are first packed side by side in shared memory, so that the partitioner (a
@@ -182,7 +134,7 @@ constexpr uint32_t TALLY_MAX_WORLD = 1024;
 template <int MODE>
 __global__ void __launch_bounds__(256) compact_partition_kernel(
     const GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind,
-    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, uint32_t world, unsigned long long *nrec,
+    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, OwnerMap owners, unsigned long long *nrec,
     unsigned long long *nbytes)
 {
     constexpr int ITEMS = COMPACT_ITEMS;
@@ -198,7 +150,7 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
     if (MODE == 1) {
-        for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
+        for (uint32_t d = threadIdx.x; d < owners.world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
         __syncthreads();
     }
     for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -233,16 +185,17 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
             Key key; key.k0 = v.x; key.k1 = v.y;
             const uint32_t part = partition_kind == 1 ? __byte_perm((uint32_t)key.k0, 0, 0x0123) % num_reducers
                                                       : partition_of_key(key, bytes, num_reducers);
-            v.w = part;
+            const uint64_t chunk = sort_chunk(key, bytes, 0);
+            const uint32_t owner = owners.world > 1 ? owner_of(owners, part, chunk) : 0;
+            v.w = part | (unsigned long long)owner << 32; // EntryArrays::part / ::owner
             ((ulonglong4 *)ent.e)[idx] = v;
             if (MODE == 0) {
-                const uint64_t chunk = sort_chunk(key, bytes, 0);
                 SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
                 items[idx] = it;
                 hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
                 any = true;
             } else {
-                const uint32_t d = part % world;
+                const uint32_t d = owner;
                 atomicAdd(&s_rec[d], 1u);
                 if (key_is_long(key)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(key));
             }
@@ -252,7 +205,7 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
     if (MODE == 0) {
         orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
     } else {
-        for (uint32_t d = threadIdx.x; d < world; d += blockDim.x) {
+        for (uint32_t d = threadIdx.x; d < owners.world; d += blockDim.x) {
             if (s_rec[d]) atomicAdd(&nrec[d], (unsigned long long)s_rec[d]);
             if (s_bytes[d]) atomicAdd(&nbytes[d], s_bytes[d]);
         }

@@ -17,6 +17,8 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
+from . import _native
+
 REC_BYTES = 24
 
 
@@ -111,6 +113,47 @@ def shuffle(ctx, group=None, slot_bytes=None):
     return int(segment_bytes(matrix[:, :W], matrix[:, W:]).max())
 
 
+def split_rows(part_counts, world):
+    """Where the world-1 equal-share cut points of a finished job fall.  part_counts[r][p] = rows of
+    partition p held by rank r (within a partition the ranks' slices follow each other in rank
+    order, under either ownership rule).  Returns [(rank, row on that rank)] for cuts 1..world-1,
+    or [] for an empty job."""
+    c = np.asarray(part_counts, dtype=np.int64)
+    total = int(c.sum())
+    if total == 0:
+        return []
+    begins = np.concatenate([np.zeros((c.shape[0], 1), np.int64), np.cumsum(c, axis=1)], axis=1)  # per-rank part_begin
+    blocks = [(p, r) for p in range(c.shape[1]) for r in range(c.shape[0]) if c[r, p]]             # global output order
+    ends = np.cumsum([c[r, p] for p, r in blocks])
+    cuts = []
+    for j in range(1, world):
+        pos = j * total // world
+        b = int(np.searchsorted(ends, pos, side="right"))
+        p, r = blocks[b]
+        cuts.append((r, int(begins[r, p] + pos - (ends[b] - c[r, p]))))
+    return cuts
+
+
+def balance_owners(ctx, group=None):
+    """Collective, after a finished job on every rank: installs world-1 splitters at equal shares
+    of that job's rows, so that later jobs of the same shape give every rank the same number of
+    keys to merge (mr_shuffle_set_owners).  Returns the splitters."""
+    info = ctx.job_sync()
+    rows = ctx.rows_part_begin()
+    counts = [None] * ctx.world_size
+    dist.all_gather_object(counts, np.diff(rows.astype(np.int64)).tolist(), group=group)
+    cuts = split_rows(counts, ctx.world_size)
+    mine = {j: ctx.row_sort_word(row) for j, (r, row) in enumerate(cuts) if r == ctx.rank}
+    parts = [None] * ctx.world_size
+    dist.all_gather_object(parts, mine, group=group)
+    merged = {}
+    for d in parts:
+        merged.update(d)
+    splitters = [merged[j] for j in range(len(cuts))]
+    ctx.set_owners(splitters)
+    return splitters
+
+
 def p2p_slot_for(max_segment_bytes, headroom=1.25):
     """Slot size for the peer-to-peer shuffle from the largest exact segment seen: its records are
     32 bytes where the packed segments have 24, its header 32 where they have 16."""
@@ -119,13 +162,21 @@ def p2p_slot_for(max_segment_bytes, headroom=1.25):
 
 def p2p_connect(ctx, slot_bytes, group=None):
     """Collective: every rank sets up its receive window and maps everybody else's (the 128-byte
-    blobs travel through the process group, which stands for the host's control plane).  Raises
-    NativeError(MR_ERR_UNSUPPORTED) where peers cannot map each other's memory."""
+    blobs travel through the process group, which stands for the host's control plane).  Where any
+    rank cannot map a peer's memory, EVERY rank raises NativeError (so that all of them fall back to
+    another transport together)."""
     mine = ctx.p2p_setup(int(slot_bytes))
     blobs = [None] * ctx.world_size
     dist.all_gather_object(blobs, mine, group=group)
-    ctx.p2p_attach(blobs)
-    dist.barrier(group=group)     # nobody signals into a window that is not there yet
+    err = None
+    try:
+        ctx.p2p_attach(blobs)
+    except _native.NativeError as e:
+        err = e
+    ok = [None] * ctx.world_size
+    dist.all_gather_object(ok, err is None, group=group)   # also: nobody signals into a window that is not there yet
+    if not all(ok):
+        raise err or _native.NativeError(_native.MR_ERR_UNSUPPORTED, "a peer could not map the receive windows")
     return int(slot_bytes)
 
 

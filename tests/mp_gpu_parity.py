@@ -136,6 +136,34 @@ def main():
         assert got.n == int(owned.sum()), (rank, it, got.n, int(owned.sum()))
         assert got.keys() == wk, f"rank {rank}: p2p keys differ in job {it}"
         assert np.array_equal(got.part, want.part[owned]) and np.array_equal(got.count, want.count[owned])
+    # owners by key range: splitters at equal shares of this job's rows; every later job, through any
+    # of the three shuffles, leaves rank r with the r-th contiguous piece of the oracle's output order
+    splitters = parallel.balance_owners(ctx)
+    assert len(splitters) == world - 1 and splitters == sorted(splitters)
+    owner = np.array([ctx.owner_of(k) for k in want.keys()])
+    assert np.all(np.diff(owner) >= 0), "owner ranks must follow the output order"
+    share = np.bincount(owner, minlength=world)
+    assert share.max() - share.min() <= max(8, want.n // 50), share      # equal shares (keys equal in 7 bytes stay together)
+    mine = owner == rank
+    wk = [k for k, o in zip(want.keys(), mine) if o]
+    slot = None
+    for mode in ("exact", "fixed", "p2p", "p2p"):
+        ctx.job_begin(keep_input=True)
+        ctx.map_finish()
+        if mode == "p2p":
+            ctx.shuffle_p2p()
+        else:
+            biggest = parallel.shuffle(ctx, slot_bytes=slot)
+            slot = parallel.slot_for(biggest)
+        ctx.reduce_all()
+        got = ctx.rows()
+        assert got.n == int(mine.sum()), (rank, mode, got.n, int(mine.sum()))
+        assert got.keys() == wk, f"rank {rank}: keys differ with range owners, {mode} shuffle"
+        assert np.array_equal(got.part, want.part[mine]) and np.array_equal(got.count, want.count[mine])
+        if mode == "fixed":
+            parallel.p2p_connect(ctx, parallel.p2p_slot_for(biggest))
+    ctx.job_sync()
+    ctx.set_owners([])                                    # back to partition mod world
     dist.barrier()
     parallel.p2p_connect(ctx, 64)                         # slots that cannot hold the segments
     ctx.job_begin(keep_input=True)
