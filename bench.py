@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--scale", type=int, default=1, help="corpus scale per rank (1 = config 2 shape)")
     ap.add_argument("--shuffle", default="auto", choices=["auto", "p2p", "nccl"],
                     help="N>1: peer-to-peer windows (auto: where the GPUs can map each other) or NCCL all-to-all")
+    ap.add_argument("--mod-owners", action="store_true", help="N>1: owner = partition mod ranks instead of balanced key ranges")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -217,6 +218,16 @@ def main():
     job(False)
     info = ctx.job_sync()
     assert info.n_tokens == tokens_local, (info.n_tokens, tokens_local)
+    owners = "partition mod ranks"
+    if world > 1 and not args.mod_owners:
+        # equal shares of the output order per rank instead (10 partitions on 8 ranks would leave two
+        # ranks with twice the others' keys); one more exact-size job measures the new segments
+        parallel.balance_owners(ctx)
+        owners = "key ranges (splitters at equal shares of the first job's rows)"
+        shuffle_slot[0] = None
+        job(True)
+        info = ctx.job_sync()
+        assert info.n_tokens == tokens_local
     rows_n, key_bytes = int(info.n_keys), int(info.key_bytes)
     tot = torch.tensor([tokens_local, bytes_local, rows_n, key_bytes], dtype=torch.int64, device=dev)
     if world > 1:
@@ -339,7 +350,7 @@ def main():
         "config": {"workload": f"config2 x{args.scale}: synthetic Europarl-shaped word count, {nper} splits/rank, R={R}",
                    "tokens": tokens_total, "input_bytes": bytes_total, "distinct_keys": rows_total,
                    "partitions": R, "seed": hex(SEED), "parallelism": f"splits sharded over {world} rank(s), "
-                   "owner = partition mod ranks" + (f", shuffle = {shuffle_kind[0]}" if world > 1 else ""),
+                   f"owner = {owners}" + (f", shuffle = {shuffle_kind[0]}" if world > 1 else ""),
                    "l2": "input per rank (294 MB) is larger than L2 (126 MB); no flush between steps"},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }))
