@@ -864,9 +864,8 @@ int launch_sort(mr_ctx *ctx)
     cudaStream_t s = ctx->stream;
     CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
     CU(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
-    sort_setup_kernel<<<1, 32, 0, s>>>(ctx->d_ctl, ctx->max_keys);
-    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->d_ctl);
-    ctx->stats.launches += 2;
+    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+    ctx->stats.launches += 1;
     // the sort key has 64 chunk bits plus the bits of the largest partition id: more passes than
     // that can never be needed (which ones are needed is decided on the device)
     uint32_t part_bits = 0;

@@ -278,19 +278,61 @@ __device__ __forceinline__ uint32_t extract_digit(const DigitRun *runs, uint32_t
     return d;
 }
 
-// digit histograms of every pass in one read of the keys
-__global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, Ctl *ctl)
+// The digit plan again, run by run instead of bit by bit, into whatever arrays the caller has
+// (shared memory in radix_hist_kernel).  Same plan as sort_setup_kernel.
+__device__ inline uint32_t build_digit_plan(uint64_t vlo, uint32_t vhi, DigitRun (*runs)[8], unsigned int *nruns)
+{
+    uint32_t pass = 0, used = 0, nr = 0;
+    for (int half = 0; half < 2; ++half) {
+        uint64_t v = half ? (uint64_t)vhi : vlo; // runs do not straddle the lo/hi boundary
+        const uint32_t base = half ? 64 : 0;
+        while (v) {
+            const uint32_t start = __ffsll((long long)v) - 1;
+            const uint64_t ones = ~(v >> start);           // zero bits of the shifted word
+            uint32_t w = ones ? __ffsll((long long)ones) - 1 : 64 - start;
+            if (w > RADIX_BITS - used) w = RADIX_BITS - used;
+            DigitRun r; r.shift = (uint8_t)(base + start); r.width = (uint8_t)w; r.dst = (uint8_t)used; r.pad = 0;
+            runs[pass][nr++] = r;
+            used += w;
+            v &= ~((w >= 64 ? ~0ull : ((1ull << w) - 1)) << start);
+            if (used == RADIX_BITS) { nruns[pass] = nr; ++pass; used = 0; nr = 0; }
+        }
+    }
+    if (used) { nruns[pass] = nr; ++pass; }
+    return pass;
+}
+
+// digit histograms of every pass in one read of the keys.  Every CTA derives the digit plan from
+// the varying-bit masks for itself (a few dozen instructions of one thread, hidden behind the
+// zeroing of the histogram); CTA 0 publishes it for the passes and clamps n.
+__global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, unsigned long long max_keys, Ctl *ctl)
 {
     __shared__ unsigned int h[MAX_PASSES][RADIX_BINS];
     __shared__ DigitRun runs[MAX_PASSES][8];
     __shared__ unsigned int nruns[MAX_PASSES];
-    const uint32_t np = ctl->npasses;
-    const uint64_t n = ctl->n;
-    if ((uint64_t)blockIdx.x * blockDim.x >= n || np == 0) return;
+    __shared__ unsigned int s_np;
+    unsigned long long n = ctl->n;
+    const bool over = n > max_keys;
+    if (over) n = max_keys;
+    if (blockIdx.x && (uint64_t)blockIdx.x * blockDim.x >= n) return;
+    if (threadIdx.x == 0) {
+        uint64_t vlo = ctl->or_lo ^ ctl->and_lo;
+        uint32_t vhi = ctl->or_hi ^ ctl->and_hi;
+        if (n < 2) { vlo = 0; vhi = 0; }
+        s_np = build_digit_plan(vlo, vhi, runs, nruns);
+    }
     for (uint32_t i = threadIdx.x; i < MAX_PASSES * RADIX_BINS; i += blockDim.x) (&h[0][0])[i] = 0;
-    if (threadIdx.x < MAX_PASSES * 8) (&runs[0][0])[threadIdx.x] = (&ctl->runs[0][0])[threadIdx.x];
-    if (threadIdx.x < MAX_PASSES) nruns[threadIdx.x] = ctl->nruns[threadIdx.x];
     __syncthreads();
+    const uint32_t np = s_np;
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < np * 8) (&ctl->runs[0][0])[threadIdx.x] = (&runs[0][0])[threadIdx.x];
+        if (threadIdx.x < np) ctl->nruns[threadIdx.x] = nruns[threadIdx.x];
+        if (threadIdx.x == 0) {
+            ctl->npasses = np;
+            if (over) { ctl->n = max_keys; atomicOr(&ctl->err, ERR_KEYS_FULL); } // reported by the host
+        }
+    }
+    if (np == 0) return;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const SortItem it = items[i];
