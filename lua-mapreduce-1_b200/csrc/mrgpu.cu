@@ -67,6 +67,7 @@ __global__ void ctl_owner_reset_kernel(Ctl *ctl)
     ctl->npasses = 0;
     ctl->n_tie = 0; ctl->tie_overflow = 0; ctl->tie_small = 0; ctl->rows_ticket = 0;
     ctl->n_out = 0; ctl->key_bytes = 0;
+    ctl->max_tie_len = 0;
 }
 
 constexpr uint32_t MAX_WORLD = 1024;
@@ -381,6 +382,7 @@ cudaError_t launch_map(mr_ctx *ctx, const MapParams &p)
 }
 
 int run_general_ties(mr_ctx *ctx, uint32_t nt);
+int run_lsd_ties(mr_ctx *ctx, uint32_t max_len);
 int launch_rows(mr_ctx *ctx);
 void nccl_release(mr_ctx *ctx);
 void p2p_release(mr_ctx *ctx);
@@ -859,7 +861,8 @@ int launch_compact(mr_ctx *ctx, bool tally = false)
     return MR_OK;
 }
 
-int launch_sort(mr_ctx *ctx)
+// digit histograms + the radix passes over item[0] (the digit plan is made on the device)
+int launch_radix(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
     CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
@@ -876,6 +879,14 @@ int launch_sort(mr_ctx *ctx)
                                                                                 ctx->max_tiles, ctx->d_ctl);
         ctx->stats.launches++;
     }
+    CU(cudaGetLastError());
+    return MR_OK;
+}
+
+int launch_sort(mr_ctx *ctx)
+{
+    cudaStream_t s = ctx->stream;
+    { int rc = launch_radix(ctx); if (rc) return rc; }
     uint64_t tie_cap = 1; while (tie_cap < ctx->max_keys) tie_cap <<= 1;
     tie_mark_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, s>>>(
         ctx->bufs, ctx->d_ties, (uint32_t)tie_cap, ctx->ent, ctx->bytes_base, ctx->d_ctl);
@@ -920,6 +931,23 @@ int run_general_ties(mr_ctx *ctx, uint32_t nt)
     tie_writeback_kernel<<<(nt + 255) / 256, 256, 0, s>>>(ctx->bufs, ctx->d_ties, ctx->d_posv, nt, ctx->d_ctl);
     ctx->stats.launches++;
     CU(cudaGetLastError());
+    return MR_OK;
+}
+
+// Many keys in large tie groups: the whole order again, least significant 7-byte round first
+// (rekey_kernel's comment).  (max_len - 1) / 7 + 1 rounds of the radix sort.
+int run_lsd_ties(mr_ctx *ctx, uint32_t max_len)
+{
+    cudaStream_t s = ctx->stream;
+    const int rmax = max_len ? (int)((max_len - 1) / 7) : 0;
+    for (int round = rmax; round >= 0; --round) {
+        sort_round_reset_kernel<<<4, 256, 0, s>>>(ctx->d_ctl);
+        rekey_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, s>>>(ctx->bufs, (uint32_t)round, ctx->ent,
+                                                                                     ctx->bytes_base, ctx->max_keys, ctx->d_ctl);
+        ctx->stats.launches += 2;
+        int rc = launch_radix(ctx);
+        if (rc) return rc;
+    }
     return MR_OK;
 }
 
@@ -973,7 +1001,10 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
         if (rc) return rc;
         if (ctx->h_ctl->tie_overflow) {
             // rare: many keys agree in their first 7 bytes; order them, then redo the rows
-            if ((rc = run_general_ties(ctx, ctx->h_ctl->n_tie))) return rc;
+            // keys sharing long prefixes.  Up to 64K of them: pairwise compares of whole keys in a
+            // bitonic network; more (and keys of bounded length): the radix sort again, round by round
+            const bool lsd = ctx->h_ctl->n_tie > (1u << 16) && ctx->h_ctl->max_tie_len <= 7 * 12;
+            if ((rc = lsd ? run_lsd_ties(ctx, ctx->h_ctl->max_tie_len) : run_general_ties(ctx, ctx->h_ctl->n_tie))) return rc;
             if ((rc = launch_rows(ctx))) return rc;
                     CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
             CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));

@@ -52,6 +52,8 @@ struct Ctl {
     unsigned long long key_bytes;    // sum of key lengths over rows
     unsigned long long tokens;
     unsigned long long pool_used;    // bytes of the key pool in use (bigram keys longer than 15 bytes)
+    unsigned int max_tie_len;        // longest key among the members of large tie groups
+    unsigned int reserved0;
     unsigned int nruns[MAX_PASSES];
     DigitRun runs[MAX_PASSES][8];
     unsigned int tickets[MAX_PASSES];
@@ -550,6 +552,7 @@ __global__ void __launch_bounds__(256) tie_mark_kernel(SortBufs bufs, TieItem *t
     const uint32_t lane = threadIdx.x & 31, lt = lanemask_lt();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t rounds = (n + stride - 1) / stride;
+    uint32_t max_len = 0;
     for (uint64_t r = 0; r < rounds; ++r) {
         const uint64_t i = r * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
         bool big = false;
@@ -573,6 +576,7 @@ __global__ void __launch_bounds__(256) tie_mark_kernel(SortBufs bufs, TieItem *t
                 if (g > TIE_SMALL_GROUP) {
                     big = true;
                     myval = me.val;
+                    max_len = max(max_len, key_len(ent.key(me.val)));
                 } else if (g > 1 && lo_i == i) {
                     // head of a small group: insertion sort of the entry indices by full key
                     uint32_t v[TIE_SMALL_GROUP];
@@ -599,6 +603,45 @@ __global__ void __launch_bounds__(256) tie_mark_kernel(SortBufs bufs, TieItem *t
             if (k < tie_cap) { ties[k].pos = (uint32_t)i; ties[k].val = myval; }
         }
     }
+    // how many 7-byte rounds a full re-sort would need (run_lsd_ties): one atomic per warp
+    for (int d = 16; d; d >>= 1) max_len = max(max_len, __shfl_xor_sync(0xFFFFFFFFu, max_len, d));
+    if (lane == 0 && max_len) atomicMax(&ctl->max_tie_len, max_len);
+}
+
+// Many large tie groups (keys sharing long prefixes: bigrams, URLs, paths): instead of comparing
+// whole keys pairwise, sort everything again least-significant round first -- sort word of round
+// rmax, ..., of round 1, then (partition, round 0); every round is the same stable radix sort,
+// so the result is the full order.  This kernel writes round `round`'s items into item[0] (from
+// wherever the previous round left them) and collects the varying bits for the digit plan.
+__global__ void sort_round_reset_kernel(Ctl *ctl)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) { ctl->or_lo = 0; ctl->and_lo = ~0ull; ctl->or_hi = 0; ctl->and_hi = ~0u; } // npasses stays: it says where the items are
+    if (t < MAX_PASSES) ctl->tickets[t] = 0;
+    for (uint32_t i = t; i < MAX_PASSES * RADIX_BINS; i += gridDim.x * blockDim.x) (&ctl->ghist[0][0])[i] = 0;
+}
+
+__global__ void __launch_bounds__(256) rekey_kernel(SortBufs bufs, uint32_t round, EntryArrays ent,
+                                                    const uint8_t *bytes, unsigned long long max_keys, Ctl *ctl)
+{
+    const SortItem *src = bufs.item[ctl->npasses & 1];
+    SortItem *dst = bufs.item[0];
+    uint32_t hi_or = 0, hi_and = ~0u;
+    uint64_t lo_or = 0, lo_and = ~0ull;
+    bool any = false;
+    const uint64_t n = ctl->n < max_keys ? ctl->n : max_keys;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        SortItem it = src[i];
+        const ulonglong4 e = ld256(&ent.e[it.val]);
+        Key key; key.k0 = e.x; key.k1 = e.y;
+        it.lo = sort_chunk(key, bytes, round);
+        it.hi = round == 0 ? (uint32_t)e.w : 0;
+        dst[i] = it;
+        hi_or |= it.hi; hi_and &= it.hi; lo_or |= it.lo; lo_and &= it.lo;
+        any = true;
+    }
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
 }
 
 // Up to TIE_SMALL_MAX members of large groups: one CTA copies their keys into shared memory,

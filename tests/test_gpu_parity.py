@@ -126,6 +126,19 @@ def test_many_keys_sharing_a_7_byte_prefix_general_path():
     assert info.tie_rounds == 2
 
 
+def test_one_hundred_thousand_keys_in_large_tie_groups():
+    # more than 64K keys in groups that agree in their first 7 bytes: the order comes from radix
+    # rounds over the later bytes (run_lsd_ties), inline keys and keys longer than 15 bytes alike
+    rnd = random.Random(9)
+    keys = [b"shared/%06d" % i for i in range(60000)]
+    keys += [b"sharedpath/%05d/%s" % (i, bytes(rnd.choice(b"xyz") for _ in range(rnd.randrange(1, 12)))) for i in range(50000)]
+    keys += [b"other", b"shared/", b"shared"]
+    rnd.shuffle(keys)
+    text = b" ".join(keys) + b" " + b" ".join(keys[:5000])
+    got, info = check([text], 10, max_keys=1 << 18)
+    assert info.tie_rounds == 2 and info.n_keys == len(set(keys))
+
+
 def test_synthetic_corpus_small():
     splits, tok = corpus.generate(lines=[3000, 3000, 1234, 1], first_split=190)
     got, info = check(splits, 10, max_keys=1 << 18)
