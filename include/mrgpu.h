@@ -127,6 +127,10 @@ int mr_job_begin(mr_ctx *ctx, int keep_input);
  * unchanged until mr_map_finish has returned and the stream has caught up
  * (mr_job_sync, or any later result call).  Tokens never span splits. */
 int mr_map_split(mr_ctx *ctx, uint64_t split_id, const void *bytes, uint64_t n);
+/* Same, the library reading the file itself (mapfn.lua:4 opens its value with io.lines):
+ * one page-locked buffer per context, so consecutive files do not overlap their copies;
+ * a host that wants the overlap reads the files itself and calls mr_map_split. */
+int mr_map_split_path(mr_ctx *ctx, uint64_t split_id, const char *path);
 /* Same with bytes already in device memory (device->device copy). */
 int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, uint64_t n);
 

@@ -18,7 +18,7 @@ MR_PARTITION_FNV1_LUA52, MR_PARTITION_MOD_U32 = 0, 1
 # every symbol include/mrgpu.h declares
 EXPORTS = (
     "mr_abi_version", "mr_ctx_create", "mr_ctx_destroy", "mr_last_error", "mr_job_begin",
-    "mr_map_split", "mr_map_split_device", "mr_map_records", "mr_map_records_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
+    "mr_map_split", "mr_map_split_path", "mr_map_split_device", "mr_map_records", "mr_map_records_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
     "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
     "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
@@ -95,6 +95,7 @@ def load(build_if_missing=True):
     L.mr_job_begin.argtypes = [vp, C.c_int]
     L.mr_map_split.argtypes = [vp, u64, vp, u64]
     L.mr_map_split_device.argtypes = [vp, u64, vp, u64]
+    L.mr_map_split_path.argtypes = [vp, u64, C.c_char_p]
     L.mr_map_records.argtypes = [vp, u64, vp, vp, u64]
     L.mr_map_records_device.argtypes = [vp, u64, vp, vp, u64]
     L.mr_map_finish.argtypes = [vp]
@@ -184,6 +185,10 @@ class Context:
         """data: bytes-like or a uint8 numpy array (host memory)."""
         arr = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
         self._ck(self._L.mr_map_split(self._h, split_id, arr.ctypes.data if arr.size else None, arr.size))
+
+    def map_split_path(self, split_id, path):
+        """The library reads the file itself (what the reference's mapfn does with its value)."""
+        self._ck(self._L.mr_map_split_path(self._h, split_id, os.fsencode(path)))
 
     def map_split_ptr(self, split_id, ptr, n, device=False):
         fn = self._L.mr_map_split_device if device else self._L.mr_map_split

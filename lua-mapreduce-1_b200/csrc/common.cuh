@@ -205,16 +205,19 @@ struct FnvLua52 {
     __device__ __forceinline__ FnvLua52() : h(2166136261u) {}
     __device__ __forceinline__ void byte(uint32_t c)
     {
-        unsigned long long p = (unsigned long long)h * 16777619u;
-        const int top = 63 - __clzll((long long)p);
-        if (top >= 53) {
-            const int s = top - 52;
-            const unsigned long long half = 1ull << (s - 1), rem = p & ((1ull << s) - 1);
-            p >>= s;
-            if (rem > half || (rem == half && (p & 1))) ++p;
-            p <<= s;
+        // Only the low 32 bits of the rounded product survive `% 2^32`, and the rounding touches
+        // at most the low 4 bits plus a carry that runs upwards, so it is done on the low word;
+        // the high word only says how many bits are dropped: p < 2^57, top bit = 63 - clz(p),
+        // s = top - 52 = 11 - clz(high word) when that is positive.
+        uint32_t lo = h * 16777619u;
+        const uint32_t hi = __umulhi(h, 16777619u);
+        const int s = 11 - __clz((int)hi);
+        if (s > 0) {
+            // round to nearest, ties to even: adding half-1+odd(quotient) carries exactly when it must
+            const uint32_t add = (1u << (s - 1)) - 1u + ((lo >> s) & 1u);
+            lo = ((lo + add) >> s) << s;
         }
-        h = (uint32_t)p ^ c;
+        h = lo ^ c;
     }
     __device__ __forceinline__ uint32_t partition(uint32_t num_reducers) const { return h % num_reducers; }
 };

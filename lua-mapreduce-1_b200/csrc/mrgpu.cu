@@ -246,6 +246,9 @@ struct mr_ctx {
     uint64_t input_bytes = 0;
     bool any_split = false;
     uint8_t *d_pool = nullptr; // bigram contexts: bytes of keys longer than 15 bytes
+    uint8_t *h_file = nullptr; // pinned: mr_map_split_path reads files through it
+    uint64_t file_cap = 0;
+    bool file_busy = false;   // a copy out of h_file may still be in flight
     Gap *h_gaps = nullptr;    // pinned
     Gap *d_gaps = nullptr;
     uint32_t ngaps = 0;       // gaps collected since the last flush, at h_gaps[gap_base ..]
@@ -292,6 +295,7 @@ struct mr_ctx {
     unsigned int *d_p2p_done = nullptr;
     uint64_t p2p_epoch = 0;
     bool p2p_attached = false;
+    bool p2p_sent_pending = false;      // Ctl::sent holds the records this rank sent (map_keys)
 
     // owner ranks by key range (mr_shuffle_set_owners); none: owner = partition mod world_size
     unsigned long long *d_split_word = nullptr;
@@ -431,6 +435,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_gaps) cudaFreeHost(ctx->h_gaps);
+    if (ctx->h_file) cudaFreeHost(ctx->h_file);
     cudaFree(ctx->d_gaps);
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     for (cudaEvent_t e : { ctx->ev_map0, ctx->ev_map1, ctx->ev_red0, ctx->ev_red1, ctx->ev_gaps, ctx->ev_copy, ctx->ev_job })
@@ -667,6 +672,35 @@ int mr_map_split(mr_ctx *ctx, uint64_t split_id, const void *bytes, uint64_t n)
     return stage_split(ctx, bytes, n, cudaMemcpyHostToDevice);
 }
 
+int mr_map_split_path(mr_ctx *ctx, uint64_t split_id, const char *path)
+{
+    // what the reference's mapfn does with its value (mapfn.lua:4: io.lines(value)): the file is
+    // read here, into a page-locked buffer the context keeps, and staged like any other split
+    if (!ctx || !path) return MR_ERR_INVALID;
+    FILE *f = fopen(path, "rb");
+    if (!f) return fail(ctx, MR_ERR_INVALID, "mr_map_split_path: cannot open %s", path);
+    int rc = MR_OK;
+    uint64_t n = 0;
+    if (fseek(f, 0, SEEK_END) == 0) { long sz = ftell(f); n = sz > 0 ? (uint64_t)sz : 0; }
+    rewind(f);
+    CU(cudaSetDevice(ctx->cfg.device));
+    // the buffer is reused (or replaced): the previous file's copy must have left it
+    if (ctx->file_busy) { CU(cudaStreamSynchronize(ctx->copy_stream)); ctx->file_busy = false; }
+    if (n > ctx->file_cap) {
+        if (ctx->h_file) cudaFreeHost(ctx->h_file);
+        ctx->h_file = nullptr; ctx->file_cap = 0;
+        cudaError_t e = cudaMallocHost((void **)&ctx->h_file, n + n / 4 + 4096);
+        if (e != cudaSuccess) { fclose(f); return fail(ctx, MR_ERR_NOMEM, "mr_map_split_path: %s", cudaGetErrorString(e)); }
+        ctx->file_cap = n + n / 4 + 4096;
+    }
+    if (n && fread(ctx->h_file, 1, n, f) != n) rc = fail(ctx, MR_ERR_INVALID, "mr_map_split_path: short read of %s", path);
+    fclose(f);
+    if (rc) return rc;
+    (void)split_id;
+    ctx->file_busy = n != 0;
+    return stage_split(ctx, ctx->h_file, n, cudaMemcpyHostToDevice);
+}
+
 int mr_map_split_device(mr_ctx *ctx, uint64_t split_id, const void *dev_bytes, uint64_t n)
 {
     (void)split_id;
@@ -842,20 +876,14 @@ int mr_map_finish(mr_ctx *ctx)
 
 namespace {
 
-// table -> entries with partition ids, plus sort items (tally == false) or per-owner tallies for
-// the peer-to-peer shuffle (tally == true); one read of the table either way
-int launch_compact(mr_ctx *ctx, bool tally = false)
+// table -> entries with partition ids and owner ranks, sort items, varying-bit masks: one kernel
+int launch_compact(mr_ctx *ctx)
 {
     const uint64_t tiles = (ctx->slots + 256 * COMPACT_ITEMS - 1) / (256 * COMPACT_ITEMS);
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
-    if (tally)
-        compact_partition_kernel<1><<<grid, 256, 0, ctx->stream>>>(
-            ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
-            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners(), ctx->d_shuf, ctx->d_shuf + ctx->cfg.world_size);
-    else
-        compact_partition_kernel<0><<<grid, 256, 0, ctx->stream>>>(
-            ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
-            ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners(), nullptr, nullptr);
+    compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(
+        ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
+        ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners());
     ctx->stats.launches += 1;
     CU(cudaGetLastError());
     return MR_OK;
@@ -1020,6 +1048,7 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
         ctx->info.input_bytes = ctx->input_bytes;
         ctx->info.key_bytes = ctx->h_ctl->key_bytes;
         if (!ctx->imported) ctx->info.map_keys = ctx->h_ctl->n;
+        if (ctx->p2p_sent_pending) { ctx->info.map_keys = ctx->h_ctl->sent; ctx->p2p_sent_pending = false; }
         ctx->info.tie_rounds = ctx->tie_rounds;
         ctx->info.flags = 0;
         if (ctx->map_timed) cudaEventElapsedTime(&ctx->stats.map_ms, ctx->ev_map0, ctx->ev_map1);
@@ -1564,14 +1593,9 @@ int mr_shuffle_p2p(mr_ctx *ctx)
     if (ctx->map_dirty) { int rc = mr_map_finish(ctx); if (rc) return rc; }
     const uint32_t W = ctx->cfg.world_size;
     cudaStream_t s = ctx->stream;
-    // sender: table -> entries with partition ids and tallies per owner (one kernel), then headers
-    // and records into the owners' slots and the flags (one kernel)
+    // sender: ONE kernel from the global table to records in the owners' slots, headers and flags
     CU(cudaMemsetAsync(ctx->d_shuf, 0, (5ull * W + 1) * 8, s));
-    int rc = launch_compact(ctx, true);
-    if (rc) return rc;
-    unsigned long long *nrec = ctx->d_shuf, *nbytes = ctx->d_shuf + W, *rec_cur = ctx->d_shuf + 2 * W,
-                       *byte_cur = ctx->d_shuf + 3 * W;
-    const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
+    unsigned long long *rec_cur = ctx->d_shuf + 2 * W, *byte_cur = ctx->d_shuf + 3 * W;
     const uint64_t epoch = ++ctx->p2p_epoch;
     const uint32_t parity = (uint32_t)(epoch & 1);
     P2PParams p;
@@ -1581,8 +1605,12 @@ int mr_shuffle_p2p(mr_ctx *ctx)
     p.rank = ctx->cfg.rank;
     p.slot_bytes = ctx->p2p_slot;
     p.epoch = epoch;
-    p2p_scatter_kernel<<<g, 256, 0, s>>>(p, ctx->ent, ctx->bytes_base, nrec, nbytes, rec_cur, byte_cur, ctx->d_p2p_done,
-                                         ctx->max_keys, ctx->d_ctl);
+    const uint64_t tiles = (ctx->slots + 256 * P2P_SEND_ITEMS - 1) / (256 * P2P_SEND_ITEMS);
+    const unsigned g = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
+    const size_t dyn = 24ull * W;
+    if (dyn > 8192) CU(cudaFuncSetAttribute(p2p_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    p2p_send_kernel<<<g, 256, dyn, s>>>(p, ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind,
+                                      ctx->owners(), rec_cur, byte_cur, ctx->d_p2p_done, ctx->d_ctl);
     // owner: a fresh control block (token count and errors kept), then index the window in place
     uint8_t *mybuf = ctx->p2p_win + P2P_FLAG_BYTES + (uint64_t)parity * W * ctx->p2p_slot;
     ctl_owner_reset_kernel<<<1, 1, 0, s>>>(ctx->d_ctl);
@@ -1591,6 +1619,7 @@ int mr_shuffle_p2p(mr_ctx *ctx)
                                                 ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
     ctx->stats.launches += 3;
     CU(cudaGetLastError());
+    ctx->p2p_sent_pending = true;
     ctx->ent.e = (GEntry *)mybuf;
     ctx->bytes_base = mybuf;
     ctx->imported = true;

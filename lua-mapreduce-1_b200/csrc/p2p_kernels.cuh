@@ -8,8 +8,8 @@
 //   [ flags: P2P_FLAG_BYTES ][ buffer 0: world slots ][ buffer 1: world slots ]
 //
 //   slot s of a buffer = what rank s sent:  [ header 32 B {records, key bytes, 0, 0} ]
-//                                           [ records: GEntry 32 B {k0, k1, count, partition} ]
-//                                           [ bytes of keys longer than 15 bytes ]
+//                                           [ records: GEntry 32 B {k0, k1, count, partition} ... ->
+//                                           <- ... bytes of keys longer than 15 bytes ] (slot end)
 //
 // Records are table entries already (same 32-byte layout), long keys carry offsets relative to
 // the start of the receiving buffer, so the owner sorts and reduces them where they lie.
@@ -57,82 +57,128 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
     return t;
 }
 
-// entries -> records in the owners' slots.  Each CTA takes one contiguous chunk of entries: tally
-// per owner, reserve ranges with one atomic per owner, hand out places from shared-memory cursors.
-// The last CTA to finish publishes this rank's epoch in every owner's flag array (release at
-// system scope after all CTAs fenced their remote stores).
-__global__ void __launch_bounds__(256) p2p_scatter_kernel(P2PParams p, EntryArrays ent, const uint8_t *bytes,
-                                                          const unsigned long long *nrec_total,
-                                                          const unsigned long long *nbytes_total,
-                                                          unsigned long long *rec_cur, unsigned long long *byte_cur,
-                                                          unsigned int *done_ctas, unsigned long long max_keys, Ctl *ctl)
+// The sender's side in ONE kernel: global table -> records in the owners' slots.  A tile of table
+// slots is packed in shared memory (so that the partitioner runs on full warps), every record
+// gets its owner, the tile reserves its places in each owner's slot with one atomic per owner,
+// and the records go straight out over NVLink -- no dense entry array, no second pass.  Records
+// grow upwards from the slot header, bytes of keys longer than 15 bytes downwards from the slot
+// end, so no total has to be known before the first store.  The last CTA to finish writes the
+// headers (poisoned if records and bytes of some slot met: sender and owner both report it) and
+// publishes this rank's epoch in every owner's flag array (release at system scope, after every
+// CTA fenced its remote stores).
+constexpr int P2P_SEND_ITEMS = 4;
+__global__ void __launch_bounds__(256) p2p_send_kernel(P2PParams p, const GEntry *gt, uint64_t nslots,
+                                                       const uint8_t *bytes, uint32_t num_reducers,
+                                                       uint32_t partition_kind, OwnerMap owners,
+                                                       unsigned long long *rec_cur, unsigned long long *byte_cur,
+                                                       unsigned int *done_ctas, Ctl *ctl)
 {
-    __shared__ unsigned int s_rec[P2P_MAX_WORLD];
-    __shared__ unsigned long long s_bytes[P2P_MAX_WORLD], s_rec_base[P2P_MAX_WORLD], s_byte_base[P2P_MAX_WORLD];
+    constexpr int ITEMS = P2P_SEND_ITEMS;
+    __shared__ ulonglong4 s_ent[256 * ITEMS];
+    __shared__ unsigned short s_rl[256 * ITEMS];         // place of the record among the tile's records for its owner
+    __shared__ unsigned int s_bl[256 * ITEMS];           // same for its key bytes
+    __shared__ unsigned int wsum[8];
     __shared__ bool s_last;
-    __shared__ unsigned int s_full;
-    // a segment that does not fit its slot: nothing is written but poisoned headers, so that sender
-    // and owners all report it; every CTA works that out for itself from the tallies
-    if (threadIdx.x == 0) s_full = 0;
-    __syncthreads();
-    for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x)
-        if (P2P_HDR + nrec_total[d] * P2P_REC + nbytes_total[d] > p.slot_bytes) s_full = 1;
-    __syncthreads();
-    const bool full = s_full;
-    if (blockIdx.x == 0) {
-        if (full && threadIdx.x == 0) atomicOr(&ctl->err, ERR_SHUFFLE_FULL);
-        for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) {
-            ulonglong2 *hdr = (ulonglong2 *)(p.peer_buf[d] + (unsigned long long)p.rank * p.slot_bytes);
-            hdr[0] = full ? make_ulonglong2(~0ull, 0) : make_ulonglong2(nrec_total[d], nbytes_total[d]);
-            hdr[1] = make_ulonglong2(0, 0);
+    // per-owner tallies and reserved bases: 24 bytes per rank of dynamic shared memory
+    extern __shared__ __align__(16) unsigned char p2p_dyn[];
+    unsigned long long *s_rec_base = (unsigned long long *)p2p_dyn, *s_byt_base = s_rec_base + p.world;
+    unsigned int *s_rec = (unsigned int *)(s_byt_base + p.world), *s_byt = s_rec + p.world;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t tile_slots = 256 * ITEMS;
+    const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
+    const unsigned long long slot_at = (unsigned long long)p.rank * p.slot_bytes; // offset in the owner's buffer
+    unsigned long long sent = 0;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        ulonglong4 e[ITEMS];
+        uint32_t nocc = 0;
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
+            e[i] = make_ulonglong4(0, 0, 0, 0);
+            if (slot < nslots) e[i] = ld256(&gt[slot]);
+            nocc += e[i].y != 0;
         }
-    }
-    const uint64_t n = ctl->n < max_keys ? ctl->n : max_keys;
-    const uint64_t chunk = (n + gridDim.x - 1) / gridDim.x;
-    const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
-    if (!full && lo < hi) {
-        for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
+        for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) { s_rec[d] = 0; s_byt[d] = 0; }
+        uint32_t incl = nocc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
+        if (lane == 31) wsum[warp] = incl;
         __syncthreads();
-        for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-            const uint32_t d = ent.owner(i);
-            atomicAdd(&s_rec[d], 1u);
-            const Key k = ent.key(i);
-            if (key_is_long(k)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(k));
+        uint32_t woff = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { uint32_t c = wsum[w]; if (w < (int)warp) woff += c; total += c; }
+        uint32_t pos = woff + incl - nocc;
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (e[i].y != 0) s_ent[pos++] = e[i];
+        __syncthreads();
+        // owner and place inside the tile, per record
+        for (uint32_t t = threadIdx.x; t < total; t += 256) {
+            ulonglong4 v = s_ent[t];
+            Key key; key.k0 = v.x; key.k1 = v.y;
+            const uint32_t part = partition_kind == 1 ? __byte_perm((uint32_t)key.k0, 0, 0x0123) % num_reducers
+                                                      : partition_of_key(key, bytes, num_reducers);
+            const uint32_t d = owners.world > 1 ? owner_of(owners, part, sort_chunk(key, bytes, 0)) : 0;
+            s_ent[t].w = part | (unsigned long long)d << 32;
+            s_rl[t] = (unsigned short)atomicAdd(&s_rec[d], 1u);
+            if (key_is_long(key)) s_bl[t] = atomicAdd(&s_byt[d], key_len(key));
         }
         __syncthreads();
         for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) {
             s_rec_base[d] = s_rec[d] ? atomicAdd(&rec_cur[d], (unsigned long long)s_rec[d]) : 0;
-            s_byte_base[d] = s_bytes[d] ? atomicAdd(&byte_cur[d], s_bytes[d]) : 0;
-            s_rec[d] = 0; s_bytes[d] = 0;
+            s_byt_base[d] = s_byt[d] ? atomicAdd(&byte_cur[d], (unsigned long long)s_byt[d]) : 0;
         }
         __syncthreads();
-        for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-            const ulonglong4 e = ld256(&ent.e[i]);
-            Key k; k.k0 = e.x; k.k1 = e.y;
-            const uint32_t d = (uint32_t)(e.w >> 32);
-            const unsigned long long slot_at = (unsigned long long)p.rank * p.slot_bytes; // offset in the owner's buffer
+        for (uint32_t t = threadIdx.x; t < total; t += 256) {
+            const ulonglong4 v = s_ent[t];
+            Key k; k.k0 = v.x; k.k1 = v.y;
+            const uint32_t d = (uint32_t)(v.w >> 32);
             uint8_t *slot = p.peer_buf[d] + slot_at;
-            const unsigned long long r = s_rec_base[d] + atomicAdd(&s_rec[d], 1u);
+            const unsigned long long rec_end = P2P_HDR + (s_rec_base[d] + s_rl[t] + 1) * P2P_REC;
+            bool fits = rec_end <= p.slot_bytes;
             if (key_is_long(k)) {
                 const uint32_t len = key_len(k);
-                const unsigned long long bo = P2P_HDR + nrec_total[d] * P2P_REC + s_byte_base[d] +
-                                              atomicAdd(&s_bytes[d], (unsigned long long)len);
-                uint8_t *dst = slot + bo;
-                const uint64_t off = key_off(k);
-                for (uint32_t j = 0; j < len; ++j) dst[j] = bytes[off + j];
-                k = make_long_key(slot_at + bo, len, (uint32_t)k.k1); // offset as the owner will see it
+                const unsigned long long below = s_byt_base[d] + s_bl[t] + len; // bytes from the slot end down to this key's start
+                fits = fits && below + P2P_HDR <= p.slot_bytes;
+                if (fits) {
+                    const unsigned long long bo = p.slot_bytes - below;
+                    uint8_t *dst = slot + bo;
+                    const uint64_t off = key_off(k);
+                    for (uint32_t j = 0; j < len; ++j) dst[j] = bytes[off + j];
+                    k = make_long_key(slot_at + bo, len, (uint32_t)k.k1); // offset as the owner will see it
+                }
             }
-            ulonglong2 *rec = (ulonglong2 *)(slot + P2P_HDR + r * P2P_REC);
-            rec[0] = make_ulonglong2(k.k0, k.k1);
-            rec[1] = make_ulonglong2(e.z, e.w);
+            if (fits) { // a record that does not fit is simply not stored: the header check below reports the slot
+                ulonglong2 *rec = (ulonglong2 *)(slot + rec_end - P2P_REC);
+                rec[0] = make_ulonglong2(k.k0, k.k1);
+                rec[1] = make_ulonglong2(v.z, v.w & 0xFFFFFFFFull);
+            }
         }
+        sent += total;
+        __syncthreads();
     }
-    __threadfence_system(); // this thread's remote stores are performed before the CTA is counted as done
+    if (threadIdx.x == 0 && sent) atomicAdd(&ctl->sent, sent); // records this rank sent (mr_job_info.map_keys)
+    // the CTA's remote stores are ordered before it is counted as done: the barrier makes them
+    // visible to thread 0, whose system-scope fence is cumulative over them (one fence per CTA --
+    // a fence in every thread cost a third of this kernel's time)
     __syncthreads();
-    if (threadIdx.x == 0) s_last = atomicAdd(done_ctas, 1u) == gridDim.x - 1;
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        s_last = atomicAdd(done_ctas, 1u) == gridDim.x - 1;
+    }
     __syncthreads();
     if (!s_last) return;
+    __threadfence();
+    for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) {
+        const unsigned long long nr = *(volatile unsigned long long *)&rec_cur[d], nb = *(volatile unsigned long long *)&byte_cur[d];
+        const bool full = P2P_HDR + nr * P2P_REC + nb > p.slot_bytes;
+        if (full) atomicOr(&ctl->err, ERR_SHUFFLE_FULL);
+        ulonglong2 *hdr = (ulonglong2 *)(p.peer_buf[d] + slot_at);
+        hdr[0] = full ? make_ulonglong2(~0ull, 0) : make_ulonglong2(nr, nb);
+        hdr[1] = make_ulonglong2(0, 0);
+    }
     __threadfence_system();
+    __syncthreads();
     for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) {
         unsigned long long *flag = (unsigned long long *)p.peer_win[d] + p.rank;
         asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(p.epoch) : "memory");

@@ -54,6 +54,7 @@ struct Ctl {
     unsigned long long pool_used;    // bytes of the key pool in use (bigram keys longer than 15 bytes)
     unsigned int max_tie_len;        // longest key among the members of large tie groups
     unsigned int reserved0;
+    unsigned long long sent;         // peer-to-peer shuffle: records this rank sent (its map_keys)
     unsigned int nruns[MAX_PASSES];
     DigitRun runs[MAX_PASSES][8];
     unsigned int tickets[MAX_PASSES];
@@ -127,34 +128,24 @@ __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t 
 // costs ~1.4 ns each).
 constexpr int COMPACT_ITEMS = 4;
 
-// table slots -> dense entries WITH their partition ids, in one read of the table.  A tile's
-// occupied slots are first packed side by side in shared memory, so that the partitioner (a
-// byte loop per key) runs on full warps although only a fraction of the slots is occupied.
-//   MODE 0  also builds the sort items and the varying-bit masks (single rank, exact shuffle)
-//   MODE 1  also tallies records / long-key bytes per owner rank (peer-to-peer shuffle)
-constexpr uint32_t TALLY_MAX_WORLD = 1024;
-template <int MODE>
+// table slots -> dense entries WITH their partition ids (and owner ranks), sort items and the
+// varying-bit masks, in one read of the table.  A tile's occupied slots are first packed side by
+// side in shared memory, so that the partitioner (a byte loop per key) runs on full warps
+// although only a fraction of the slots is occupied.
 __global__ void __launch_bounds__(256) compact_partition_kernel(
     const GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind,
-    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, OwnerMap owners, unsigned long long *nrec,
-    unsigned long long *nbytes)
+    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, OwnerMap owners)
 {
     constexpr int ITEMS = COMPACT_ITEMS;
     __shared__ ulonglong4 s_ent[256 * ITEMS];
     __shared__ unsigned int wsum[8];
     __shared__ unsigned long long s_base;
-    __shared__ unsigned int s_rec[MODE == 1 ? TALLY_MAX_WORLD : 1];
-    __shared__ unsigned long long s_bytes[MODE == 1 ? TALLY_MAX_WORLD : 1];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t tile_slots = 256 * ITEMS;
     const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
     uint32_t hi_or = 0, hi_and = ~0u;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
-    if (MODE == 1) {
-        for (uint32_t d = threadIdx.x; d < owners.world; d += blockDim.x) { s_rec[d] = 0; s_bytes[d] = 0; }
-        __syncthreads();
-    }
     for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         ulonglong4 e[ITEMS];
         uint32_t nocc = 0;
@@ -191,27 +182,14 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
             const uint32_t owner = owners.world > 1 ? owner_of(owners, part, chunk) : 0;
             v.w = part | (unsigned long long)owner << 32; // EntryArrays::part / ::owner
             ((ulonglong4 *)ent.e)[idx] = v;
-            if (MODE == 0) {
-                SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
-                items[idx] = it;
-                hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
-                any = true;
-            } else {
-                const uint32_t d = owner;
-                atomicAdd(&s_rec[d], 1u);
-                if (key_is_long(key)) atomicAdd(&s_bytes[d], (unsigned long long)key_len(key));
-            }
+            SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
+            items[idx] = it;
+            hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
+            any = true;
         }
         __syncthreads();
     }
-    if (MODE == 0) {
-        orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
-    } else {
-        for (uint32_t d = threadIdx.x; d < owners.world; d += blockDim.x) {
-            if (s_rec[d]) atomicAdd(&nrec[d], (unsigned long long)s_rec[d]);
-            if (s_bytes[d]) atomicAdd(&nbytes[d], s_bytes[d]);
-        }
-    }
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
 }
 
 // dense entries -> partition id + sort item (+ which key bits vary at all)

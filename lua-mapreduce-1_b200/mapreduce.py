@@ -339,9 +339,8 @@ class worker:
                     ctx.map_records(len(mine), value[0], value[1])
                 elif isinstance(value, (bytes, bytearray, memoryview)) or hasattr(value, "ctypes"):
                     ctx.map_split(len(mine), value)
-                else:   # mapfn.lua:4: the value names a file
-                    with open(value, "rb") as f:
-                        ctx.map_split(len(mine), f.read())
+                else:   # mapfn.lua:4: the value names a file; the library reads it (mr_map_split_path)
+                    ctx.map_split_path(len(mine), value)
                 self._mark(job, FINISHED, finished_time=time.time())
                 mine.append((job, t0, c0))
             except Exception as e:

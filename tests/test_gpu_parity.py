@@ -220,6 +220,32 @@ def test_capacity_errors_are_reported():
     assert e.value.code in (_native.MR_ERR_NOMEM, _native.MR_ERR_OVERFLOW)
 
 
+def test_splits_named_by_path(tmp_path):
+    # mr_map_split_path: files of very different sizes through the one page-locked buffer, an empty
+    # file, a missing file
+    splits, _ = corpus.generate(lines=[3000, 5, 0, 1200, 40000, 7])
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    paths = []
+    for i, s in enumerate(splits):
+        p = tmp_path / f"s{i}.txt"
+        p.write_bytes(bytes(s))
+        paths.append(str(p))
+    want = O.run_naive(splits, 10)
+    ctx = _native.Context(10, 1 << 23, max_keys=1 << 18)
+    try:
+        for rep in range(2):
+            ctx.job_begin()
+            for i, p in enumerate(paths):
+                ctx.map_split_path(i, p)
+            ctx.reduce_all()
+            assert_rows_equal(ctx.rows(), want, f"by path, job {rep}")
+        with pytest.raises(_native.NativeError) as e:
+            ctx.map_split_path(99, str(tmp_path / "missing.txt"))
+        assert e.value.code == _native.MR_ERR_INVALID and "cannot open" in str(e.value)
+    finally:
+        ctx.close()
+
+
 def test_device_memory_input():
     import torch
     splits, _ = corpus.generate(lines=[1000])

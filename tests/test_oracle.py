@@ -123,3 +123,24 @@ def test_bigram_oracle_against_python_restatement():
     r = O.run_bigram(splits, 10)
     assert r.as_dict() == dict(want) and r.tokens == sum(want.values())
     assert r.keys() == [k for _, k in sorted((O.partition(k, 10), k) for k in want)]
+
+
+def test_low_word_rounding_used_on_the_device_equals_the_double_product():
+    # common.cuh FnvLua52::byte rounds the 57-bit product h * 16777619 to 53 bits on its low word
+    # only; here the same formula in numpy against real doubles, two million states h incl. ties
+    import numpy as np
+    rng = np.random.default_rng(5)
+    h = np.concatenate([rng.integers(0, 2**32, 2_000_000, dtype=np.uint64),
+                        np.arange(0xFFFF0000, 2**32, dtype=np.uint64), np.arange(0, 70000, dtype=np.uint64)])
+    p = h.astype(np.float64) * 16777619.0                                   # IEEE product, rounded to 53 bits
+    want = (p - np.floor(p / 4294967296.0) * 4294967296.0).astype(np.uint64)
+    full = h * np.uint64(16777619)
+    lo, hi = full & np.uint64(0xFFFFFFFF), full >> np.uint64(32)
+    nbits = np.zeros(len(h), dtype=np.int64)
+    nz = hi > 0
+    nbits[nz] = np.floor(np.log2(hi[nz].astype(np.float64))).astype(np.int64) + 1   # 32 - clz(hi)
+    s = np.maximum(nbits - 21, 0).astype(np.uint64)                        # 11 - clz(hi)
+    sm1 = np.where(s > 0, s - np.uint64(1), np.uint64(0))
+    add = np.where(s > 0, (np.uint64(1) << sm1) - np.uint64(1) + ((lo >> s) & np.uint64(1)), np.uint64(0))
+    got = (((lo + add) >> s) << s) & np.uint64(0xFFFFFFFF)
+    assert np.array_equal(got, want)
