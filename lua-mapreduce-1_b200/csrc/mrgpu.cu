@@ -256,6 +256,7 @@ struct mr_ctx {
 
     // tables and entries
     GEntry *d_gtab = nullptr;
+    bool table_dirty = true;  // the table may hold keys (set by the map kernels, cleared by compaction / sender)
     uint64_t slots = 0;
     uint64_t max_keys = 0;
     EntryArrays ent{};
@@ -575,7 +576,12 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
         ctx->rec_remap = !ctx->rec_splits.empty();
         ctx->staged_since_map = 0;
     }
-    CU(cudaMemsetAsync(ctx->d_gtab, 0, ctx->slots * sizeof(GEntry), ctx->stream));
+    // the kernels that read the table out (compaction, peer-to-peer sender) leave it empty; it is
+    // cleared here only when a job mapped something and never got that far
+    if (ctx->table_dirty) {
+        CU(cudaMemsetAsync(ctx->d_gtab, 0, ctx->slots * sizeof(GEntry), ctx->stream));
+        ctx->table_dirty = false;
+    }
     CU(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
     ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(ctx->d_ctl);
     CU(cudaGetLastError());
@@ -733,6 +739,7 @@ static int run_map_round(mr_ctx *ctx)
         bp.end = end;
         bp.limit = end + TAIL_GUARD;
         bp.gtab = ctx->d_gtab;
+        ctx->table_dirty = true;
         bp.gmask = (uint32_t)(ctx->slots - 1);
         bp.max_key = MR_MAX_TOKEN_BYTES;
         bp.pool = ctx->d_pool;
@@ -756,6 +763,7 @@ static int run_map_round(mr_ctx *ctx)
     p.first_seg = ctx->mapped_segs;
     p.nseg = end / SEG - ctx->mapped_segs;
     p.gtab = ctx->d_gtab;
+    ctx->table_dirty = true;
     p.gmask = (uint32_t)(ctx->slots - 1);
     p.max_token = MR_MAX_TOKEN_BYTES;
     p.tokens = &ctx->d_ctl->tokens;
@@ -787,6 +795,7 @@ static int launch_records(mr_ctx *ctx, const mr_ctx::RecSplit &r)
     p.vals = (const uint32_t *)(ctx->d_arena + r.off_v);
     p.n = r.n;
     p.gtab = ctx->d_gtab;
+    ctx->table_dirty = true;
     p.gmask = (uint32_t)(ctx->slots - 1);
     p.records = &ctx->d_ctl->tokens;
     p.err = &ctx->d_ctl->err;
@@ -884,6 +893,7 @@ int launch_compact(mr_ctx *ctx)
     compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(
         ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
         ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners());
+    ctx->table_dirty = false;
     ctx->stats.launches += 1;
     CU(cudaGetLastError());
     return MR_OK;
@@ -1611,6 +1621,7 @@ int mr_shuffle_p2p(mr_ctx *ctx)
     if (dyn > 8192) CU(cudaFuncSetAttribute(p2p_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
     p2p_send_kernel<<<g, 256, dyn, s>>>(p, ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind,
                                       ctx->owners(), rec_cur, byte_cur, ctx->d_p2p_done, ctx->d_ctl);
+    ctx->table_dirty = false;
     // owner: a fresh control block (token count and errors kept), then index the window in place
     uint8_t *mybuf = ctx->p2p_win + P2P_FLAG_BYTES + (uint64_t)parity * W * ctx->p2p_slot;
     ctl_owner_reset_kernel<<<1, 1, 0, s>>>(ctx->d_ctl);

@@ -39,17 +39,6 @@ struct P2PParams {
     unsigned long long epoch;
 };
 
-// 32-byte load that takes part in the memory model (ld256 is non-coherent: fine for data written
-// by earlier kernels, not for records a peer stored while this kernel was already running)
-__device__ __forceinline__ ulonglong4 ld256_coherent(const void *p)
-{
-    ulonglong4 r;
-    asm volatile("ld.global.v4.u64 {%0, %1, %2, %3}, [%4];"
-                 : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
-                 : "l"(p) : "memory");
-    return r;
-}
-
 __device__ __forceinline__ unsigned long long globaltimer_ns()
 {
     unsigned long long t;
@@ -67,7 +56,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 // publishes this rank's epoch in every owner's flag array (release at system scope, after every
 // CTA fenced its remote stores).
 constexpr int P2P_SEND_ITEMS = 4;
-__global__ void __launch_bounds__(256) p2p_send_kernel(P2PParams p, const GEntry *gt, uint64_t nslots,
+__global__ void __launch_bounds__(256) p2p_send_kernel(P2PParams p, GEntry *gt, uint64_t nslots,
                                                        const uint8_t *bytes, uint32_t num_reducers,
                                                        uint32_t partition_kind, OwnerMap owners,
                                                        unsigned long long *rec_cur, unsigned long long *byte_cur,
@@ -95,8 +84,11 @@ __global__ void __launch_bounds__(256) p2p_send_kernel(P2PParams p, const GEntry
         for (int i = 0; i < ITEMS; ++i) {
             const uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
             e[i] = make_ulonglong4(0, 0, 0, 0);
-            if (slot < nslots) e[i] = ld256(&gt[slot]);
-            nocc += e[i].y != 0;
+            if (slot < nslots) e[i] = ld256_coherent(&gt[slot]);
+            if (e[i].y != 0) {
+                ((ulonglong4 *)gt)[slot] = make_ulonglong4(0, 0, 0, 0); // the table is left empty for the next job
+                ++nocc;
+            }
         }
         for (uint32_t d = threadIdx.x; d < p.world; d += blockDim.x) { s_rec[d] = 0; s_byt[d] = 0; }
         uint32_t incl = nocc;

@@ -87,6 +87,17 @@ __device__ __forceinline__ ulonglong4 ld256(const void *p)
     return r;
 }
 
+// 32-byte load that takes part in the memory model: for data this kernel also writes (table slots
+// cleared after they were read) or that a peer stored while the kernel was already running
+__device__ __forceinline__ ulonglong4 ld256_coherent(const void *p)
+{
+    ulonglong4 r;
+    asm volatile("ld.global.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
+                 : "l"(p) : "memory");
+    return r;
+}
+
 // ------------------------------------------------------------------ K3
 __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
                                              uint64_t lo_or, uint64_t lo_and, bool any)
@@ -133,7 +144,7 @@ constexpr int COMPACT_ITEMS = 4;
 // side in shared memory, so that the partitioner (a byte loop per key) runs on full warps
 // although only a fraction of the slots is occupied.
 __global__ void __launch_bounds__(256) compact_partition_kernel(
-    const GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind,
+    GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind,
     EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, OwnerMap owners)
 {
     constexpr int ITEMS = COMPACT_ITEMS;
@@ -153,8 +164,13 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
         for (int i = 0; i < ITEMS; ++i) {
             const uint64_t slot = tile * tile_slots + (uint64_t)i * 256 + threadIdx.x;
             e[i] = make_ulonglong4(0, 0, 0, 0);
-            if (slot < nslots) e[i] = ld256(&gt[slot]);
-            nocc += e[i].y != 0;
+            if (slot < nslots) e[i] = ld256_coherent(&gt[slot]);
+            if (e[i].y != 0) {
+                // leave the table empty for the next job: only occupied slots are written, which is
+                // a fraction of what clearing the whole table costs
+                ((ulonglong4 *)gt)[slot] = make_ulonglong4(0, 0, 0, 0);
+                ++nocc;
+            }
         }
         uint32_t incl = nocc;
 #pragma unroll
