@@ -37,6 +37,15 @@ constexpr uint64_t REC_BYTES = 24; // shuffle record {k0, k1, count}
 
 inline uint64_t round_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
+// start of a job: the whole control block to zero, the AND masks to all ones (one launch)
+__global__ void ctl_job_reset_kernel(Ctl *ctl)
+{
+    uint32_t *w = (uint32_t *)ctl;
+    for (uint32_t i = threadIdx.x; i < sizeof(Ctl) / 4; i += blockDim.x) w[i] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) { ctl->and_lo = ~0ull; ctl->and_hi = ~0u; }
+}
+
 __global__ void ctl_init_kernel(Ctl *ctl)
 {
     // everything else was zeroed by the memset before this launch
@@ -388,7 +397,7 @@ cudaError_t launch_map(mr_ctx *ctx, const MapParams &p)
 
 int run_general_ties(mr_ctx *ctx, uint32_t nt);
 int run_lsd_ties(mr_ctx *ctx, uint32_t max_len);
-int launch_rows(mr_ctx *ctx);
+int launch_rows(mr_ctx *ctx, bool zeroed);
 void nccl_release(mr_ctx *ctx);
 void p2p_release(mr_ctx *ctx);
 
@@ -582,8 +591,7 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
         CU(cudaMemsetAsync(ctx->d_gtab, 0, ctx->slots * sizeof(GEntry), ctx->stream));
         ctx->table_dirty = false;
     }
-    CU(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
-    ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(ctx->d_ctl);
+    ctl_job_reset_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->d_ctl);
     CU(cudaGetLastError());
     ctx->bytes_base = ctx->d_pool ? ctx->d_pool : ctx->d_arena;
     ctx->ent.e = ctx->ent_own;
@@ -903,9 +911,9 @@ int launch_compact(mr_ctx *ctx)
 int launch_radix(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
-    CU(cudaMemsetAsync(ctx->d_status, 0, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS * 4, s));
     CU(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
-    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl);
+    radix_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl,
+                                                                                    ctx->d_status, ctx->max_tiles);
     ctx->stats.launches += 1;
     // the sort key has 64 chunk bits plus the bits of the largest partition id: more passes than
     // that can never be needed (which ones are needed is decided on the device)
@@ -927,19 +935,24 @@ int launch_sort(mr_ctx *ctx)
     { int rc = launch_radix(ctx); if (rc) return rc; }
     uint64_t tie_cap = 1; while (tie_cap < ctx->max_keys) tie_cap <<= 1;
     tie_mark_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 8), 256, 0, s>>>(
-        ctx->bufs, ctx->d_ties, (uint32_t)tie_cap, ctx->ent, ctx->bytes_base, ctx->d_ctl);
+        ctx->bufs, ctx->d_ties, (uint32_t)tie_cap, ctx->ent, ctx->bytes_base, ctx->d_ctl, ctx->rows.count, ctx->rows_st.heads,
+        3u * ctx->rows_tiles);
     tie_fix_small_kernel<<<1, 1024, 0, s>>>(ctx->bufs, ctx->d_ties, ctx->ent, ctx->bytes_base, ctx->d_ctl);
     ctx->stats.launches += 2;
     CU(cudaGetLastError());
     return MR_OK;
 }
 
-int launch_rows(mr_ctx *ctx)
+// zeroed: tie_mark_kernel has just cleared what the rows kernel needs cleared (the first pass of a
+// job); the second pass after a re-sort clears it here
+int launch_rows(mr_ctx *ctx, bool zeroed)
 {
     cudaStream_t s = ctx->stream;
-    CU(cudaMemsetAsync(ctx->rows.count, 0, ctx->max_keys * 8, s));
-    CU(cudaMemsetAsync(ctx->rows_st.heads, 0, 3ull * ctx->rows_tiles * 8, s));
-    CU(cudaMemsetAsync(&ctx->d_ctl->rows_ticket, 0, sizeof(unsigned int), s));
+    if (!zeroed) {
+        CU(cudaMemsetAsync(ctx->rows.count, 0, ctx->max_keys * 8, s));
+        CU(cudaMemsetAsync(ctx->rows_st.heads, 0, 3ull * ctx->rows_tiles * 8, s));
+        CU(cudaMemsetAsync(&ctx->d_ctl->rows_ticket, 0, sizeof(unsigned int), s));
+    }
     rows_kernel<<<ctx->rows_tiles, ROWS_THREADS, 0, s>>>(ctx->bufs, ctx->ent, ctx->bytes_base, ctx->rows,
                                                         ctx->cfg.num_reducers, ctx->cfg.reduce_kind,
                                                         ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl);
@@ -1020,7 +1033,7 @@ int mr_reduce_all(mr_ctx *ctx)
     int rc;
     if (!ctx->imported) { if ((rc = launch_compact(ctx))) return rc; }
     if ((rc = launch_sort(ctx))) return rc;
-    if ((rc = launch_rows(ctx))) return rc;
+    if ((rc = launch_rows(ctx, true))) return rc;
     CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
     ctx->red_timed = true;
     ctx->state = mr_ctx::REDUCED;
@@ -1043,7 +1056,7 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
             // bitonic network; more (and keys of bounded length): the radix sort again, round by round
             const bool lsd = ctx->h_ctl->n_tie > (1u << 16) && ctx->h_ctl->max_tie_len <= 7 * 12;
             if ((rc = lsd ? run_lsd_ties(ctx, ctx->h_ctl->max_tie_len) : run_general_ties(ctx, ctx->h_ctl->n_tie))) return rc;
-            if ((rc = launch_rows(ctx))) return rc;
+            if ((rc = launch_rows(ctx, false))) return rc;
                     CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
             CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
             CU(cudaStreamSynchronize(ctx->stream));

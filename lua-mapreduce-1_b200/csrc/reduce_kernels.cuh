@@ -301,7 +301,8 @@ __device__ inline uint32_t build_digit_plan(uint64_t vlo, uint32_t vhi, DigitRun
 // digit histograms of every pass in one read of the keys.  Every CTA derives the digit plan from
 // the varying-bit masks for itself (a few dozen instructions of one thread, hidden behind the
 // zeroing of the histogram); CTA 0 publishes it for the passes and clamps n.
-__global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, unsigned long long max_keys, Ctl *ctl)
+__global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, unsigned long long max_keys, Ctl *ctl,
+                                                         uint32_t *status, uint32_t max_tiles)
 {
     __shared__ unsigned int h[MAX_PASSES][RADIX_BINS];
     __shared__ DigitRun runs[MAX_PASSES][8];
@@ -329,6 +330,15 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, 
         }
     }
     if (np == 0) return;
+    {
+        // the look-back status words of the passes to come (only the passes and tiles that exist)
+        uint64_t nact = (n + blockDim.x - 1) / blockDim.x;
+        if (nact < 1) nact = 1;
+        if (nact > gridDim.x) nact = gridDim.x;
+        const uint64_t ntiles = (n + SORT_TILE - 1) / SORT_TILE, per_pass = ntiles * RADIX_BINS;
+        for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < np * per_pass; i += nact * blockDim.x)
+            status[(i / per_pass) * max_tiles * RADIX_BINS + i % per_pass] = 0;
+    }
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const SortItem it = items[i];
@@ -539,9 +549,19 @@ __device__ inline bool tie_less(const TieItem &a, const TieItem &b, const EntryA
 }
 
 __global__ void __launch_bounds__(256) tie_mark_kernel(SortBufs bufs, TieItem *ties, uint32_t tie_cap,
-                                                       EntryArrays ent, const uint8_t *bytes, Ctl *ctl)
+                                                       EntryArrays ent, const uint8_t *bytes, Ctl *ctl,
+                                                       unsigned long long *rows_count, unsigned long long *rows_status,
+                                                       uint32_t rows_status_words)
 {
     const uint64_t n = ctl->n;
+    {
+        // what the rows kernel expects to be zero: its counts (at most one row per item), its
+        // look-back words, its ticket
+        const uint64_t gstride = (uint64_t)gridDim.x * blockDim.x, g0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (uint64_t i = g0; i < n; i += gstride) rows_count[i] = 0;
+        for (uint64_t i = g0; i < rows_status_words; i += gstride) rows_status[i] = 0;
+        if (g0 == 0) ctl->rows_ticket = 0;
+    }
     SortItem *items = bufs.item[ctl->npasses & 1];
     const uint32_t lane = threadIdx.x & 31, lt = lanemask_lt();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
