@@ -253,14 +253,17 @@ class worker:
         ntasks, it, sleep = 0, 0, DEFAULT_SLEEP
         while it < self.max_iter and ntasks < self.max_tasks:
             with b.lock:
-                status = b.task["status"]
+                task = b.task
                 if b.finished:
                     return ntasks
-            if status in (TASK_WAIT, TASK_FINISHED):
-                it += 1
-                time.sleep(min(sleep, self.max_sleep))
-                sleep *= 1.5    # worker.lua:100-101 back-off
-                continue
+                # nothing to take: no task yet, or every job of this iteration is already done by
+                # this worker and the server is still in its final phase (a "loop" iteration
+                # replaces b.task) -- the reference's take_next_job returns nothing then
+                if task["status"] in (TASK_WAIT, TASK_FINISHED) or task is getattr(self, "_done_task", None):
+                    it += 1
+                    b.lock.wait(min(sleep, self.max_sleep))
+                    sleep *= 1.5    # worker.lua:100-101 back-off
+                    continue
             self._run_task()
             ntasks += 1
             it, sleep = 0, DEFAULT_SLEEP
@@ -293,7 +296,11 @@ class worker:
 
     def _run_task(self):
         b = self.board
-        params = b.task["params"]
+        # one iteration = one task document with its own job lists; a "loop" iteration of the
+        # server swaps all of them, so this run keeps the ones it started with
+        with b.lock:
+            task, map_jobs, red_jobs, results = b.task, b.map_jobs, b.red_jobs, b.results
+        params = task["params"]
         mods = params["mods"]
         desc = self._native_config(mods)
         R = int(desc["num_reducers"])
@@ -315,18 +322,18 @@ class worker:
             return (j["_id"], v if isinstance(v, (str, bytes)) else id(v))
 
         with b.lock:
-            wanted = [signature(j) for j in b.map_jobs]
-        resident = (b.task["iteration"] > 1 and getattr(self, "_resident", None) == (id(ctx), wanted)
+            wanted = [signature(j) for j in map_jobs]
+        resident = (task["iteration"] > 1 and getattr(self, "_resident", None) == (id(ctx), wanted)
                     and len(wanted) > 0)
         ctx.job_begin(keep_input=resident)
         self.kept_input = resident
         # ---- map jobs (job.lua:166-227): stage every split this worker claims
         mine = []
         while True:
-            job = self._take(b.map_jobs)
+            job = self._take(map_jobs)
             if job is None:
                 with b.lock:
-                    if all(j["status"] in (FINISHED, WRITTEN, FAILED) for j in b.map_jobs):
+                    if all(j["status"] in (FINISHED, WRITTEN, FAILED) for j in map_jobs):
                         break
                     b.lock.wait(DEFAULT_SLEEP)
                 continue
@@ -360,20 +367,20 @@ class worker:
         self._resident = (id(ctx), wanted) if len(mine) == len(wanted) else None
         # ---- wait for the reduce phase, publish one reduce job per non-empty partition
         with b.lock:
-            while b.task["status"] == TASK_MAP:
+            while task["status"] == TASK_MAP:
                 b.lock.wait(DEFAULT_SLEEP)
-            if not b.task.get("reduce_ready"):
+            if not task.get("reduce_ready"):
                 rows_per_part = self._partition_sizes(ctx)
                 width = len(str(max(R - 1, 0)))
                 for p in range(R):   # server.lua:297-324: empty partitions get no job, no file
                     if rows_per_part[p]:
                         name = f"{params['result_ns']}.P{p:0{width}d}"
-                        b.red_jobs.append(_make_job(p, {"partition": p, "result": name}))
-                b.task["reduce_ready"] = True
+                        red_jobs.append(_make_job(p, {"partition": p, "result": name}))
+                task["reduce_ready"] = True
                 b.lock.notify_all()
         # ---- reduce jobs (job.lua:232-295): rows are already merged and sorted in HBM
         while True:
-            job = self._take(b.red_jobs)
+            job = self._take(red_jobs)
             if job is None:
                 break
             t0, c0 = time.time(), time.process_time()
@@ -383,14 +390,15 @@ class worker:
                 if records:     # number keys travel as 4 big-endian bytes
                     rows = [(int.from_bytes(k, "big"), c) for k, c in rows]
                 with b.lock:
-                    b.results[job["value"]["result"]] = (lambda r=rows: iter(r))
+                    results[job["value"]["result"]] = (lambda r=rows: iter(r))
                 self._mark(job, WRITTEN, written_time=time.time(), cpu_time=time.process_time() - c0,
                            real_time=time.time() - t0)
             except Exception as e:
                 self._broken(job, e)
         with b.lock:
-            while not all(j["status"] in (WRITTEN, FAILED) for j in b.red_jobs):
+            while not all(j["status"] in (WRITTEN, FAILED) for j in red_jobs):
                 b.lock.wait(DEFAULT_SLEEP)
+        self._done_task = task
 
     @staticmethod
     def _partition_sizes(ctx):
