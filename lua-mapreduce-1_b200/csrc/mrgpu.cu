@@ -1029,6 +1029,10 @@ int mr_reduce_all(mr_ctx *ctx)
     if (ctx->state == mr_ctx::IDLE) { int rc = mr_map_finish(ctx); if (rc) return rc; }
     if (ctx->state != mr_ctx::MAPPED) return fail(ctx, MR_ERR_INVALID, "mr_reduce_all: already reduced");
     if (ctx->map_dirty) { int rc = mr_map_finish(ctx); if (rc) return rc; }
+    if (ctx->cfg.world_size > 1 && !ctx->imported)
+        return fail(ctx, MR_ERR_INVALID, "mr_reduce_all: this context is rank %u of %u; run one of the shuffles "
+                    "(mr_shuffle_p2p, mr_shuffle_nccl, mr_shuffle_count/pack/import) after mr_map_finish first",
+                    ctx->cfg.rank, ctx->cfg.world_size);
     CU(cudaEventRecord(ctx->ev_red0, ctx->stream));
     int rc;
     if (!ctx->imported) { if ((rc = launch_compact(ctx))) return rc; }

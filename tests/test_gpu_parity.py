@@ -305,6 +305,18 @@ def test_native_transport_single_rank():
         ctx.close()
 
 
+def test_a_rank_of_many_must_shuffle_before_it_reduces():
+    ctx = _native.Context(10, 1 << 20, max_keys=1 << 12, world_size=2, rank=0)
+    try:
+        ctx.map_split(0, b"a b a")
+        ctx.map_finish()
+        with pytest.raises(_native.NativeError) as e:
+            ctx.reduce_all()
+        assert e.value.code == _native.MR_ERR_INVALID and "shuffle" in str(e.value)
+    finally:
+        ctx.close()
+
+
 def test_p2p_shuffle_single_rank():
     # the peer-to-peer shuffle with a world of one: the window is this context's own memory
     splits, tok = corpus.generate(lines=[900, 1, 0, 1100])
