@@ -189,12 +189,13 @@ def main():
     shuffle_slot = [None]
     shuffle_kind = ["nccl all-to-all, exact sizes"]
     biggest_seen = [0]
+    shuffle_stats = {}
 
     def do_shuffle():
         if shuffle_kind[0].startswith("p2p"):
             ctx.shuffle_p2p()
             return
-        biggest = parallel.shuffle(ctx, slot_bytes=shuffle_slot[0])
+        biggest = parallel.shuffle(ctx, slot_bytes=shuffle_slot[0], stats=shuffle_stats)
         if shuffle_slot[0] is None:
             biggest_seen[0] = biggest
             shuffle_slot[0] = parallel.slot_for(biggest)
@@ -250,7 +251,7 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
     barrier()
     t_start = torch.cuda.Event(enable_timing=True); t_end = torch.cuda.Event(enable_timing=True)
     t_start.record()
@@ -262,6 +263,7 @@ def main():
         ev[s][1].record()
         if world > 1:
             do_shuffle()
+        ev[s][3].record()
         ctx.reduce_all()
         ev[s][2].record()
         launches += int(ctx.stats().launches)
@@ -273,10 +275,12 @@ def main():
     ms_total = t_start.elapsed_time(t_end)
     map_ms = [ev[s][0].elapsed_time(ev[s][1]) for s in range(args.steps)]
     red_ms = [ev[s][1].elapsed_time(ev[s][2]) for s in range(args.steps)]
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    shuf_ms = [ev[s][1].elapsed_time(ev[s][3]) for s in range(args.steps)]
+    t = torch.tensor([ms_total, sum(shuf_ms) / len(shuf_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / args.steps
+    ms_step = float(t[0].item()) / args.steps
+    shuf_ms_max = float(t[1].item())
     value = tokens_total / (ms_step * 1e-3)
 
     # ---- end to end through the public API: host buffers in, rows out, every step
@@ -334,6 +338,25 @@ def main():
                 "job_frac": (bytes_total + keybytes_total + 8 * rows_total) / world / (ms_step * 1e-3) / 1e9 / peak,
                 "map_ms": map_avg_ms, "reduce_ms": sum(red_ms) / len(red_ms)}
 
+    # the exchange against the NVLink roofline: bytes that leave this rank per job over
+    # the time from the end of its map side to the end of the exchange (waiting for the slowest
+    # sender included), max over ranks; 900 GB/s per direction per GPU
+    nvlink = None
+    if world > 1 and "matrix" in shuffle_stats:
+        mtx = shuffle_stats["matrix"][rank]
+        away = [d for d in range(world) if d != rank]
+        nrec_away = int(sum(int(mtx[d]) for d in away))
+        long_away = int(sum(int(mtx[world + d]) for d in away))
+        mean_key = keybytes_total / max(rows_total, 1)
+        rec_bytes = 32 if shuffle_kind[0].startswith("p2p") else 24
+        nvlink = {"shuffle_ms": shuf_ms_max, "records_leaving_rank0": nrec_away,
+                  "wire_bytes_rank0": rec_bytes * nrec_away + long_away,
+                  "algorithmic_bytes_rank0": int(nrec_away * (mean_key + 8)),
+                  "achieved": nrec_away * (mean_key + 8) / (shuf_ms_max * 1e-3) / 1e9, "peak": 900.0, "unit": "GB/s",
+                  "note": "algorithmic = (mean key length of the job + 8) per record leaving the rank"}
+        nvlink["frac"] = nvlink["achieved"] / nvlink["peak"]
+        nvlink["wire_frac"] = nvlink["wire_bytes_rank0"] / (shuf_ms_max * 1e-3) / 1e9 / 900.0
+
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         from oracle import oracle as O
@@ -352,7 +375,7 @@ def main():
                    "partitions": R, "seed": hex(SEED), "parallelism": f"splits sharded over {world} rank(s), "
                    f"owner = {owners}" + (f", shuffle = {shuffle_kind[0]}" if world > 1 else ""),
                    "l2": "input per rank (294 MB) is larger than L2 (126 MB); no flush between steps"},
-        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "roofline": roofline, "nvlink": nvlink, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }))
     ctx.close()
     if world > 1:

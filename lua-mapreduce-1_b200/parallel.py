@@ -84,8 +84,9 @@ def exchange_segments(send, send_off, recv, recv_off, group=None):
     return recv
 
 
-def shuffle(ctx, group=None, slot_bytes=None):
-    """The shuffle of one job on a _native.Context (GPU ranks).
+def shuffle(ctx, group=None, slot_bytes=None, stats=None):
+    """The shuffle of one job on a _native.Context (GPU ranks).  stats: a dict that receives the
+    size matrix of an exact-size shuffle ("matrix": [src][records per dst..., long-key bytes per dst...]).
 
     slot_bytes=None: exact sizes -- count -> gather (one host sync) -> pack -> all-to-all -> import.
         Returns the largest segment any rank sends to any rank, which a caller running the same
@@ -103,6 +104,8 @@ def shuffle(ctx, group=None, slot_bytes=None):
         return int(slot_bytes)
     counts = device_i64(ctx.shuffle_count(), 2 * W, dev)
     matrix = gather_counts(counts, group)
+    if stats is not None:
+        stats["matrix"] = matrix
     send_off, recv_off, recv_nrec = plan_from_counts(matrix, rank)
     base, off, nrec = ctx.shuffle_pack(matrix[rank].astype(np.uint64))
     assert np.array_equal(off.astype(np.int64), send_off)
