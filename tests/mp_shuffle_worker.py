@@ -48,6 +48,40 @@ def main():
     tot = torch.tensor([sum(merged.values())], dtype=torch.int64)
     dist.all_reduce(tot)
     assert int(tot.item()) == want.tokens
+    # balanced owners: the collective that picks world-1 splitters from a finished job, with a
+    # stand-in for the context (the rows this rank would hold under partition-mod-world ownership)
+    def sort_word(key):
+        return int.from_bytes(key[:7].ljust(7, b"\0"), "big") << 8 | min(len(key), 8)
+
+    my_rows = [(int(p), k) for p, k in zip(want.part, want.keys()) if parallel.owner_of_partition(int(p), world) == rank]
+
+    class FakeContext:
+        def __init__(self):
+            self.world_size, self.rank, self.rows, self.installed = world, rank, my_rows, None
+
+        def job_sync(self):
+            return None
+
+        def rows_part_begin(self):
+            return np.searchsorted(np.array([p for p, _ in self.rows], dtype=np.int64), np.arange(R + 1)).astype(np.uint64)
+
+        def row_sort_word(self, row):
+            p, k = self.rows[row]
+            return p, sort_word(k)
+
+        def set_owners(self, splitters):
+            self.installed = list(splitters)
+
+    fake = FakeContext()
+    splitters = parallel.balance_owners(fake)
+    assert fake.installed == splitters and len(splitters) == world - 1 and splitters == sorted(splitters)
+    everyone = [None] * world
+    dist.all_gather_object(everyone, splitters)
+    assert all(e == splitters for e in everyone)                      # every rank installs the same cut points
+    owner = [sum(1 for sp in splitters if sp <= (int(p), sort_word(k))) for p, k in zip(want.part, want.keys())]
+    assert owner == sorted(owner)                                     # contiguous pieces of the output order
+    share = np.bincount(owner, minlength=world)
+    assert share.max() - share.min() <= 16, share                     # equal shares (keys equal in 7 bytes stay together)
     dist.barrier()
     dist.destroy_process_group()
     print(f"rank {rank}: ok, {len(merged)} keys owned")
