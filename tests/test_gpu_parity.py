@@ -401,3 +401,20 @@ def test_multi_gpu_shuffle_parity():
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
     assert p.stdout.count("multi-GPU parity ok") == n
+
+
+def test_multi_gpu_fuzz():
+    # randomised cases through every multi-GPU path; skipped on a single-GPU box
+    import os
+    import subprocess
+    import sys
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={min(n, 4)}",
+           "--master-addr", "127.0.0.1", "--master-port", "29657", os.path.join(root, "tests", "mp_gpu_fuzz.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=500, cwd=root)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
+    assert p.stdout.count("multi-GPU fuzz ok") == min(n, 4)
