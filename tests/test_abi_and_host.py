@@ -51,6 +51,17 @@ def test_c_worker_builds_against_the_header_alone(tmp_path):
         assert p.returncode == 1 and "mr_ctx_create" in p.stderr and "no CPU path" in p.stderr
 
 
+def test_lua_c_api_binding_type_checks_against_the_header():
+    # bindings/lua_mrgpu.c is the Lua 5.2 C-API glue a maintainer of the reference would add; no Lua
+    # here, so it is compiled (not linked) against include/mrgpu.h and the declarations of the Lua
+    # functions it uses (tests/lua_stub, signatures of the 5.2 manual) with warnings as errors
+    import subprocess
+    p = subprocess.run(["gcc", "-std=gnu11", "-Wall", "-Wextra", "-Werror", "-fsyntax-only",
+                        "-I", os.path.join(ROOT, "tests", "lua_stub"), "-I", os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "bindings", "lua_mrgpu.c")], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+
+
 def test_bad_config_is_rejected():
     lib = _native.load()
     h = ctypes.c_void_p()
