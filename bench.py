@@ -138,7 +138,9 @@ def run_reference(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
         "config": {"workload": "config2: synthetic Europarl-shaped word count, 197 splits x 10k lines, R=10",
                    "note": "the Lua+MongoDB reference cannot run in this image (no Lua VM, no mongod); "
-                           "this is its CPU algorithm restated in C with OpenMP threads standing in for workers"},
+                           "this is its CPU algorithm restated in C with OpenMP threads standing in for workers; "
+                           "one config-2 shard is timed at every N (the host cores' tokens/s does not depend on how "
+                           "many shards they are given)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample_txt},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
