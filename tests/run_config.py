@@ -2,9 +2,9 @@
 """Runs one of BASELINE.json's parity configs at (near) full size on one GPU, compares with the oracle
 exactly, and prints one JSON line.  Not a bench line (bench.py is config 2); evidence for configs 3-5.
 
-    python scripts/run_config.py --config 3   # 10x corpus, 1,970 splits, ~491 M tokens, word count
-    python scripts/run_config.py --config 4   # bigram count over the config-2 corpus
-    python scripts/run_config.py --config 5   # integer-key group-by-sum, Zipf(1.2) keys + heavy hitters
+    python tests/run_config.py --config 3   # 10x corpus, 1,970 splits, ~491 M tokens, word count
+    python tests/run_config.py --config 4   # bigram count over the config-2 corpus
+    python tests/run_config.py --config 5   # integer-key group-by-sum, Zipf(1.2) keys + heavy hitters
 """
 import argparse
 import json
