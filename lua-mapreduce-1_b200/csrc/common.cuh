@@ -56,6 +56,44 @@ enum : uint32_t {
     ERR_SHUFFLE_FULL = 8u,
 };
 
+// ---------------------------------------------------------------- both sides of the fence
+// The partitioner, the sort words and the owner map are also compiled for the host
+// (tests/host_helpers.cu), so that the very code the kernels run is unit-tested on a machine
+// without a GPU.  The four intrinsics they use, spelled for both sides; in device code each
+// is exactly the intrinsic it names.
+__host__ __device__ __forceinline__ unsigned long long ld_ro64(const unsigned long long *p)
+{
+#ifdef __CUDA_ARCH__
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t bswap32(uint32_t x)
+{
+#ifdef __CUDA_ARCH__
+    return __byte_perm(x, 0, 0x0123);
+#else
+    return __builtin_bswap32(x);
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b)
+{
+#ifdef __CUDA_ARCH__
+    return __umulhi(a, b);
+#else
+    return (uint32_t)(((unsigned long long)a * b) >> 32);
+#endif
+}
+__host__ __device__ __forceinline__ int clz32(uint32_t x)
+{
+#ifdef __CUDA_ARCH__
+    return __clz((int)x);
+#else
+    return x ? __builtin_clz(x) : 32;
+#endif
+}
+
 // ---------------------------------------------------------------- whitespace
 // C-locale isspace (Lua's %s, mapfn.lua:5): 0x20 and 0x09..0x0D.  Returns 0x80 in
 // every byte lane of x that is whitespace; exact for every lane (no borrow tricks).
@@ -102,25 +140,25 @@ __device__ __forceinline__ uint32_t hash_key(const Key &k)
 
 // 8 bytes at an arbitrary byte offset, little-endian.  May read up to 15 bytes past
 // off; every byte space carries that much slack.
-__device__ __forceinline__ uint64_t load8(const uint8_t *base, uint64_t off)
+__host__ __device__ __forceinline__ uint64_t load8(const uint8_t *base, uint64_t off)
 {
     const unsigned long long *p = (const unsigned long long *)(base + (off & ~7ull));
     uint32_t sh = (uint32_t)(off & 7) * 8;
-    uint64_t w0 = __ldg(p);
+    uint64_t w0 = ld_ro64(p);
     if (sh == 0) return w0;
-    uint64_t w1 = __ldg(p + 1);
+    uint64_t w1 = ld_ro64(p + 1);
     return (w0 >> sh) | (w1 << (64 - sh));
 }
 
-__device__ __forceinline__ uint64_t low_bytes_mask(uint32_t nbytes) // nbytes in 0..8
+__host__ __device__ __forceinline__ uint64_t low_bytes_mask(uint32_t nbytes) // nbytes in 0..8
 {
     return nbytes >= 8 ? ~0ull : ((1ull << (8 * nbytes)) - 1);
 }
 
-__device__ __forceinline__ uint64_t bswap64(uint64_t v)
+__host__ __device__ __forceinline__ uint64_t bswap64(uint64_t v)
 {
     uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
-    return ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | __byte_perm(hi, 0, 0x0123);
+    return ((uint64_t)bswap32(lo) << 32) | bswap32(hi);
 }
 
 __device__ inline bool bytes_equal(const uint8_t *base, uint64_t a, uint64_t b, uint32_t len)
@@ -146,7 +184,7 @@ __device__ __forceinline__ bool same_key(const Key &a, const Key &b, const uint8
 // bits, min(remaining length, 8) in the low byte.  Numeric order of the words of round 0,
 // then round 1, ... is unsigned-byte lexicographic order with the shorter key first
 // (Lua string `<`, utils.lua:126 / utils.lua:214).
-__device__ inline uint64_t sort_chunk(const Key &k, const uint8_t *bytes, uint32_t round)
+__host__ __device__ inline uint64_t sort_chunk(const Key &k, const uint8_t *bytes, uint32_t round)
 {
     const uint32_t len = key_len(k);
     const uint32_t skip = 7u * round;
@@ -179,7 +217,7 @@ struct OwnerMap {
     uint32_t world;
 };
 
-__device__ __forceinline__ uint32_t owner_of(const OwnerMap &m, uint32_t part, uint64_t w /* sort_chunk(key, bytes, 0) */)
+__host__ __device__ __forceinline__ uint32_t owner_of(const OwnerMap &m, uint32_t part, uint64_t w /* sort_chunk(key, bytes, 0) */)
 {
     if (m.n == 0) return part % m.world;
     uint32_t lo = 0, hi = m.n; // first splitter greater than (part, w)
@@ -202,16 +240,16 @@ __device__ __forceinline__ uint32_t owner_of(const OwnerMap &m, uint32_t part, u
 // doubles below 2^32 equals the integer remainder.
 struct FnvLua52 {
     uint32_t h;
-    __device__ __forceinline__ FnvLua52() : h(2166136261u) {}
-    __device__ __forceinline__ void byte(uint32_t c)
+    __host__ __device__ __forceinline__ FnvLua52() : h(2166136261u) {}
+    __host__ __device__ __forceinline__ void byte(uint32_t c)
     {
         // Only the low 32 bits of the rounded product survive `% 2^32`, and the rounding touches
         // at most the low 4 bits plus a carry that runs upwards, so it is done on the low word;
         // the high word only says how many bits are dropped: p < 2^57, top bit = 63 - clz(p),
         // s = top - 52 = 11 - clz(high word) when that is positive.
         uint32_t lo = h * 16777619u;
-        const uint32_t hi = __umulhi(h, 16777619u);
-        const int s = 11 - __clz((int)hi);
+        const uint32_t hi = mulhi32(h, 16777619u);
+        const int s = 11 - clz32(hi);
         if (s > 0) {
             // round to nearest, ties to even: adding half-1+odd(quotient) carries exactly when it must
             const uint32_t add = (1u << (s - 1)) - 1u + ((lo >> s) & 1u);
@@ -219,10 +257,10 @@ struct FnvLua52 {
         }
         h = lo ^ c;
     }
-    __device__ __forceinline__ uint32_t partition(uint32_t num_reducers) const { return h % num_reducers; }
+    __host__ __device__ __forceinline__ uint32_t partition(uint32_t num_reducers) const { return h % num_reducers; }
 };
 
-__device__ inline uint32_t partition_of_key(const Key &k, const uint8_t *bytes, uint32_t num_reducers)
+__host__ __device__ inline uint32_t partition_of_key(const Key &k, const uint8_t *bytes, uint32_t num_reducers)
 {
     FnvLua52 f;
     const uint32_t len = key_len(k);
