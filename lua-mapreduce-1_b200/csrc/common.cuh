@@ -59,7 +59,7 @@ enum : uint32_t {
 // ---------------------------------------------------------------- both sides of the fence
 // The partitioner, the sort words and the owner map are also compiled for the host
 // (tests/host_helpers.cu), so that the very code the kernels run is unit-tested on a machine
-// without a GPU.  The four intrinsics they use, spelled for both sides; in device code each
+// without a GPU.  The intrinsics they use, spelled for both sides; in device code each
 // is exactly the intrinsic it names.
 __host__ __device__ __forceinline__ unsigned long long ld_ro64(const unsigned long long *p)
 {
@@ -85,6 +85,14 @@ __host__ __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b)
     return (uint32_t)(((unsigned long long)a * b) >> 32);
 #endif
 }
+__host__ __device__ __forceinline__ int ffs64(unsigned long long x) // 1-based index of the lowest set bit, 0 if none
+{
+#ifdef __CUDA_ARCH__
+    return __ffsll((long long)x);
+#else
+    return __builtin_ffsll((long long)x);
+#endif
+}
 __host__ __device__ __forceinline__ int clz32(uint32_t x)
 {
 #ifdef __CUDA_ARCH__
@@ -97,7 +105,7 @@ __host__ __device__ __forceinline__ int clz32(uint32_t x)
 // ---------------------------------------------------------------- whitespace
 // C-locale isspace (Lua's %s, mapfn.lua:5): 0x20 and 0x09..0x0D.  Returns 0x80 in
 // every byte lane of x that is whitespace; exact for every lane (no borrow tricks).
-__device__ __forceinline__ uint32_t space_flags(uint32_t x)
+__host__ __device__ __forceinline__ uint32_t space_flags(uint32_t x)
 {
     uint32_t y = x & 0x7F7F7F7Fu;
     uint32_t eq20 = ~((y ^ 0x20202020u) + 0x7F7F7F7Fu); // bit7 set iff low7 == 0x20
@@ -107,7 +115,7 @@ __device__ __forceinline__ uint32_t space_flags(uint32_t x)
 }
 
 // 4-bit mask (bit i = byte i of x is NOT whitespace)
-__device__ __forceinline__ uint32_t nonspace_nibble(uint32_t x)
+__host__ __device__ __forceinline__ uint32_t nonspace_nibble(uint32_t x)
 {
     uint32_t f = (~space_flags(x)) & 0x80808080u;
     return (((f >> 7) * 0x01020408u) >> 24) & 0xFu;

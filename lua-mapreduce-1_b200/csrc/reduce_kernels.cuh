@@ -262,7 +262,7 @@ __global__ void sort_setup_kernel(Ctl *ctl, unsigned long long max_keys)
     ctl->npasses = pass;
 }
 
-__device__ __forceinline__ uint32_t extract_digit(const DigitRun *runs, uint32_t nruns, uint32_t hi,
+__host__ __device__ __forceinline__ uint32_t extract_digit(const DigitRun *runs, uint32_t nruns, uint32_t hi,
                                                   uint64_t lo)
 {
     uint32_t d = 0;
@@ -276,16 +276,16 @@ __device__ __forceinline__ uint32_t extract_digit(const DigitRun *runs, uint32_t
 
 // The digit plan again, run by run instead of bit by bit, into whatever arrays the caller has
 // (shared memory in radix_hist_kernel).  Same plan as sort_setup_kernel.
-__device__ inline uint32_t build_digit_plan(uint64_t vlo, uint32_t vhi, DigitRun (*runs)[8], unsigned int *nruns)
+__host__ __device__ inline uint32_t build_digit_plan(uint64_t vlo, uint32_t vhi, DigitRun (*runs)[8], unsigned int *nruns)
 {
     uint32_t pass = 0, used = 0, nr = 0;
     for (int half = 0; half < 2; ++half) {
         uint64_t v = half ? (uint64_t)vhi : vlo; // runs do not straddle the lo/hi boundary
         const uint32_t base = half ? 64 : 0;
         while (v) {
-            const uint32_t start = __ffsll((long long)v) - 1;
+            const uint32_t start = ffs64(v) - 1;
             const uint64_t ones = ~(v >> start);           // zero bits of the shifted word
-            uint32_t w = ones ? __ffsll((long long)ones) - 1 : 64 - start;
+            uint32_t w = ones ? ffs64(ones) - 1 : 64 - start;
             if (w > RADIX_BITS - used) w = RADIX_BITS - used;
             DigitRun r; r.shift = (uint8_t)(base + start); r.width = (uint8_t)w; r.dst = (uint8_t)used; r.pad = 0;
             runs[pass][nr++] = r;

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "reduce_kernels.cuh"
 
 using namespace mr;
 
@@ -64,6 +65,41 @@ uint32_t th_owner_of(uint32_t n, const uint32_t *sp_part, const unsigned long lo
     OwnerMap m;
     m.part = sp_part; m.word = sp_word; m.n = n; m.world = world;
     return owner_of(m, part, word);
+}
+
+// whitespace classification of the tokeniser: 0x80 in every byte lane of x that is C-locale isspace
+uint32_t th_space_flags(uint32_t x) { return space_flags(x); }
+uint32_t th_nonspace_nibble(uint32_t x) { return nonspace_nibble(x); }
+
+// the radix sort's digit plan for the varying bits (vlo, vhi): returns the number of passes and
+// writes, for every pass, its runs as (shift, width, dst) triples into out[pass][run][3]
+uint32_t th_digit_plan(uint64_t vlo, uint32_t vhi, uint8_t *out /* [MAX_PASSES][8][3] */, uint32_t *nruns_out /* [MAX_PASSES] */)
+{
+    DigitRun runs[MAX_PASSES][8];
+    unsigned int nruns[MAX_PASSES];
+    memset(runs, 0, sizeof runs);
+    memset(nruns, 0, sizeof nruns);
+    const uint32_t np = build_digit_plan(vlo, vhi, runs, nruns);
+    for (uint32_t p = 0; p < (uint32_t)MAX_PASSES; ++p) {
+        nruns_out[p] = nruns[p];
+        for (int r = 0; r < 8; ++r) {
+            out[(p * 8 + r) * 3 + 0] = runs[p][r].shift;
+            out[(p * 8 + r) * 3 + 1] = runs[p][r].width;
+            out[(p * 8 + r) * 3 + 2] = runs[p][r].dst;
+        }
+    }
+    return np;
+}
+
+// digit of pass `pass` of the key (hi, lo) under the plan of (vlo, vhi)
+uint32_t th_digit(uint64_t vlo, uint32_t vhi, uint32_t pass, uint32_t hi, uint64_t lo)
+{
+    DigitRun runs[MAX_PASSES][8];
+    unsigned int nruns[MAX_PASSES];
+    memset(runs, 0, sizeof runs);
+    memset(nruns, 0, sizeof nruns);
+    const uint32_t np = build_digit_plan(vlo, vhi, runs, nruns);
+    return pass < np ? extract_digit(runs[pass], nruns[pass], hi, lo) : 0;
 }
 
 } // extern "C"

@@ -1,5 +1,6 @@
-"""The device helpers of csrc/common.cuh, compiled for the host (tests/host_helpers.cu): the
-partitioner, the sort words and the owner map that the kernels run, checked on CPU against the
+"""The device helpers of csrc/common.cuh and csrc/reduce_kernels.cuh, compiled for the host
+(tests/host_helpers.cu): the partitioner, the sort words, the owner map, the tokeniser's whitespace
+classifier and the radix sort's digit plan -- the source the kernels run -- checked on CPU against the
 oracle's binary64 partitioner, the library's host-side mr_partition_of, and Python's own byte-string
 order (Lua's `<` on strings in the C locale).  No GPU needed: the device build of the same source is
 byte-for-byte what it was before these functions became __host__ __device__ (checked by comparing
@@ -22,7 +23,8 @@ OUT = os.path.join(ROOT, "tests", "_build", "libhost_helpers.so")
 
 @pytest.fixture(scope="module")
 def lib():
-    deps = [SRC, os.path.join(ROOT, "lua-mapreduce-1_b200", "csrc", "common.cuh")]
+    deps = [SRC, os.path.join(ROOT, "lua-mapreduce-1_b200", "csrc", "common.cuh"),
+            os.path.join(ROOT, "lua-mapreduce-1_b200", "csrc", "reduce_kernels.cuh")]
     if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
         nvcc = "/usr/local/cuda/bin/nvcc"
@@ -38,6 +40,14 @@ def lib():
     L.th_sort_word.argtypes = [C.c_char_p, C.c_uint64, C.c_uint32]
     L.th_owner_of.restype = C.c_uint32
     L.th_owner_of.argtypes = [C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.c_uint32, C.c_uint32, C.c_uint64]
+    L.th_space_flags.restype = C.c_uint32
+    L.th_space_flags.argtypes = [C.c_uint32]
+    L.th_nonspace_nibble.restype = C.c_uint32
+    L.th_nonspace_nibble.argtypes = [C.c_uint32]
+    L.th_digit_plan.restype = C.c_uint32
+    L.th_digit_plan.argtypes = [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint8), C.POINTER(C.c_uint32)]
+    L.th_digit.restype = C.c_uint32
+    L.th_digit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
     return L
 
 
@@ -96,3 +106,59 @@ def test_owner_map_is_upper_bound_over_the_splitters(lib):
         for p, w in probes:
             got = lib.th_owner_of(len(sp), parts, wordsv, world, p, w)
             assert got == bisect.bisect_right(sp, (p, w)), (world, p, w)
+
+
+def test_whitespace_flags_are_isspace_in_every_byte_lane(lib):
+    # mapfn.lua:5 splits on %s = C-locale isspace: 0x20 and 0x09..0x0D.  The SWAR classifier must be
+    # exact in each byte lane whatever the neighbouring bytes are (no borrow from lane to lane)
+    space = {0x20, 0x09, 0x0A, 0x0B, 0x0C, 0x0D}
+    rnd = random.Random(4)
+    edge = [0x00, 0x08, 0x09, 0x0D, 0x0E, 0x1F, 0x20, 0x21, 0x7F, 0x80, 0x88, 0x89, 0x8D, 0xA0, 0xFF]
+    words = [a | b << 8 | c << 16 | d << 24 for a in edge for b in edge for c in edge for d in edge[::3]]
+    words += [rnd.getrandbits(32) for _ in range(100000)]
+    words += [b | (b2 << (8 * lane)) for b in range(256) for b2 in (0x09, 0x20, 0xFF) for lane in (1, 2, 3)]
+    for x in words:
+        want = sum(0x80 << (8 * i) for i in range(4) if (x >> (8 * i)) & 0xFF in space)
+        assert lib.th_space_flags(x) == want, hex(x)
+        nib = sum(1 << i for i in range(4) if (x >> (8 * i)) & 0xFF not in space)
+        assert lib.th_nonspace_nibble(x) == nib, hex(x)
+
+
+def test_digit_plan_covers_the_varying_bits_once_and_sorts_like_the_keys(lib):
+    rnd = random.Random(5)
+    MAXP = 12
+    for trial in range(300):
+        vlo = rnd.getrandbits(64) & rnd.getrandbits(64) if trial % 3 else rnd.getrandbits(64)
+        vhi = rnd.getrandbits(32) & rnd.getrandbits(32) & (0xF if trial % 2 else 0xFFFFFFFF)
+        if trial == 0:
+            vlo, vhi = 0, 0
+        if trial == 1:
+            vlo, vhi = 2**64 - 1, 2**32 - 1
+        out = (C.c_uint8 * (MAXP * 8 * 3))()
+        nruns = (C.c_uint32 * MAXP)()
+        np_ = lib.th_digit_plan(vlo, vhi, out, nruns)
+        nbits = bin(vlo).count("1") + bin(vhi).count("1")
+        assert np_ == (nbits + 7) // 8
+        covered = 0
+        for p in range(np_):
+            used = 0
+            assert 1 <= nruns[p] <= 8
+            for r in range(nruns[p]):
+                shift, width, dst = out[(p * 8 + r) * 3], out[(p * 8 + r) * 3 + 1], out[(p * 8 + r) * 3 + 2]
+                assert dst == used and width >= 1 and not (shift < 64 < shift + width)    # no run straddles lo/hi
+                mask = ((1 << width) - 1) << shift
+                assert mask & covered == 0 and mask & (vlo | vhi << 64) == mask           # only varying bits, each once
+                assert mask > covered or covered == 0                                     # least significant first
+                covered |= mask
+                used += width
+            assert used == 8 or p == np_ - 1
+        assert covered == vlo | vhi << 64
+        # sorting by the digits, least significant pass first (stable), is sorting by the varying bits
+        if nbits and trial < 60:
+            keys = [(rnd.getrandbits(32), rnd.getrandbits(64)) for _ in range(200)]
+            order = list(range(len(keys)))
+            for p in range(np_):
+                order.sort(key=lambda i: lib.th_digit(vlo, vhi, p, keys[i][0], keys[i][1]))
+            want = sorted(range(len(keys)), key=lambda i: ((keys[i][0] & vhi), (keys[i][1] & vlo), ))
+            got_keys = [((keys[i][0] & vhi), (keys[i][1] & vlo)) for i in order]
+            assert got_keys == [((keys[i][0] & vhi), (keys[i][1] & vlo)) for i in want]
