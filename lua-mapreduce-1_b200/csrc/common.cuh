@@ -121,6 +121,42 @@ __host__ __device__ __forceinline__ uint32_t nonspace_nibble(uint32_t x)
     return (((f >> 7) * 0x01020408u) >> 24) & 0xFu;
 }
 
+// ---------------------------------------------------------------- token bounds from masks
+// m: bit i = byte i of a lane's 32 bytes is a token byte; nxt: the same for the 32 bytes that
+// follow; carry: 1 if the byte before byte 0 is a token byte.  A token starts where a token byte
+// follows a non-token byte; its class comes from mask algebra alone: bit i of t8 says bytes
+// i..i+7 are all token bytes (length >= 8), t16 the same for 16.
+struct TokenMasks {
+    unsigned long long w;   // m | nxt << 32
+    uint32_t starts;        // token starts among the lane's 32 bytes
+    uint32_t s_long;        // ... of tokens of 16+ bytes
+    uint32_t s_med;         // ... of 8..15 bytes
+    uint32_t s_short;       // ... of 1..7 bytes
+};
+__host__ __device__ __forceinline__ TokenMasks token_masks(uint32_t m, uint32_t nxt, uint32_t carry)
+{
+    TokenMasks r;
+    r.w = (unsigned long long)m | ((unsigned long long)nxt << 32);
+    r.starts = m & ~((m << 1) | carry);
+    unsigned long long t = r.w & (r.w >> 1);
+    t &= t >> 2;
+    const unsigned long long t8 = t & (t >> 4);
+    const unsigned long long t16 = t8 & (t8 >> 8);
+    r.s_long = r.starts & (uint32_t)t16;
+    r.s_med = r.starts & (uint32_t)t8 & ~(uint32_t)t16;
+    r.s_short = r.starts & ~(uint32_t)t8;
+    return r;
+}
+// length (1..15) of the short or medium token that starts at bit `bit` of w's low word
+__host__ __device__ __forceinline__ uint32_t token_len(unsigned long long w, uint32_t bit)
+{
+#ifdef __CUDA_ARCH__
+    return __ffs((int)~(uint32_t)(w >> bit)) - 1;
+#else
+    return (uint32_t)__builtin_ffs((int)~(uint32_t)(w >> bit)) - 1;
+#endif
+}
+
 // ---------------------------------------------------------------- hashing
 __device__ __forceinline__ uint32_t mix32(uint32_t h)
 {

@@ -251,16 +251,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         if (lane == 0) carry = prev_ns;
         uint32_t nxt = __shfl_down_sync(0xFFFFFFFFu, m, 1);
         if (lane == 31) nxt = am;
-        const unsigned long long w = (unsigned long long)m | ((unsigned long long)nxt << 32);
-        const uint32_t starts = m & ~((m << 1) | carry);
-        // bit i of t8: bytes i..i+7 are all token bytes (length >= 8); t16: length >= 16
-        unsigned long long t = w & (w >> 1);
-        t &= t >> 2;
-        const unsigned long long t8 = t & (t >> 4);
-        const unsigned long long t16 = t8 & (t8 >> 8);
-        const uint32_t s_long = starts & (uint32_t)t16;
-        const uint32_t s_med = starts & (uint32_t)t8 & ~(uint32_t)t16;
-        const uint32_t s_short = starts & ~(uint32_t)t8;
+        const TokenMasks tm = token_masks(m, nxt, carry);
+        const unsigned long long w = tm.w;
+        const uint32_t starts = tm.starts, s_long = tm.s_long, s_med = tm.s_med, s_short = tm.s_short;
         const uint32_t packed = __popc(s_short) | (__popc(s_med) << 16);
         uint32_t incl = packed;
 #pragma unroll
@@ -276,7 +269,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         while (st) {
             const uint32_t bit = __ffs((int)st) - 1;
             st &= st - 1;
-            const uint32_t len = __ffs((int)~(uint32_t)(w >> bit)) - 1; // 1..15
+            const uint32_t len = token_len(w, bit); // 1..15
             const uint16_t e = (uint16_t)((lane * 32 + bit) | (len << 10));
             if ((s_med >> bit) & 1u) ws->list[o_m--] = e;
             else ws->list[o_s++] = e;

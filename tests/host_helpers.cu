@@ -102,4 +102,15 @@ uint32_t th_digit(uint64_t vlo, uint32_t vhi, uint32_t pass, uint32_t hi, uint64
     return pass < np ? extract_digit(runs[pass], nruns[pass], hi, lo) : 0;
 }
 
+// token bounds of the map kernel: out = {starts, s_long, s_med, s_short}
+void th_token_masks(uint32_t m, uint32_t nxt, uint32_t carry, uint32_t *out)
+{
+    const TokenMasks t = token_masks(m, nxt, carry);
+    out[0] = t.starts; out[1] = t.s_long; out[2] = t.s_med; out[3] = t.s_short;
+}
+uint32_t th_token_len(uint32_t m, uint32_t nxt, uint32_t bit)
+{
+    return token_len((unsigned long long)m | ((unsigned long long)nxt << 32), bit);
+}
+
 } // extern "C"

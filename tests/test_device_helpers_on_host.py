@@ -24,7 +24,7 @@ OUT = os.path.join(ROOT, "tests", "_build", "libhost_helpers.so")
 @pytest.fixture(scope="module")
 def lib():
     deps = [SRC, os.path.join(ROOT, "lua-mapreduce-1_b200", "csrc", "common.cuh"),
-            os.path.join(ROOT, "lua-mapreduce-1_b200", "csrc", "reduce_kernels.cuh")]
+            os.path.join(ROOT, "lua-mapreduce-1_b200", "csrc", "reduce_kernels.cuh")]   # map_kernel.cuh uses the same helpers
     if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
         nvcc = "/usr/local/cuda/bin/nvcc"
@@ -48,6 +48,10 @@ def lib():
     L.th_digit_plan.argtypes = [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint8), C.POINTER(C.c_uint32)]
     L.th_digit.restype = C.c_uint32
     L.th_digit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
+    L.th_token_masks.restype = None
+    L.th_token_masks.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
+    L.th_token_len.restype = C.c_uint32
+    L.th_token_len.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
     return L
 
 
@@ -162,3 +166,37 @@ def test_digit_plan_covers_the_varying_bits_once_and_sorts_like_the_keys(lib):
             want = sorted(range(len(keys)), key=lambda i: ((keys[i][0] & vhi), (keys[i][1] & vlo), ))
             got_keys = [((keys[i][0] & vhi), (keys[i][1] & vlo)) for i in order]
             assert got_keys == [((keys[i][0] & vhi), (keys[i][1] & vlo)) for i in want]
+
+
+def test_token_bounds_from_masks_are_what_splitting_on_whitespace_gives(lib):
+    # a lane of the map kernel sees its 32 bytes, the 32 that follow and whether the byte before is a
+    # token byte; where tokens start, how long the short ones are and which class each falls in must
+    # be what bytes.split() says about the same 65 bytes
+    rnd = random.Random(6)
+    space = b" \t\n\r\x0b\x0c"
+    for trial in range(3000):
+        p_space = rnd.choice([0.05, 0.15, 0.3, 0.6, 0.95])
+        data = bytes(rnd.choice(space) if rnd.random() < p_space else rnd.randrange(0x21, 0x100) for _ in range(65))
+        if trial % 7 == 0:                                   # long runs: tokens of 16+ bytes, tokens that leave the window
+            data = bytes(0x41 if (i // rnd.choice([9, 17, 33])) % 2 else 0x20 for i in range(65))
+        carry, body = int(data[0] not in space), data[1:]
+        nib = lambda b4: lib.th_nonspace_nibble(int.from_bytes(b4, "little"))
+        m = sum(nib(body[4 * i:4 * i + 4]) << (4 * i) for i in range(8))
+        nxt = sum(nib(body[32 + 4 * i:36 + 4 * i]) << (4 * i) for i in range(8))
+        out = (C.c_uint32 * 4)()
+        lib.th_token_masks(m, nxt, carry, out)
+        starts, s_long, s_med, s_short = out
+        for i in range(32):
+            is_start = body[i] not in space and (data[i] in space)          # data[i] is the byte before body[i]
+            assert (starts >> i) & 1 == int(is_start), (trial, i)
+            if not is_start:
+                assert not ((s_long | s_med | s_short) >> i) & 1
+                continue
+            n = 0
+            while i + n < 64 and body[i + n] not in space:
+                n += 1
+            cls = "long" if n >= 16 else "med" if n >= 8 else "short"       # 16+ seen in the window is 16+ for sure
+            assert ((s_long >> i) & 1, (s_med >> i) & 1, (s_short >> i) & 1) == \
+                (int(cls == "long"), int(cls == "med"), int(cls == "short")), (trial, i, n)
+            if cls != "long":
+                assert lib.th_token_len(m, nxt, i) == n, (trial, i, n)
