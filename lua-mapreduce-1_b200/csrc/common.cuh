@@ -157,6 +157,51 @@ __host__ __device__ __forceinline__ uint32_t token_len(unsigned long long w, uin
 #endif
 }
 
+// ---------------------------------------------------------------- inline keys from staged words
+// x with the bytes at index >= n cleared; n may be <= 0 (clears all) or >= 4 (keeps all).
+// PTX shl clamps shift amounts above 31, which C does not.
+__host__ __device__ __forceinline__ uint32_t keep_low_bytes(uint32_t x, int n)
+{
+#ifdef __CUDA_ARCH__
+    uint32_t hi;
+    asm("shl.b32 %0, %1, %2;" : "=r"(hi) : "r"(0xFFFFFFFFu), "r"((uint32_t)max(n, 0) * 8u));
+    return x & ~hi;
+#else
+    return n <= 0 ? 0u : n >= 4 ? x : x & ((1u << (8 * n)) - 1u);
+#endif
+}
+// the 32 bits that start `sh` bits (0, 8, 16, 24) into the 64-bit pair (lo, hi)
+__host__ __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
+{
+#ifdef __CUDA_ARCH__
+    return __funnelshift_r(lo, hi, sh);
+#else
+    sh &= 31;
+    return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
+#endif
+}
+// a token of 1..7 bytes that starts bs/8 bytes into the aligned words x0, x1, x2:
+// w0 = bytes 0..3, w1 = bytes 4..6 | length << 24 (the two halves of an inline key's words)
+struct ShortKey { uint32_t w0, w1; };
+__host__ __device__ __forceinline__ ShortKey short_key(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t bs, uint32_t len)
+{
+    ShortKey k;
+    k.w0 = keep_low_bytes(funnel_r(x0, x1, bs), (int)len);
+    k.w1 = keep_low_bytes(funnel_r(x1, x2, bs), (int)len - 4) | (len << 24);
+    return k;
+}
+// a token of 8..15 bytes from five aligned words: the 128-bit inline key
+__host__ __device__ __forceinline__ Key medium_key(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t x4,
+                                                   uint32_t bs, uint32_t len)
+{
+    Key key;
+    key.k0 = (uint64_t)funnel_r(x0, x1, bs) | ((uint64_t)funnel_r(x1, x2, bs) << 32);
+    const uint32_t w2 = keep_low_bytes(funnel_r(x2, x3, bs), (int)len - 8);
+    const uint32_t w3 = keep_low_bytes(funnel_r(x3, x4, bs), (int)len - 12) | (len << 24);
+    key.k1 = (uint64_t)w2 | ((uint64_t)w3 << 32);
+    return key;
+}
+
 // ---------------------------------------------------------------- hashing
 __device__ __forceinline__ uint32_t mix32(uint32_t h)
 {

@@ -91,15 +91,6 @@ __device__ __forceinline__ ulonglong2 lds128(uint32_t saddr)
     return r;
 }
 
-// x with the bytes at index >= n cleared; n may be <= 0 (clears all) or >= 4 (keeps all).
-// PTX shl clamps shift amounts above 31, which C does not.
-__device__ __forceinline__ uint32_t keep_low_bytes(uint32_t x, int n)
-{
-    uint32_t hi;
-    asm("shl.b32 %0, %1, %2;" : "=r"(hi) : "r"(0xFFFFFFFFu), "r"((uint32_t)max(n, 0) * 8u));
-    return x & ~hi;
-}
-
 // slot of (bucket, way) in the split layout: [ways 0-1 of all buckets][ways 2-3 of all buckets]
 __device__ __forceinline__ uint32_t slot_of(uint32_t bucket, int way, uint32_t slots)
 {
@@ -302,8 +293,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                 const uint32_t pos = e & 1023u, len = e >> 10;
                 const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
                 const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2];
-                const uint32_t w0 = keep_low_bytes(__funnelshift_r(x0, x1, bs), (int)len);
-                const uint32_t skh = keep_low_bytes(__funnelshift_r(x1, x2, bs), (int)len - 4) | (len << 24);
+                const ShortKey skk = short_key(x0, x1, x2, bs, len);
+                const uint32_t w0 = skk.w0, skh = skk.w1;
                 const unsigned long long sk = (uint64_t)w0 | ((uint64_t)skh << 32); // bytes + length
                 const uint32_t bucket = (w0 * 0x9E3779B1u + skh * 0x85EBCA77u) >> (32 - (LOG2_SLOTS - 2));
                 // ways 0-1 live in the first half of the key array, ways 2-3 in the second, so the
@@ -347,11 +338,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
                 const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
                 const uint32_t x0 = ws->stage[wi], x1 = ws->stage[wi + 1], x2 = ws->stage[wi + 2],
                                x3 = ws->stage[wi + 3], x4 = ws->stage[wi + 4];
-                Key key;
-                key.k0 = (uint64_t)__funnelshift_r(x0, x1, bs) | ((uint64_t)__funnelshift_r(x1, x2, bs) << 32);
-                const uint32_t w2 = keep_low_bytes(__funnelshift_r(x2, x3, bs), (int)len - 8);
-                const uint32_t w3 = keep_low_bytes(__funnelshift_r(x3, x4, bs), (int)len - 12) | (len << 24);
-                key.k1 = (uint64_t)w2 | ((uint64_t)w3 << 32);
+                const Key key = medium_key(x0, x1, x2, x3, x4, bs, len);
                 *(ulonglong2 *)&ws->gq[nq + (j - t0)] = make_ulonglong2(key.k0, key.k1);
             }
             nq += min(32u, n_med - t0);

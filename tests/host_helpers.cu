@@ -113,4 +113,21 @@ uint32_t th_token_len(uint32_t m, uint32_t nxt, uint32_t bit)
     return token_len((unsigned long long)m | ((unsigned long long)nxt << 32), bit);
 }
 
+// inline keys from staged words: words = the aligned 32-bit words of the staging buffer, pos = byte
+// position of the token in it, len = its length; out = {k0, k1} (a short key has k1 = 0 here: its
+// length travels in the top byte of k0, as in the CTA table)
+void th_inline_key(const uint32_t *words, uint32_t pos, uint32_t len, unsigned long long *out)
+{
+    const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
+    if (len <= 7) {
+        const ShortKey k = short_key(words[wi], words[wi + 1], words[wi + 2], bs, len);
+        out[0] = (unsigned long long)k.w0 | ((unsigned long long)k.w1 << 32);
+        out[1] = 0;
+    } else {
+        const Key k = medium_key(words[wi], words[wi + 1], words[wi + 2], words[wi + 3], words[wi + 4], bs, len);
+        out[0] = k.k0;
+        out[1] = k.k1;
+    }
+}
+
 } // extern "C"

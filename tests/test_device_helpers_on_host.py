@@ -52,6 +52,8 @@ def lib():
     L.th_token_masks.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
     L.th_token_len.restype = C.c_uint32
     L.th_token_len.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
+    L.th_inline_key.restype = None
+    L.th_inline_key.argtypes = [C.POINTER(C.c_uint32), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
     return L
 
 
@@ -200,3 +202,22 @@ def test_token_bounds_from_masks_are_what_splitting_on_whitespace_gives(lib):
                 (int(cls == "long"), int(cls == "med"), int(cls == "short")), (trial, i, n)
             if cls != "long":
                 assert lib.th_token_len(m, nxt, i) == n, (trial, i, n)
+
+
+def test_inline_keys_built_from_staged_words_hold_the_token_bytes_and_length(lib):
+    # a token at any byte position of the staging buffer: the short key (<= 7 bytes) is its bytes
+    # little-endian with the length in the top byte of ONE 64-bit word; the medium key (8..15 bytes)
+    # is bytes 0..7 in k0, bytes 8..14 and the length << 56 in k1 -- never a byte of the neighbours
+    rnd = random.Random(7)
+    for trial in range(4000):
+        buf = bytes(rnd.randrange(1, 256) for _ in range(40))
+        words = (C.c_uint32 * 10)(*[int.from_bytes(buf[4 * i:4 * i + 4], "little") for i in range(10)])
+        pos, n = rnd.randrange(0, 20), rnd.randint(1, 15)
+        tok = buf[pos:pos + n]
+        out = (C.c_uint64 * 2)()
+        lib.th_inline_key(words, pos, n, out)
+        if n <= 7:
+            assert out[0] == int.from_bytes(tok, "little") | n << 56 and out[1] == 0, (pos, n)
+        else:
+            assert out[0] == int.from_bytes(tok[:8], "little"), (pos, n)
+            assert out[1] == int.from_bytes(tok[8:], "little") | n << 56, (pos, n)
