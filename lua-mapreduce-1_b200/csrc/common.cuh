@@ -93,6 +93,14 @@ __host__ __device__ __forceinline__ int ffs64(unsigned long long x) // 1-based i
     return __builtin_ffsll((long long)x);
 #endif
 }
+__host__ __device__ __forceinline__ int ffs32(uint32_t x) // 1-based index of the lowest set bit, 0 if none
+{
+#ifdef __CUDA_ARCH__
+    return __ffs((int)x);
+#else
+    return __builtin_ffs((int)x);
+#endif
+}
 __host__ __device__ __forceinline__ int clz32(uint32_t x)
 {
 #ifdef __CUDA_ARCH__
@@ -250,7 +258,7 @@ __host__ __device__ __forceinline__ uint64_t bswap64(uint64_t v)
     return ((uint64_t)bswap32(lo) << 32) | bswap32(hi);
 }
 
-__device__ inline bool bytes_equal(const uint8_t *base, uint64_t a, uint64_t b, uint32_t len)
+__host__ __device__ inline bool bytes_equal(const uint8_t *base, uint64_t a, uint64_t b, uint32_t len)
 {
     if (a == b) return true;
     for (uint32_t i = 0; i < len; i += 8) {
@@ -260,7 +268,7 @@ __device__ inline bool bytes_equal(const uint8_t *base, uint64_t a, uint64_t b, 
     return true;
 }
 
-__device__ __forceinline__ bool same_key(const Key &a, const Key &b, const uint8_t *bytes)
+__host__ __device__ __forceinline__ bool same_key(const Key &a, const Key &b, const uint8_t *bytes)
 {
     if (a.k1 != b.k1) return false;       // length / hash differ
     if (a.k0 == b.k0) return true;
@@ -375,7 +383,7 @@ __host__ __device__ inline uint32_t partition_of_key(const Key &k, const uint8_t
 // is, a minimum as its bitwise complement (then "min" is a max of complements).
 enum ReduceOp : uint32_t { OP_SUM = 0, OP_MIN = 1, OP_MAX = 2, OP_COUNT = 3 };
 
-__device__ __forceinline__ unsigned long long op_encode(uint32_t op, unsigned long long v)
+__host__ __device__ __forceinline__ unsigned long long op_encode(uint32_t op, unsigned long long v)
 {
     return op == OP_COUNT ? 1ull : (op == OP_MIN ? ~v : v);
 }
@@ -436,7 +444,7 @@ __device__ inline void gtable_add(GEntry *gt, uint32_t gmask, const uint8_t *byt
 
 // Length (up to the next whitespace byte) and hash of the token starting at off.
 // Returns 0 if the token is longer than max_len.
-__device__ inline uint32_t scan_long_token(const uint8_t *bytes, uint64_t off, uint32_t max_len,
+__host__ __device__ inline uint32_t scan_long_token(const uint8_t *bytes, uint64_t off, uint32_t max_len,
                                            uint32_t *hash_out)
 {
     uint64_t h = 0xCBF29CE484222325ull;
@@ -445,8 +453,8 @@ __device__ inline uint32_t scan_long_token(const uint8_t *bytes, uint64_t off, u
         uint64_t w = load8(bytes, off + len);
         uint32_t f0 = space_flags((uint32_t)w), f1 = space_flags((uint32_t)(w >> 32));
         uint32_t nb = 8;
-        if (f0) nb = (uint32_t)(__ffs((int)f0) - 8) >> 3;
-        else if (f1) nb = 4 + ((uint32_t)(__ffs((int)f1) - 8) >> 3);
+        if (f0) nb = (uint32_t)(ffs32(f0) - 8) >> 3;
+        else if (f1) nb = 4 + ((uint32_t)(ffs32(f1) - 8) >> 3);
         if (nb) {
             h = (h ^ (w & low_bytes_mask(nb))) * 0x9E3779B97F4A7C15ull;
             h ^= h >> 32;

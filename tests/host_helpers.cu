@@ -130,4 +130,26 @@ void th_inline_key(const uint32_t *words, uint32_t pos, uint32_t len, unsigned l
     }
 }
 
+// the long-token scanner (tokens of 16+ bytes): length up to the next whitespace byte, 0 if longer
+// than max_len; *hash = the 32-bit hash a long key carries
+uint32_t th_scan_long_token(const uint8_t *bytes, uint64_t off, uint32_t max_len, uint32_t *hash)
+{
+    return scan_long_token(bytes, off, max_len, hash);
+}
+
+// equality of two long keys that live at offsets a and b of one byte space (hash and length equal)
+int th_same_long_key(const uint8_t *space, uint64_t a, uint64_t b, uint32_t la, uint32_t lb, uint32_t ha, uint32_t hb)
+{
+    return same_key(make_long_key(a, la, ha), make_long_key(b, lb, hb), space) ? 1 : 0;
+}
+
+// reducers: the encoded running value (identity 0) and back
+unsigned long long th_op_roundtrip(uint32_t op, unsigned long long a, unsigned long long b)
+{
+    // what the tables do with two values of one key: encode both, merge (sum or max), decode
+    const unsigned long long ea = op_encode(op, a), eb = op_encode(op, b);
+    const unsigned long long m = (op == OP_SUM || op == OP_COUNT) ? ea + eb : (ea > eb ? ea : eb);
+    return op_decode(op, m);
+}
+
 } // extern "C"

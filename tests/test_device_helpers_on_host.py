@@ -54,6 +54,12 @@ def lib():
     L.th_token_len.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
     L.th_inline_key.restype = None
     L.th_inline_key.argtypes = [C.POINTER(C.c_uint32), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+    L.th_scan_long_token.restype = C.c_uint32
+    L.th_scan_long_token.argtypes = [C.c_char_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint32)]
+    L.th_same_long_key.restype = C.c_int
+    L.th_same_long_key.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    L.th_op_roundtrip.restype = C.c_uint64
+    L.th_op_roundtrip.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64]
     return L
 
 
@@ -221,3 +227,34 @@ def test_inline_keys_built_from_staged_words_hold_the_token_bytes_and_length(lib
         else:
             assert out[0] == int.from_bytes(tok[:8], "little"), (pos, n)
             assert out[1] == int.from_bytes(tok[8:], "little") | n << 56, (pos, n)
+
+
+def test_long_token_scanner_and_long_key_equality(lib):
+    rnd = random.Random(8)
+    space = b" \t\n\r\x0b\x0c"
+    for trial in range(1500):
+        n1, n2 = rnd.randint(1, 300), rnd.randint(1, 300)
+        t1 = bytes(rnd.choice([rnd.randrange(0x21, 0x100), 0x00, 0x0E, 0x1F]) for _ in range(n1))
+        t2 = t1 if trial % 3 == 0 else bytes(rnd.choice(t1) for _ in range(n2))
+        pad = rnd.randrange(0, 9)
+        buf = b"x" * pad + t1 + bytes([rnd.choice(space)]) + t2 + bytes([rnd.choice(space)]) + b"tail" + b" " * 32
+        a, b = pad, pad + len(t1) + 1
+        h1, h2 = C.c_uint32(), C.c_uint32()
+        assert lib.th_scan_long_token(buf, a, 1 << 20, C.byref(h1)) == len(t1)       # stops at the first whitespace byte
+        assert lib.th_scan_long_token(buf, b, 1 << 20, C.byref(h2)) == len(t2)
+        assert lib.th_scan_long_token(buf, a, len(t1) - 1, C.byref(C.c_uint32())) == 0 or len(t1) == 0   # too long: refused
+        if t1 == t2:
+            assert h1.value == h2.value                                              # the hash depends on the bytes only
+        same = lib.th_same_long_key(buf, a, b, len(t1), len(t2), h1.value, h2.value)
+        assert same == int(t1 == t2), (trial, t1, t2)
+
+
+def test_reducer_encodings_have_identity_zero_and_merge_correctly(lib):
+    rnd = random.Random(9)
+    SUM, MIN, MAX, COUNT = 0, 1, 2, 3
+    for _ in range(2000):
+        a, b = rnd.getrandbits(rnd.choice([1, 8, 32, 52])), rnd.getrandbits(rnd.choice([1, 8, 32, 52]))
+        assert lib.th_op_roundtrip(SUM, a, b) == a + b
+        assert lib.th_op_roundtrip(MIN, a, b) == min(a, b)
+        assert lib.th_op_roundtrip(MAX, a, b) == max(a, b)
+        assert lib.th_op_roundtrip(COUNT, a, b) == 2
