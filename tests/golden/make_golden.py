@@ -5,7 +5,10 @@
 wordcount_fixture.json  known answers for the reference's own WordCount input (the four
                         Lua files of examples/WordCount/taskfn.lua:8-11), computed by a
                         pure-Python restatement that is independent of oracle/mr_oracle.c.
-                        The input itself is reference source and is not copied here.
+wordcount_fixture/      that input as DATA for the GPU box (which has no reference tree): the four
+                        files' bytes back to back, zlib-compressed, plus their lengths and sha256
+                        (input.bin.z, manifest.json).  It is the one input the reference's own
+                        test.sh runs (test.sh:11-15); it is read as bytes by the tests, never as code.
 torture_rows.json       full expected rows for the torture split of corpus.TORTURE.
 """
 import collections
@@ -80,6 +83,13 @@ def main():
         g[f"R{R}"] = {"keys_per_partition": per, "sha256": digest(r),
                       "first": [[p, k.decode("latin-1"), v] for p, k, v in r[:5]]}
     json.dump(g, open(os.path.join(HERE, "wordcount_fixture.json"), "w"), indent=1)
+    fx = os.path.join(HERE, "wordcount_fixture")
+    os.makedirs(fx, exist_ok=True)
+    import zlib
+    open(os.path.join(fx, "input.bin.z"), "wb").write(zlib.compress(b"".join(splits), 9))
+    json.dump({"files": files, "lengths": [len(s) for s in splits],
+               "sha256": [hashlib.sha256(s).hexdigest() for s in splits]},
+              open(os.path.join(fx, "manifest.json"), "w"), indent=1)
 
     from lua_mapreduce_1_b200 import corpus
     t = {}

@@ -82,7 +82,7 @@ def test_long_token_spanning_many_segments():
 
 
 def test_reference_shaped_fixture(reference_fixture):
-    # config 1: the reference's own input (only where the reference tree is mounted)
+    # config 1: the reference's own input (test.sh:11-15), from the committed data blob
     g = golden("wordcount_fixture.json")
     for R in (15, 10):
         got, info = check(reference_fixture, R)
