@@ -35,3 +35,12 @@ def assert_rows_equal(got, want, what=""):
     bad = np.nonzero(got.count != want.count)[0]
     assert bad.size == 0, f"{what}: {bad.size} counts differ, first at row {bad[0]}: " \
                           f"{got.count[bad[0]]} != {want.count[bad[0]]} key {want.key(int(bad[0]))!r}"
+
+
+def sort_word(key):
+    """(first 7 key bytes big-endian) << 8 | min(len, 8): the sort word of include/mrgpu.h
+    (mr_shuffle_set_owners), restated for the tests."""
+    w = 0
+    for i in range(7):
+        w = (w << 8) | (key[i] if i < len(key) else 0)
+    return (w << 8) | min(len(key), 8)

@@ -1,0 +1,174 @@
+"""The multi-rank data path on a box with ONE GPU: N contexts (ranks) of one process, all on device 0.
+
+The reference's reduce side merges the runs of up to M mappers per partition (job.lua:253-265,
+utils.merge_iterator utils.lua:206-271: equal keys of different runs are concatenated and reduced,
+utils.lua:232-247).  On one rank every key is already distinct when it reaches the sort, so that merge
+of duplicates only happens when records of several ranks meet at their owner.  These tests make that
+happen without a second GPU: every rank maps its own splits, the records cross through each of the
+three transports (peer-to-peer windows; fixed slots and exact-size segments with the all-to-all done
+here by device-to-device copies, standing in for NCCL), and every owner's rows are compared with the
+oracle's rows for the union of the splits -- bit-exact, both ownership rules.
+"""
+import numpy as np
+import pytest
+
+from helpers import sort_word
+from lua_mapreduce_1_b200 import _native, corpus, parallel
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev_u8(ptr, n):
+    import torch
+    return parallel.device_bytes(ptr, n, torch.device("cuda", 0))
+
+
+def exchange_fixed(ctxs, slot):
+    """mr_shuffle_pack_fixed -> (the all-to-all, as copies) -> mr_shuffle_import_fixed"""
+    W = len(ctxs)
+    send = [_dev_u8(c.shuffle_pack_fixed(slot), W * slot) for c in ctxs]
+    recv = [_dev_u8(c.shuffle_recv_buffer(W * slot), W * slot) for c in ctxs]
+    for s in range(W):
+        for d in range(W):
+            recv[d][s * slot:(s + 1) * slot].copy_(send[s][d * slot:(d + 1) * slot])
+    for c in ctxs:
+        c.shuffle_import_fixed(slot)
+
+
+def exchange_exact(ctxs):
+    """mr_shuffle_count -> sizes to the host -> mr_shuffle_pack -> copies -> mr_shuffle_import"""
+    import torch
+    W = len(ctxs)
+    dev = torch.device("cuda", 0)
+    matrix = np.stack([parallel.device_i64(c.shuffle_count(), 2 * W, dev).cpu().numpy() for c in ctxs]).astype(np.int64)
+    plans = [parallel.plan_from_counts(matrix, r) for r in range(W)]
+    send, recv = [], []
+    for r, c in enumerate(ctxs):
+        base, off, nrec = c.shuffle_pack(matrix[r].astype(np.uint64))
+        assert np.array_equal(off.astype(np.int64), plans[r][0])
+        send.append(_dev_u8(base, int(plans[r][0][-1])))
+        recv.append(_dev_u8(c.shuffle_recv_buffer(int(plans[r][1][-1])), int(plans[r][1][-1])))
+    for s in range(W):
+        for d in range(W):
+            so, ro = plans[s][0], plans[d][1]
+            n = int(so[d + 1] - so[d])
+            assert n == int(ro[s + 1] - ro[s])
+            if n:
+                recv[d][int(ro[s]):int(ro[s]) + n].copy_(send[s][int(so[d]):int(so[d]) + n])
+    for r, c in enumerate(ctxs):
+        c.shuffle_import(plans[r][1].astype(np.uint64), plans[r][2].astype(np.uint64))
+    return matrix
+
+
+def expected_rows_of_rank(want, W, r, splitters):
+    """Row indices of the oracle's rows that rank r owns (include/mrgpu.h, mr_shuffle_set_owners)."""
+    keys = want.keys()
+    if not splitters:
+        return [i for i in range(want.n) if int(want.part[i]) % W == r]
+    pw = [(int(want.part[i]), sort_word(keys[i])) for i in range(want.n)]
+    owner = [sum(1 for s in splitters if s <= x) for x in pw]
+    return [i for i in range(want.n) if owner[i] == r]
+
+
+def equal_share_splitters(want, W):
+    keys = want.keys()
+    cuts = [want.n * j // W for j in range(1, W)]
+    return [(int(want.part[i]), sort_word(keys[i])) for i in cuts]
+
+
+def run_ranks(splits_of_rank, R, transport, balanced, jobs=2):
+    import torch
+    W = len(splits_of_rank)
+    union = [s for ss in splits_of_rank for s in ss]
+    want = O.run_naive(union, R)
+    stream = torch.cuda.Stream(device=0)
+    with torch.cuda.stream(stream):
+        # the copy-based transports run every rank on one stream (the copies are torch's); the
+        # peer-to-peer windows need the ranks to progress independently: private streams
+        handle = None if transport == "p2p" else stream.cuda_stream
+        arena = max(sum(len(s) for s in ss) for ss in splits_of_rank) + 64 * len(union) + (1 << 16)
+        ctxs = [_native.Context(R, arena, max_keys=1 << 18, device=0, stream=handle, world_size=W, rank=r)
+                for r in range(W)]
+        try:
+            splitters = equal_share_splitters(want, W) if balanced else []
+            for c in ctxs:
+                c.set_owners(splitters)
+            if transport == "p2p":
+                blobs = [c.p2p_setup(8 << 20) for c in ctxs]
+                for c in ctxs:
+                    c.p2p_attach(blobs)
+            for it in range(jobs):
+                for r, c in enumerate(ctxs):
+                    if it == 0:
+                        for i, s in enumerate(splits_of_rank[r]):
+                            c.map_split(i, s)
+                    else:
+                        c.job_begin(keep_input=True)
+                    c.map_finish()
+                if transport == "p2p":
+                    for c in ctxs:
+                        c.shuffle_p2p()
+                elif transport == "fixed":
+                    exchange_fixed(ctxs, 8 << 20)
+                else:
+                    exchange_exact(ctxs)
+                for c in ctxs:
+                    c.reduce_all()
+                keys = want.keys()
+                seen_rows = seen_tokens = sent = 0
+                for r, c in enumerate(ctxs):
+                    info = c.job_sync()
+                    got = c.rows()
+                    idx = expected_rows_of_rank(want, W, r, splitters)
+                    what = f"{transport} balanced={balanced} job {it} rank {r}"
+                    assert got.keys() == [keys[i] for i in idx], what
+                    assert np.array_equal(got.count, want.count[idx]), what
+                    assert np.array_equal(got.part, want.part[idx]), what
+                    seen_rows += got.n
+                    seen_tokens += int(info.n_tokens)
+                    sent += int(info.map_keys)
+                assert seen_rows == want.n and seen_tokens == want.tokens
+                assert sent >= want.n      # records before the merge: a key arrives once per rank that saw it
+            return want, sent
+        finally:
+            for c in ctxs:
+                c.close()
+
+
+def corpus_shards(W, lines=(900, 700, 1100, 1, 0, 800)):
+    splits, _ = corpus.generate(lines=list(lines) * W)
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
+    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))     # the same split twice: every key of it meets itself
+    return [splits[r::W] for r in range(W)]
+
+
+@pytest.mark.parametrize("transport", ["p2p", "fixed", "exact"])
+@pytest.mark.parametrize("balanced", [False, True])
+def test_two_ranks_on_one_device(transport, balanced):
+    shards = corpus_shards(2)
+    want, sent = run_ranks(shards, 10, transport, balanced)
+    # the point of the exercise: most keys reached their owner from both ranks and were merged there
+    assert sent > 1.5 * want.n, (sent, want.n)
+
+
+@pytest.mark.parametrize("transport", ["p2p", "fixed", "exact"])
+def test_three_ranks_on_one_device_uneven(transport):
+    # R = 7 over 3 ranks, one rank with no split at all, one with a single tiny split
+    splits, _ = corpus.generate(lines=[1500, 1200, 900, 600])
+    shards = [list(splits), [], [b"the of and a\tto in  is that\nlonger-than-fifteen-bytes-token the"]]
+    run_ranks(shards, 7, transport, balanced=False)
+    run_ranks(shards, 7, transport, balanced=True, jobs=1)
+
+
+def test_long_keys_meet_at_their_owner():
+    # keys of 16+ bytes travel as bytes behind the records and are compared byte by byte when merged
+    rnd = np.random.RandomState(3)
+    words = [b"k%02d-" % i + bytes(rnd.choice(list(b"abcdef"), size=rnd.randint(12, 60)).tolist()) for i in range(400)]
+    words += [b"shared-prefix-of-a-long-key/" + b"x" * n for n in range(1, 40)]
+    def text(seed):
+        r = np.random.RandomState(seed)
+        return b" ".join(words[j] for j in r.randint(0, len(words), size=5000))
+    for transport in ("p2p", "fixed", "exact"):
+        want, sent = run_ranks([[text(1)], [text(2)]], 10, transport, balanced=True, jobs=1)
+        assert sent > 1.8 * want.n
