@@ -184,7 +184,16 @@ void mr_result_release(mr_result *res);
  *                         rounded up to 16.  Asynchronous.
  *   3. the caller moves the segments (NCCL all-to-all) into mr_shuffle_recv_buffer and calls
  *      mr_shuffle_import before mr_reduce_all.
- * Pointers in the plan are owned by the context. */
+ * Pointers in the plan are owned by the context.
+ * Stream contract: every call of this seam only QUEUES work on the context's stream (cfg.stream).
+ * The caller's reads of *dev_counts, its transfer out of send_base and into the receive buffer must
+ * be ordered after the preceding call and before the following one ON THAT STREAM: run the
+ * collective on the same stream (create the context on the collective library's stream), or put
+ * events between the two streams.  A context created with stream = NULL owns a private stream the
+ * caller cannot name, so it cannot be used with a caller-run collective (mr_shuffle_nccl and
+ * mr_shuffle_p2p do their own ordering).  mr_shuffle_pack checks on the device that the counts it
+ * was given cover what the count kernel tallied; counts that are too small surface as
+ * MR_ERR_OVERFLOW from mr_job_sync and nothing is written past a segment. */
 typedef struct mr_shuffle_plan {
     const uint8_t *send_base;  /* device buffer holding every outgoing segment */
     const uint64_t *send_off;  /* host array [world_size+1]: byte offsets per destination */

@@ -166,6 +166,7 @@ class Context:
             raise NativeError(rc, (self._L.mr_last_error(None) or b"").decode())
         self._h = h
         self.num_reducers, self.world_size, self.rank = num_reducers, world_size, rank
+        self.stream = stream    # cudaStream_t handle the context runs on; None = a private stream of its own
 
     def _ck(self, rc):
         if rc != MR_OK:

@@ -77,6 +77,7 @@ __global__ void ctl_owner_reset_kernel(Ctl *ctl)
     ctl->n_tie = 0; ctl->tie_overflow = 0; ctl->tie_small = 0; ctl->rows_ticket = 0;
     ctl->n_out = 0; ctl->key_bytes = 0;
     ctl->max_tie_len = 0;
+    for (int i = 0; i < MAX_PASSES; ++i) ctl->tickets[i] = 0;
 }
 
 constexpr uint32_t MAX_WORLD = 1024;
@@ -115,11 +116,25 @@ __global__ void __launch_bounds__(256) export_scatter_kernel(EntryArrays ent, co
                                                              const unsigned long long *seg_off,
                                                              const unsigned long long *nrec_total,
                                                              unsigned long long *rec_cur,
-                                                             unsigned long long *byte_cur, const Ctl *ctl)
+                                                             unsigned long long *byte_cur,
+                                                             const unsigned long long *seg_end, Ctl *ctl)
 {
     __shared__ unsigned int s_rec[MAX_WORLD];
     __shared__ unsigned long long s_bytes[MAX_WORLD], s_rec_base[MAX_WORLD], s_byte_base[MAX_WORLD];
     if (ctl->err & ERR_SHUFFLE_FULL) return; // a segment does not fit its slot: reported by the host
+    if (seg_end) {
+        // exact-size path: the segment bounds came from the HOST's copy of the tallies; if that copy was
+        // stale or wrong (read before the count kernel ran), nothing may be scattered -- every CTA
+        // sees the same numbers and takes the same way out
+        const unsigned long long *nbytes_total = nrec_total + world;
+        bool bad = false;
+        for (uint32_t d = threadIdx.x; d < world; d += blockDim.x)
+            bad |= seg_off[d] + nrec_total[d] * REC_BYTES + nbytes_total[d] > seg_end[d];
+        if (__syncthreads_or(bad)) {
+            if (threadIdx.x == 0) atomicOr(&ctl->err, ERR_SHUFFLE_FULL);
+            return;
+        }
+    }
     const uint64_t n = ctl->n;
     const uint64_t chunk = (n + gridDim.x - 1) / gridDim.x;
     const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
@@ -182,20 +197,20 @@ __global__ void __launch_bounds__(256) import_fixed_kernel(const uint8_t *recv, 
                                                            unsigned long long slot_bytes, EntryArrays ent,
                                                            unsigned long long max_keys, Ctl *ctl)
 {
-    __shared__ unsigned long long s_base, s_n, s_total;
+    __shared__ unsigned long long s_base, s_n, s_total, s_nbytes;
     const uint32_t src = blockIdx.x / IMPORT_CHUNKS, chunk = blockIdx.x % IMPORT_CHUNKS;
     if (threadIdx.x == 0) {
-        unsigned long long base = 0, total = 0, mine = 0;
+        unsigned long long base = 0, total = 0, mine = 0, mine_bytes = 0;
         for (uint32_t q = 0; q < world; ++q) {
             const unsigned long long *hdr = (const unsigned long long *)(recv + (unsigned long long)q * slot_bytes);
             unsigned long long n = hdr[0], b = hdr[1];
             if (16 + n * REC_BYTES + b > slot_bytes) { n = 0; atomicOr(&ctl->err, ERR_SHUFFLE_FULL); }
             if (q < src) base += n;
-            if (q == src) mine = n;
+            if (q == src) { mine = n; mine_bytes = n ? b : 0; }
             total += n;
         }
         if (total > max_keys) { atomicOr(&ctl->err, ERR_KEYS_FULL); total = max_keys; }
-        s_base = base; s_n = mine; s_total = total;
+        s_base = base; s_n = mine; s_total = total; s_nbytes = mine_bytes;
         if (blockIdx.x == 0) ctl->n = total;
     }
     __syncthreads();
@@ -208,7 +223,13 @@ __global__ void __launch_bounds__(256) import_fixed_kernel(const uint8_t *recv, 
     for (unsigned long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
         if (base + i >= s_total) break;
         Key k; k.k0 = rec[3 * i]; k.k1 = rec[3 * i + 1];
-        if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k), (uint32_t)k.k1);
+        if (key_is_long(k)) {
+            // offsets inside a record are the sender's word: they must stay inside its byte block
+            uint64_t off = key_off(k);
+            uint32_t len = key_len(k);
+            if (off + len > s_nbytes) { atomicOr(&ctl->err, ERR_SHUFFLE_FULL); off = 0; len = (uint32_t)min((unsigned long long)len, s_nbytes); }
+            k = make_long_key(bytes_at + off, len, (uint32_t)k.k1);
+        }
         GEntry ge; ge.k0 = k.k0; ge.k1 = k.k1; ge.cnt = rec[3 * i + 2]; ge.pad = 0;
         ent.e[base + i] = ge;
     }
@@ -216,15 +237,20 @@ __global__ void __launch_bounds__(256) import_fixed_kernel(const uint8_t *recv, 
 
 // received segment -> entries; long keys rebased to offsets inside the receive buffer
 __global__ void __launch_bounds__(256) import_segment_kernel(const uint8_t *recv, uint64_t seg_off,
-                                                             uint64_t nrec, uint64_t ent_base,
-                                                             EntryArrays ent)
+                                                             uint64_t nrec, uint64_t nbytes, uint64_t ent_base,
+                                                             EntryArrays ent, Ctl *ctl)
 {
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const unsigned long long *rec = (const unsigned long long *)(recv + seg_off);
     const uint64_t bytes_at = seg_off + nrec * REC_BYTES;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += stride) {
         Key k; k.k0 = rec[3 * i]; k.k1 = rec[3 * i + 1];
-        if (key_is_long(k)) k = make_long_key(bytes_at + key_off(k), key_len(k), (uint32_t)k.k1);
+        if (key_is_long(k)) {
+            uint64_t off = key_off(k);
+            uint32_t len = key_len(k);
+            if (off + len > nbytes) { atomicOr(&ctl->err, ERR_SHUFFLE_FULL); off = 0; len = (uint32_t)min((unsigned long long)len, (unsigned long long)nbytes); }
+            k = make_long_key(bytes_at + off, len, (uint32_t)k.k1);
+        }
         GEntry ge; ge.k0 = k.k0; ge.k1 = k.k1; ge.cnt = rec[3 * i + 2]; ge.pad = 0;
         ent.e[ent_base + i] = ge;
     }
@@ -1014,6 +1040,8 @@ int check_device_err(mr_ctx *ctx, unsigned err)
     if (err & ERR_PEER_TIMEOUT)
         return fail(ctx, MR_ERR_CUDA, "peer-to-peer shuffle: a rank did not deliver its records within %llu s",
                     P2P_TIMEOUT_NS / 1000000000ull);
+    if (err & ERR_LOOKBACK_TIMEOUT)
+        return fail(ctx, MR_ERR_CUDA, "a sort or rows tile waited for its predecessors for seconds without progress (look-back gave up)");
     if (err & ERR_KEYS_FULL)
         return fail(ctx, MR_ERR_NOMEM, "more distinct keys (or key bytes) than max_keys=%llu allows",
                     (unsigned long long)ctx->max_keys);
@@ -1239,7 +1267,7 @@ int mr_shuffle_pack(mr_ctx *ctx, const uint64_t *counts, mr_shuffle_plan *plan)
     CU(cudaMemcpyAsync(seg_off, stage, (W + 1) * 8ull, cudaMemcpyHostToDevice, s));
     const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
     export_scatter_kernel<<<g, 256, 0, s>>>(ctx->ent, ctx->bytes_base, W, ctx->d_send, seg_off, nrec, rec_cur,
-                                            byte_cur, ctx->d_ctl);
+                                            byte_cur, seg_off + 1, ctx->d_ctl);
     ctx->stats.launches++;
     CU(cudaGetLastError());
     plan->send_base = ctx->d_send;
@@ -1270,7 +1298,7 @@ int mr_shuffle_pack_fixed(mr_ctx *ctx, uint64_t slot_bytes, const uint8_t **send
     export_header_kernel<<<(W + 255) / 256, 256, 0, s>>>(ctx->d_send, W, slot_bytes, nrec, nbytes, seg_off, ctx->d_ctl);
     const unsigned g = grid_for(ctx->max_keys, 256, ctx->sm_count * 2);
     export_scatter_kernel<<<g, 256, 0, s>>>(ctx->ent, ctx->bytes_base, W, ctx->d_send, seg_off, nrec, rec_cur,
-                                            byte_cur, ctx->d_ctl);
+                                            byte_cur, nullptr, ctx->d_ctl);
     ctx->stats.launches += 2;
     CU(cudaGetLastError());
     *send_base = ctx->d_send;
@@ -1329,7 +1357,8 @@ int mr_shuffle_import(mr_ctx *ctx, const uint64_t *recv_off, const uint64_t *rec
         if (recv_off[src] + n * REC_BYTES > recv_off[src + 1]) return fail(ctx, MR_ERR_INVALID, "mr_shuffle_import: segment %u too small", src);
         if (base + n > ctx->max_keys) return fail(ctx, MR_ERR_NOMEM, "mr_shuffle_import: more than max_keys records");
         if (n) {
-            import_segment_kernel<<<grid_for(n, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->d_recv, recv_off[src], n, base, ctx->ent);
+            import_segment_kernel<<<grid_for(n, 256, ctx->sm_count * 4), 256, 0, s>>>(
+                ctx->d_recv, recv_off[src], n, recv_off[src + 1] - recv_off[src] - n * REC_BYTES, base, ctx->ent, ctx->d_ctl);
             ctx->stats.launches++;
         }
         base += n;

@@ -178,6 +178,19 @@ __global__ void __launch_bounds__(256) p2p_send_kernel(P2PParams p, GEntry *gt, 
     if (threadIdx.x == 0) *done_ctas = 0; // ready for the next shuffle (stream order protects it)
 }
 
+// 8 bytes at an arbitrary offset with loads that take part in the memory model: the bytes were
+// stored by a peer while this kernel may already have been running, so the read-only (.nc) path of
+// load8 is not allowed for them
+__device__ __forceinline__ uint64_t load8_coherent(const uint8_t *base, uint64_t off)
+{
+    const volatile unsigned long long *p = (const volatile unsigned long long *)(base + (off & ~7ull));
+    const uint32_t sh = (uint32_t)(off & 7) * 8;
+    const uint64_t w0 = p[0];
+    if (sh == 0) return w0;
+    const uint64_t w1 = p[1];
+    return (w0 >> sh) | (w1 << (64 - sh));
+}
+
 // The owner's side: wait for source src (one CTA group per source, so that early arrivals are
 // indexed while late ones are still in flight), then turn its records into sort items in place.
 // Item order is whatever the atomics give; the sort does not care.
@@ -231,7 +244,20 @@ __global__ void __launch_bounds__(256) p2p_index_kernel(const uint8_t *buf, cons
             const ulonglong4 e = ld256_coherent(&rec[first + i]);
             Key k; k.k0 = e.x; k.k1 = e.y;
             const uint32_t part = (uint32_t)e.w;
-            const uint64_t ck = sort_chunk(k, buf, 0);
+            uint64_t ck;
+            if (key_is_long(k)) {
+                // the record names its key bytes by offset: they must lie inside the sender's slot
+                // (a poisoned record is reported, never followed), and are read coherently
+                const uint64_t off = key_off(k), len = key_len(k);
+                if (off < slot_at + P2P_HDR || off + len > slot_at + slot_bytes) {
+                    atomicOr(&ctl->err, ERR_SHUFFLE_FULL);
+                    ck = 8;
+                } else {
+                    ck = (bswap64(load8_coherent(buf, off) & low_bytes_mask(7)) & ~0xFFull) | 8; // = sort_chunk(k, buf, 0)
+                }
+            } else {
+                ck = sort_chunk(k, buf, 0);
+            }
             SortItem it; it.lo = ck; it.hi = part; it.val = (uint32_t)(ent0 + first + i);
             items[base + i] = it;
             hi_or |= part; hi_and &= part; lo_or |= ck; lo_and &= ck;

@@ -353,16 +353,22 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const SortItem *items, 
 
 // tile status word: bits 30..31 = state (0 empty, 1 aggregate, 2 inclusive prefix)
 constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_VAL = (1u << 30) - 1;
+// a look-back that polls this often without progress gives up (about 10 s of L2 round trips): the
+// job then fails with an error instead of hanging the stream
+constexpr uint32_t LOOKBACK_SPIN_LIMIT = 1u << 24;
+constexpr uint32_t ERR_LOOKBACK_TIMEOUT = 32u; // joins the ERR_* bits of common.cuh (16 = ERR_PEER_TIMEOUT)
 
 struct SortBufs {
     SortItem *item[2];
 };
 
 // One LSD pass (stable).  Per tile of 4096 items: digits, warp-local ranks from ballot-built
-// peer masks, per-bin tile counts published for a decoupled look-back (tile id = block index: a
-// tile only ever waits for lower-numbered tiles, and blocks of a grid are dispatched in index
-// order), items reordered by digit in shared memory so that the global scatter writes runs of
-// consecutive 16-byte items instead of one 32-byte sector per item.
+// peer masks, per-bin tile counts published for a decoupled look-back, items reordered by digit in
+// shared memory so that the global scatter writes runs of consecutive 16-byte items instead of one
+// 32-byte sector per item.  The tile id is an atomic ticket (Ctl::tickets[pass]), not the block
+// index: a tile only ever waits for tiles whose CTA has already started, whatever order the
+// hardware dispatches blocks in; the wait itself is bounded (LOOKBACK_SPIN_LIMIT polls, seconds)
+// and ends in ERR_LOOKBACK_TIMEOUT instead of a hang.
 struct __align__(16) SortSmem {
     SortItem sorted[SORT_TILE];                 // 64 KB: the tile in digit order
     unsigned int whist[SORT_WARPS][RADIX_BINS]; // per-warp digit counts -> exclusive offsets
@@ -372,6 +378,7 @@ struct __align__(16) SortSmem {
     unsigned char dig[SORT_TILE];               // digit of sorted[i]
     DigitRun runs[8];
     unsigned int nruns;
+    unsigned int tile;                          // this CTA's ticket
 };
 
 #ifdef MRGPU_SORT_TIMING
@@ -389,7 +396,9 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
     STAMP(0);
     if (pass >= ctl->npasses) return;
     const uint64_t n = ctl->n;
-    const uint32_t tile = blockIdx.x;
+    if (threadIdx.x == 0) sm.tile = atomicAdd(&ctl->tickets[pass], 1u);
+    __syncthreads();
+    const uint32_t tile = sm.tile;
     if ((uint64_t)tile * SORT_TILE >= n) return;
     const SortItem *src = bufs.item[pass & 1];
     SortItem *dst = bufs.item[(pass & 1) ^ 1];
@@ -463,7 +472,9 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_pass_kernel(SortBufs bufs,
             // prefix crosses the (co-resident) tiles in tiles / LOOKBACK serial L2 round trips
             int t = (int)tile - 1;
             bool done = false;
+            uint32_t polls = 0;
             while (!done) {
+                if (++polls > LOOKBACK_SPIN_LIMIT) { atomicOr(&ctl->err, ERR_LOOKBACK_TIMEOUT); break; }
                 uint32_t sv[LOOKBACK];
 #pragma unroll
                 for (int k = 0; k < LOOKBACK; ++k) sv[k] = t - k >= 0 ? st[(uint64_t)(t - k) * RADIX_BINS + b] : (2u << 30);
@@ -780,7 +791,11 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
     __shared__ unsigned int wh[ROWS_THREADS / 32];
     __shared__ unsigned long long wb[ROWS_THREADS / 32];
     __shared__ unsigned long long s_prefix_h, s_prefix_b;
-    const uint32_t tile = blockIdx.x; // tiles wait only for lower-numbered ones (in-order block dispatch)
+    __shared__ unsigned int s_tile;
+    // tile id = atomic ticket: a tile waits only for tiles whose CTA has already started
+    if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->rows_ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
     const uint64_t n = ctl->n;
     if (n == 0) {
         if (tile == 0) {
@@ -846,7 +861,8 @@ __global__ void __launch_bounds__(ROWS_THREADS) rows_kernel(SortBufs bufs, Entry
         } else {
             if (lane == 0) { vagg[tile] = tb; __threadfence(); vheads[tile] = F_AGG | th; }
             int t = (int)tile - 1;
-            for (;;) {
+            for (uint32_t polls = 0;; ++polls) {
+                if (polls > LOOKBACK_SPIN_LIMIT) { if (lane == 0) atomicOr(&ctl->err, ERR_LOOKBACK_TIMEOUT); break; }
                 const int idx = t - (int)lane;
                 unsigned long long w = idx >= 0 ? vheads[idx] : F_INC;
                 const uint32_t flag = (uint32_t)(w >> 62);

@@ -300,6 +300,18 @@ class worker:
         # server swaps all of them, so this run keeps the ones it started with
         with b.lock:
             task, map_jobs, red_jobs, results = b.task, b.map_jobs, b.red_jobs, b.results
+            # ONE worker per board runs the data plane of a task.  The reference's N workers meet
+            # through run files in shared storage (job.lua:208-221, 253-260); a worker here keeps
+            # its combined records in its own GPU context, and nothing moves them between the
+            # contexts of two workers of one board -- each would reduce and publish only what it
+            # mapped itself.  So a second worker is refused, loudly, before it touches a job.
+            # (N GPUs: N ranks of ONE worker group with a shuffle, parallel.py / mr_shuffle_*.)
+            owner = task.setdefault("data_worker", self.name)
+            if owner != self.name:
+                raise RuntimeError(
+                    f"{self.name}: worker {owner} already runs this task's data plane; a board takes one "
+                    "worker (several workers would each reduce only their own splits). Use one worker "
+                    "per board, or ranks of one shuffle group for several GPUs")
         params = task["params"]
         mods = params["mods"]
         desc = self._native_config(mods)

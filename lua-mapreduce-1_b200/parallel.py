@@ -95,6 +95,17 @@ def shuffle(ctx, group=None, slot_bytes=None, stats=None):
         synchronisation at all; a segment larger than N surfaces as MR_ERR_OVERFLOW at job_sync."""
     dev = torch.device("cuda", torch.cuda.current_device())
     W, rank = ctx.world_size, ctx.rank
+    # Stream contract (include/mrgpu.h, shuffle seam): count / pack / import are asynchronous on the
+    # context's stream, and the collectives below are ordered against torch's current stream only --
+    # so the two must be the same stream, or the all-gather could read the tallies before the count
+    # kernel wrote them and the all-to-all could move a send buffer that is not packed yet.
+    cur = torch.cuda.current_stream(dev).cuda_stream
+    if getattr(ctx, "stream", cur) != cur:
+        raise _native.NativeError(_native.MR_ERR_INVALID,
+                                  "parallel.shuffle: the context must run on torch's current stream "
+                                  "(create it with stream=torch.cuda.current_stream().cuda_stream on a "
+                                  "non-default stream); a context with a private stream is not ordered "
+                                  "against the collectives")
     if slot_bytes:
         total = W * int(slot_bytes)
         send = device_bytes(ctx.shuffle_pack_fixed(int(slot_bytes)), total, dev)

@@ -18,12 +18,13 @@ class StandInContext:
     """What mapreduce.worker calls on a context, answered by the oracle."""
     created = 0
     fail_next_splits = 0            # class-wide: that many map_split calls raise (a BROKEN job each)
+    default_delay = 0.0             # class-wide: seconds every reduce_all takes
 
     def __init__(self, num_reducers, arena_bytes, max_keys=0, **kw):
         type(self).created += 1
         self.num_reducers = num_reducers
         self.splits, self.rows_, self.h2d = [], None, 0
-        self.delay = 0.0
+        self.delay = type(self).default_delay
 
     def job_begin(self, keep_input=False):
         if not keep_input:
@@ -75,6 +76,7 @@ class StandInContext:
 def stand_in(monkeypatch):
     StandInContext.created = 0
     StandInContext.fail_next_splits = 0
+    StandInContext.default_delay = 0.0
     monkeypatch.setattr(mapreduce._native, "Context", StandInContext)
     return StandInContext
 
@@ -163,3 +165,36 @@ def test_a_broken_map_job_is_retried_and_a_hopeless_one_fails_the_task(tmp_path,
     t.start()
     with pytest.raises(RuntimeError, match="job failed"):
         s2.loop()
+
+
+def test_a_second_worker_on_the_board_is_refused_and_the_result_is_whole(tmp_path, stand_in):
+    # the reference runs N workers per database (worker.lua, task.lua:258-343); here a worker keeps its
+    # combined records in its own GPU context, so two workers would each publish partial partitions.
+    # The second one must fail loudly before it claims a job, and the first one's result must be complete.
+    texts = [b"a b a\n", b"b c\n", b"c d a\n", b"e\n"] * 6
+    want = O.run_naive(texts, 15)
+    runs = []
+    stand_in.default_delay = 0.3           # the first worker is still inside the task when the second arrives
+    s = mapreduce.server.new("localhost", "cpu-two-workers")
+    s.configure({"taskfn": WordCount, "mapfn": WordCount, "partitionfn": WordCount, "reducefn": WordCount,
+                 "combinerfn": WordCount, "finalfn": final_collect(runs),
+                 "init_args": {"files": write_splits(tmp_path, texts), "num_reducers": 15}})
+    workers = [mapreduce.worker.new("localhost", "cpu-two-workers").configure({"max_iter": 2000, "max_tasks": 1})
+               for _ in range(2)]
+    errors = []
+
+    def go(w):
+        try:
+            w.execute()
+        except Exception as e:
+            errors.append(e)
+    threads = [threading.Thread(target=go, args=(w,), daemon=True) for w in workers]
+    for t in threads:
+        t.start()
+    s.loop()
+    for t in threads:
+        t.join(30)
+        assert not t.is_alive()
+    assert runs == [list(zip(want.keys(), (int(c) for c in want.count)))]       # whole, not one worker's share
+    assert len(errors) == 1 and "already runs this task's data plane" in str(errors[0])
+    assert stand_in.created == 1                                                 # the refused worker never made a context
