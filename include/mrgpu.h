@@ -303,7 +303,12 @@ uint32_t mr_partition_of(const void *key, uint64_t klen, uint32_t num_reducers);
  * order; *n_tokens (host, may be NULL) receives the token count.  The call clears the shared
  * array, runs on `stream` and returns after synchronising it.  All calls on a device share
  * the array: calls whose GPU work could overlap must be serialised by the caller.  The first
- * call on each device looks up the array's address; make it before any stream capture. */
+ * call on each device looks up the array's address; make it before any stream capture.  That
+ * first call is also when the CUDA runtime may load this library's device code onto the GPU,
+ * fixed array included (lazy module loading): a host that is about to hand the rest of device
+ * memory to its pool makes one call (n_bytes = 0 is enough) before it does so.
+ * When out_capacity is too small the call fails with MR_ERR_NOMEM, dev_out holds out_capacity
+ * valid records and *dev_n_out the number of distinct tokens found -- the capacity a retry needs. */
 #define MR_STATIC_MAX_BYTES (128u * 1024u)
 typedef struct mr_token_count {
     uint8_t key[15];   /* token bytes, zero padded */

@@ -5,8 +5,12 @@ device-wide synchronisation of cudaMalloc/cudaFree is not acceptable; for them t
 call that allocates nothing (the caller owns input and output, the hash table is a fixed array inside
 the library).  This test drives it through the C ABI, twice in a row on different inputs -- the second
 call finds the first call's table in the shared array and must clear it -- and checks every (token,
-count) pair against the context-based entry points, exactly.  Collected last on purpose.
+count) pair against the context-based entry points, exactly, and against a count made on the host
+(bytes.split() on the six whitespace bytes of mapfn.lua:5, and the CPU oracle), so that a fault shared
+by the two CUDA paths cannot hide.  Collected last on purpose.
 """
+import collections
+
 import numpy as np
 import pytest
 
@@ -47,11 +51,16 @@ def test_static_entry_point_matches_context_api_twice_in_a_row():
     second = (b"  two\tcalls share one table \n" * 50 + corpus.generate_split(8, 400)[0].tobytes()
               + b" caf\xc3\xa9 a\x00b fifteen-bytes-x x end-no-newline")
     assert len(first) <= _native.STATIC_MAX_BYTES and len(second) <= _native.STATIC_MAX_BYTES
+    from oracle import oracle as O
     for text in (first, second):
         want, want_tokens = reference_counts(text)
         got, got_tokens = static_counts(text)
         assert got_tokens == want_tokens
         assert got == want
+        host = collections.Counter(text.split())          # bytes.split(): runs of the same six whitespace bytes
+        assert got == sorted(host.items()) and got_tokens == sum(host.values())
+        naive = O.run_naive([text], 10)
+        assert got == sorted(zip(naive.keys(), (int(c) for c in naive.count))) and got_tokens == naive.tokens
 
 
 def test_static_entry_point_rejects_what_it_cannot_hold():
@@ -68,4 +77,10 @@ def test_static_entry_point_rejects_what_it_cannot_hold():
     with pytest.raises(_native.NativeError) as e:                  # three distinct tokens, room for two
         static_counts(b"a b c a", capacity=2)
     assert e.value.code == _native.MR_ERR_NOMEM
+    t = torch.from_numpy(np.frombuffer(b"a b c a", dtype=np.uint8).copy()).cuda()
+    out2 = torch.zeros(2 * 24, dtype=torch.uint8, device="cuda")
+    n2 = torch.zeros(1, dtype=torch.int64, device="cuda")
+    with pytest.raises(_native.NativeError):
+        _native.count_tokens_static(t.data_ptr(), t.numel(), out2.data_ptr(), 2, n2.data_ptr())
+    assert int(n2.item()) == 3                                     # the capacity a retry needs
     assert static_counts(b"a b c a", capacity=3)[0] == [(b"a", 2), (b"b", 1), (b"c", 1)]   # and it recovers
