@@ -46,21 +46,24 @@ def same(got, want):
                 and np.array_equal(got.key_off, want.key_off) and np.array_equal(got.key_bytes, want.key_bytes))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5])
-    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the full size")
-    a = ap.parse_args()
-    out = {"config": a.config}
+CONFIG4_SPLITS = 394     # bigrams of 2 x the config-2 corpus: ~94 M pairs, ~5 x 10^7 distinct keys (BASELINE configs[3])
+
+
+def run(config, scale=1.0):
+    """One config at `scale` of its full size on cuda:0; returns the dict main() prints."""
+    a = argparse.Namespace(config=config, scale=scale)
+    out = {"config": a.config, "scale": scale}
     if a.config in (3, 4):
-        nsplit = max(1, int((1970 if a.config == 3 else 197) * a.scale))
-        lines = corpus.split_lines(10 if a.config == 3 else 1)[:nsplit]
+        nsplit = max(1, int((1970 if a.config == 3 else CONFIG4_SPLITS) * a.scale))
+        lines = corpus.split_lines(10)[:nsplit]
         splits, tokens = corpus.generate(lines=lines)
         total = sum(len(s) for s in splits)
         bigram = a.config == 4
         mk = (1 << 26) if bigram else (1 << 20)
+        if bigram and nsplit <= 40:
+            mk = 1 << 23
         ctx = _native.Context(10, total + 64 * len(splits) + (1 << 20), max_keys=mk,
-                              table_slots=(1 << 27) if bigram else (1 << 21),
+                              table_slots=2 * mk,
                               map_kind=_native.MR_MAP_BIGRAM_WS if bigram else _native.MR_MAP_TOKENIZE_WS)
 
         def stage():
@@ -98,6 +101,15 @@ def main():
     out.update(bit_exact=same(got, want), first_job_s=first, resident_job_ms=best * 1e3,
                units_per_s_resident=int(info.n_tokens) / best, sum_ok=bool(int(got.count.sum()) == int(want.count.sum())))
     ctx.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5])
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the full size")
+    a = ap.parse_args()
+    out = run(a.config, a.scale)
     print(json.dumps(out))
     if not out["bit_exact"]:
         sys.exit(1)
