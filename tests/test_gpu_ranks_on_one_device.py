@@ -136,11 +136,14 @@ def run_ranks(splits_of_rank, R, transport, balanced, jobs=2):
                 c.close()
 
 
-def corpus_shards(W, lines=(900, 700, 1100, 1, 0, 800)):
-    splits, _ = corpus.generate(lines=list(lines) * W)
-    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))
-    splits.append(np.frombuffer(corpus.TORTURE, dtype=np.uint8))     # the same split twice: every key of it meets itself
-    return [splits[r::W] for r in range(W)]
+def corpus_shards(W):
+    """Every rank maps the same three splits (so every key of them reaches its owner once per rank and
+    has to be merged there) plus a smaller split of its own and, on the last rank, the torture split twice."""
+    common, _ = corpus.generate(lines=[900, 1100, 1, 0, 700])
+    own, _ = corpus.generate(lines=[150] * W, first_split=50)
+    shards = [list(common) + [own[r]] for r in range(W)]
+    shards[-1] += [np.frombuffer(corpus.TORTURE, dtype=np.uint8)] * 2
+    return shards
 
 
 @pytest.mark.parametrize("transport", ["p2p", "fixed", "exact"])
