@@ -246,7 +246,10 @@ int mr_shuffle_nccl(mr_ctx *ctx, uint64_t slot_bytes, uint64_t *slot_used);
  *                  mr_job_sync on the sender and the owner (set the windows up again with larger
  *                  slots); a rank that never delivers surfaces as MR_ERR_CUDA after 20 s.
  * Fails with MR_ERR_UNSUPPORTED where the devices cannot map each other's memory; mr_shuffle_nccl
- * is the transport for that case. */
+ * is the transport for that case.  One rank per GPU is assumed: the owner's kernel waits on the GPU
+ * for its peers' records, so ranks that share one GPU (tests do) must all have finished their map side
+ * (device idle) before the first of them calls mr_shuffle_p2p, or the waiting kernel can keep a peer's
+ * map kernel from ever starting (reported after 20 s, not a hang). */
 typedef struct mr_peer_info {
     uint64_t pid;           /* process that owns the window */
     uint64_t dev_ptr;       /* its address there (used by contexts of the same process) */

@@ -371,6 +371,8 @@ def test_p2p_shuffle_two_contexts_in_one_process():
                 else:
                     c.job_begin(keep_input=True)
                 c.map_finish()
+            if not two:
+                torch.cuda.synchronize()             # ranks sharing one GPU: maps done before anybody waits in a kernel
             for c in ctxs:
                 c.shuffle_p2p()                      # asynchronous: neither call waits for the other rank
             for c in ctxs:

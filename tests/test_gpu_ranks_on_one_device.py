@@ -107,6 +107,12 @@ def run_ranks(splits_of_rank, R, transport, balanced, jobs=2):
                         c.job_begin(keep_input=True)
                     c.map_finish()
                 if transport == "p2p":
+                    # Ranks that SHARE a GPU (this test only): a rank's index kernel waits inside the
+                    # kernel for its peers' records, and a peer's map kernel (one 1024-thread CTA per SM
+                    # holding most of the register file) cannot start on an SM where such a waiting CTA
+                    # already sits.  So every rank's map side is finished before the first shuffle call.
+                    # With one rank per GPU -- the deployment -- the ranks never compete for an SM.
+                    torch.cuda.synchronize()
                     for c in ctxs:
                         c.shuffle_p2p()
                 elif transport == "fixed":
