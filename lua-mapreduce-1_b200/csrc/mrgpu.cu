@@ -21,6 +21,7 @@
 #include "bigram_kernel.cuh"
 #include "records_kernel.cuh"
 #include "reduce_kernels.cuh"
+#include "msd_kernels.cuh"
 #include "p2p_kernels.cuh"
 
 using namespace mr;
@@ -306,6 +307,10 @@ struct mr_ctx {
     uint64_t key_bytes_cap = 0;
     Ctl *d_ctl = nullptr;
     Ctl *h_ctl = nullptr; // pinned
+    MsdBins *d_msd = nullptr; // [2], alternating by job (msd_kernels.cuh)
+    uint32_t msd_parity = 0;
+    bool prefer_lsd = false;  // the MSD path declined a job of this context: later jobs take the LSD path at once
+    bool used_msd = false;    // this job's reduce side was launched on the MSD path
     unsigned long long *h_stage = nullptr; // pinned, [MAX_WORLD + 1]
     const uint8_t *bytes_base = nullptr;
 
@@ -467,6 +472,7 @@ void mr_ctx_destroy(mr_ctx *ctx)
     cudaFree(ctx->rows.part); cudaFree(ctx->rows.count); cudaFree(ctx->rows.key_off);
     cudaFree(ctx->rows.key_bytes);
     cudaFree(ctx->rows.part_begin);
+    cudaFree(ctx->d_msd);
     cudaFree(ctx->d_ctl); cudaFree(ctx->d_send); cudaFree(ctx->d_recv); cudaFree(ctx->d_shuf);
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -561,7 +567,7 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->d_status, (uint64_t)MAX_PASSES * ctx->max_tiles * RADIX_BINS));
     uint64_t tie_cap = 1; while (tie_cap < mk) tie_cap <<= 1;
     CUC(dmalloc(&ctx->d_ties, tie_cap)); CUC(dmalloc(&ctx->d_posv, tie_cap));
-    ctx->rows_tiles = (uint32_t)((mk + ROWS_TILE - 1) / ROWS_TILE) + 1;
+    ctx->rows_tiles = (uint32_t)((mk + UNIT_W - 1) / UNIT_W) + 2; // look-back words: one per rows tile or per MSD unit
     CUC(dmalloc(&ctx->rows_st.heads, 3ull * ctx->rows_tiles));
     ctx->rows_st.bytes_agg = ctx->rows_st.heads + ctx->rows_tiles;
     ctx->rows_st.bytes_inc = ctx->rows_st.heads + 2ull * ctx->rows_tiles;
@@ -569,6 +575,9 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->rows.key_off, mk + 1)); CUC(dmalloc(&ctx->rows.key_bytes, ctx->key_bytes_cap));
     CUC(dmalloc(&ctx->rows.part_begin, (uint64_t)cfg->num_reducers + 1));
     CUC(dmalloc(&ctx->d_ctl, 1));
+    CUC(dmalloc(&ctx->d_msd, 2));
+    CUC(cudaMemset(ctx->d_msd, 0, 2 * sizeof(MsdBins)));
+    if (const char *v = getenv("MRGPU_REDUCE")) ctx->prefer_lsd = strcmp(v, "lsd") == 0;
     CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
     CUC(cudaMallocHost((void **)&ctx->h_stage, (MAX_WORLD + 1) * 8));
     CUC(cudaMallocHost((void **)&ctx->h_gaps, (MAX_GAPS + 1) * sizeof(Gap)));
@@ -626,6 +635,7 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
     ctx->state = mr_ctx::IDLE;
     ctx->rows_cached = false;
     ctx->tie_rounds = 0;
+    ctx->used_msd = false;
     ctx->map_timed = ctx->red_timed = false;
     ctx->stats = mr_stats{};
     ctx->stats.launches = 1;
@@ -969,6 +979,35 @@ int launch_sort(mr_ctx *ctx)
     return MR_OK;
 }
 
+// The reduce side in three launches (msd_kernels.cuh): histogram of the most significant digit,
+// scatter into bins, then sort + merge + rows per unit of bins in shared memory.
+int launch_msd(mr_ctx *ctx)
+{
+    cudaStream_t s = ctx->stream;
+    static_assert(sizeof(UnitSmem) <= 113 * 1024, "two units per SM");
+    CU(cudaFuncSetAttribute(msd_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MSD_MAX_BINS * 4)));
+    CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
+    CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
+    MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
+    ctx->msd_parity ^= 1;
+    msd_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 2), 256, MSD_MAX_BINS * 4, s>>>(
+        ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, mb, other, ctx->rows_st, ctx->rows_tiles);
+    msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
+        ctx->bufs.item[0], (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb);
+    const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
+    msd_unit_kernel<<<units, UNIT_THREADS, sizeof(UnitSmem), s>>>(
+        (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
+        ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb);
+    ctx->stats.launches += 3;
+    if (ctx->cfg.reduce_kind == MR_REDUCE_MIN_U64) {
+        rows_decode_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->rows, ctx->cfg.reduce_kind, ctx->d_ctl);
+        ctx->stats.launches += 1;
+    }
+    CU(cudaGetLastError());
+    ctx->used_msd = true;
+    return MR_OK;
+}
+
 // zeroed: tie_mark_kernel has just cleared what the rows kernel needs cleared (the first pass of a
 // job); the second pass after a re-sort clears it here
 int launch_rows(mr_ctx *ctx, bool zeroed)
@@ -1064,8 +1103,12 @@ int mr_reduce_all(mr_ctx *ctx)
     CU(cudaEventRecord(ctx->ev_red0, ctx->stream));
     int rc;
     if (!ctx->imported) { if ((rc = launch_compact(ctx))) return rc; }
-    if ((rc = launch_sort(ctx))) return rc;
-    if ((rc = launch_rows(ctx, true))) return rc;
+    if (!ctx->prefer_lsd) {
+        if ((rc = launch_msd(ctx))) return rc;
+    } else {
+        if ((rc = launch_sort(ctx))) return rc;
+        if ((rc = launch_rows(ctx, true))) return rc;
+    }
     CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
     ctx->red_timed = true;
     ctx->state = mr_ctx::REDUCED;
@@ -1082,6 +1125,19 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
         CU(cudaStreamSynchronize(ctx->stream));
         int rc = check_device_err(ctx, ctx->h_ctl->err);
         if (rc) return rc;
+        if (ctx->used_msd && ctx->h_ctl->msd_fallback) {
+            // the MSD path declined (msd_kernels.cuh, "fallback"): the whole reduce side again on the LSD
+            // path, from the untouched sort items; later jobs of this context start there
+            ctx->prefer_lsd = true;
+            ctx->used_msd = false;
+            CU(cudaMemsetAsync(&ctx->d_ctl->n_tie, 0, offsetof(Ctl, n_out) - offsetof(Ctl, n_tie), ctx->stream));
+            if ((rc = launch_sort(ctx))) return rc;
+            if ((rc = launch_rows(ctx, true))) return rc;
+            CU(cudaEventRecord(ctx->ev_red1, ctx->stream));
+            CU(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            if ((rc = check_device_err(ctx, ctx->h_ctl->err))) return rc;
+        }
         if (ctx->h_ctl->tie_overflow) {
             // rare: many keys agree in their first 7 bytes; order them, then redo the rows
             // keys sharing long prefixes.  Up to 64K of them: pairwise compares of whole keys in a

@@ -1,0 +1,572 @@
+// msd_kernels.cuh -- the reduce side for jobs of up to a few million distinct keys, built for latency:
+// three launches after the table read-out instead of eleven.
+//
+// Replaces utils.keys_sorted (utils.lua:123-128), utils.merge_iterator + heap.lua (utils.lua:206-271),
+// merge_min_keys (utils.lua:232-247), the reduce loop job.lua:264-284 and the result write
+// job.lua:272-287 -- the same reference code the LSD path of reduce_kernels.cuh replaces; that path
+// stays for what this one declines (see "fallback").
+//
+//   msd_hist_kernel     the varying bits of the 96-bit sort word (partition, 7 key bytes, min(len, 8))
+//                       are packed; their top D bits (D <= 14, chosen so that a bin holds ~64 items)
+//                       are the most-significant digit: one histogram over all items.
+//   msd_scatter_kernel  bin starts (every CTA scans the histogram for itself), then every item goes to
+//                       its bin as {packed low bits, entry index, bin}: items of one bin lie together,
+//                       bins in key order.
+//   msd_unit_kernel     units of consecutive whole bins (about 1024 items, never more than 2048) are
+//                       sorted in SHARED memory (stable LSD passes on the packed low bits and the bin
+//                       number), keys that agree in their first 7 bytes are ordered by their later
+//                       bytes, equal keys (the same key from several ranks) are merged, and the rows --
+//                       partition, count, key offsets, packed key bytes, partition starts -- are
+//                       written straight from the unit, numbered by a decoupled look-back over units.
+//
+// Fallback: the path declines (Ctl::msd_fallback, nothing written that the LSD path would not
+// overwrite) when the packed low bits exceed 64, the varying bits form more than 32 runs, a bin holds
+// more than UNIT_CAP - UNIT_W items (many more keys than 2^14 bins can spread), or a group of keys
+// equal in their first 7 bytes has more than TIE_SMALL_GROUP members.  mr_job_sync then runs the LSD
+// path; a context that declined once goes straight to the LSD path afterwards.
+#pragma once
+#include "reduce_kernels.cuh"
+
+namespace mr {
+
+constexpr int MSD_MAX_BITS = 14;
+constexpr uint32_t MSD_MAX_BINS = 1u << MSD_MAX_BITS;
+constexpr uint32_t MSD_TARGET_BIN = 64;      // items per bin aimed at
+constexpr uint32_t UNIT_W = 1024;            // a unit owns the bins that start inside its 1024 positions
+constexpr uint32_t UNIT_CAP = 2048;          // ... so it holds fewer than UNIT_W + largest bin items
+constexpr int UNIT_THREADS = 512;
+constexpr int UNIT_WARPS = UNIT_THREADS / 32;
+constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS; // 4
+constexpr uint32_t UNIT_STAGE = UNIT_CAP * INLINE_MAX;
+
+enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_RUNS = 2u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
+
+// histogram, scatter cursors and bin starts; two of these alternate by job so that each job finds
+// its own zeroed (the histogram kernel of a job clears the other one)
+struct MsdBins {
+    unsigned int hist[MSD_MAX_BINS];
+    unsigned int cursor[MSD_MAX_BINS];
+    unsigned int bin_start[MSD_MAX_BINS + 1];
+    unsigned int unit_ticket;
+    unsigned int pad[2];
+};
+static_assert(sizeof(MsdBins) % 16 == 0, "MsdBins is cleared 16 bytes at a time");
+
+// what the scatter leaves in a bin
+struct __align__(16) MsdItem {
+    unsigned long long low;  // packed varying bits below the digit
+    uint32_t val;            // entry index
+    uint32_t bin;            // digit | MSD_FLAG8 when the key has 8 or more bytes (its order may need later bytes)
+};
+constexpr uint32_t MSD_FLAG8 = 1u << 31;
+static_assert(sizeof(MsdItem) == sizeof(SortItem), "the scattered items reuse the second sort buffer");
+
+__host__ __device__ __forceinline__ uint32_t popc64_hd(unsigned long long x)
+{
+#ifdef __CUDA_ARCH__
+    return (uint32_t)__popcll(x);
+#else
+    return (uint32_t)__builtin_popcountll(x);
+#endif
+}
+
+// The plan: packed position j of the j-th varying bit (least significant first: lo bit 0 upwards, then
+// hi), the top D packed bits are the digit.  Runs never straddle the lo/hi boundary nor the
+// low/digit boundary.
+__host__ __device__ inline void msd_build_plan(unsigned long long vlo, uint32_t vhi, unsigned long long n, MsdPlan *p)
+{
+    const uint32_t V = popc64_hd(vlo) + popc64_hd(vhi);
+    uint32_t D = 0;
+    while (D < (uint32_t)MSD_MAX_BITS && ((unsigned long long)MSD_TARGET_BIN << D) < n) ++D;
+    if (D > V) D = V;
+    const uint32_t low_bits = V - D;
+    p->D = D;
+    p->low_bits = low_bits;
+    p->fallback = low_bits > 64 ? MSD_FB_WIDE : 0;
+    uint32_t packed = 0, nr = 0;
+    for (int half = 0; half < 2 && !p->fallback; ++half) {
+        unsigned long long v = half ? (unsigned long long)vhi : vlo;
+        const uint32_t base = half ? 64 : 0;
+        while (v) {
+            const uint32_t start = (uint32_t)ffs64(v) - 1;
+            const unsigned long long ones = ~(v >> start);
+            uint32_t w = ones ? (uint32_t)ffs64(ones) - 1 : 64 - start;
+            if (packed < low_bits && packed + w > low_bits) w = low_bits - packed;
+            if (nr == (uint32_t)MSD_MAX_RUNS) { p->fallback |= MSD_FB_RUNS; break; }
+            MsdRun r;
+            r.shift = (uint8_t)(base + start);
+            r.width = (uint8_t)w;
+            r.to_digit = packed >= low_bits;
+            r.dst = (uint8_t)(r.to_digit ? packed - low_bits : packed);
+            p->runs[nr++] = r;
+            packed += w;
+            v &= ~((w >= 64 ? ~0ull : ((1ull << w) - 1)) << start);
+        }
+    }
+    p->nruns = nr;
+}
+
+__host__ __device__ __forceinline__ void msd_extract(const MsdRun *runs, uint32_t nruns, uint32_t hi, unsigned long long lo,
+                                                     uint32_t &digit, unsigned long long &low)
+{
+    digit = 0;
+    low = 0;
+    for (uint32_t i = 0; i < nruns; ++i) {
+        const MsdRun r = runs[i];
+        const unsigned long long src = r.shift < 64 ? lo >> r.shift : (unsigned long long)(hi >> (r.shift - 64));
+        const unsigned long long f = src & (r.width >= 64 ? ~0ull : ((1ull << r.width) - 1));
+        if (r.to_digit) digit |= (uint32_t)f << r.dst;
+        else low |= f << r.dst;
+    }
+}
+
+// 8-bit digit `pass` of the virtual number (local bin : low), least significant first
+__host__ __device__ __forceinline__ uint32_t msd_pass_digit(unsigned long long low, uint32_t lbin, uint32_t low_bits, uint32_t pass)
+{
+    const uint32_t b0 = pass * 8;
+    unsigned long long v;
+    if (b0 >= low_bits) v = (unsigned long long)lbin >> (b0 - low_bits);
+    else {
+        v = low >> b0;                                   // b0 < low_bits <= 64
+        if (b0 + 8 > low_bits) v |= (unsigned long long)lbin << (low_bits - b0);
+    }
+    return (uint32_t)v & 0xFFu;
+}
+
+// ------------------------------------------------------------------ histogram
+__global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, unsigned long long max_keys, Ctl *ctl,
+                                                       MsdBins *mb, MsdBins *mb_next, RowsStatus st, uint32_t st_words)
+{
+    extern __shared__ unsigned int msd_h[];        // [1 << D] (at most MSD_MAX_BINS)
+    __shared__ MsdPlan plan;
+    unsigned long long n = ctl->n;
+    const bool over = n > max_keys;
+    if (over) n = max_keys;
+    // the other job's bins, and the look-back words of the units to come
+    {
+        const uint64_t g0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, gs = (uint64_t)gridDim.x * blockDim.x;
+        uint4 *z = (uint4 *)mb_next;
+        for (uint64_t i = g0; i < sizeof(MsdBins) / 16; i += gs) z[i] = make_uint4(0, 0, 0, 0);
+        const uint64_t units = (n + UNIT_W - 1) / UNIT_W + 1;
+        for (uint64_t i = g0; i < units && i < st_words; i += gs) { st.heads[i] = 0; st.bytes_agg[i] = 0; st.bytes_inc[i] = 0; }
+    }
+    if (threadIdx.x == 0) {
+        unsigned long long vlo = ctl->or_lo ^ ctl->and_lo;
+        uint32_t vhi = ctl->or_hi ^ ctl->and_hi;
+        if (n < 2) { vlo = 0; vhi = 0; }
+        msd_build_plan(vlo, vhi, n, &plan);
+    }
+    __syncthreads();
+    if (blockIdx.x == 0) {
+        uint32_t *dst = (uint32_t *)&ctl->msd_plan;
+        const uint32_t *src = (const uint32_t *)&plan;
+        for (uint32_t i = threadIdx.x; i < sizeof(MsdPlan) / 4; i += blockDim.x) dst[i] = src[i];
+        if (threadIdx.x == 0) {
+            ctl->msd_fallback = plan.fallback;
+            if (over) { ctl->n = max_keys; atomicOr(&ctl->err, ERR_KEYS_FULL); }
+        }
+    }
+    if (plan.fallback || n == 0) return;
+    const uint32_t bins = 1u << plan.D;
+    for (uint32_t i = threadIdx.x; i < bins; i += blockDim.x) msd_h[i] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const SortItem it = items[i];
+        uint32_t d;
+        unsigned long long low;
+        msd_extract(plan.runs, plan.nruns, it.hi, it.lo, d, low);
+        atomicAdd(&msd_h[d], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < bins; i += blockDim.x) {
+        const unsigned int c = msd_h[i];
+        if (c) atomicAdd(&mb->hist[i], c);
+    }
+}
+
+// ------------------------------------------------------------------ scatter
+__global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, MsdItem *out, Ctl *ctl, MsdBins *mb)
+{
+    extern __shared__ unsigned int msd_start[];    // [bins + 1]
+    __shared__ unsigned int wsum[32];
+    __shared__ unsigned int s_big;
+    __shared__ MsdRun runs[MSD_MAX_RUNS];
+    if (ctl->msd_fallback) return;
+    const unsigned long long n = ctl->n;
+    if (n == 0) return;
+    const uint32_t D = ctl->msd_plan.D, bins = 1u << D, nruns = ctl->msd_plan.nruns;
+    if (threadIdx.x < nruns) runs[threadIdx.x] = ctl->msd_plan.runs[threadIdx.x];
+    if (threadIdx.x == 0) s_big = 0;
+    // exclusive scan of the histogram: 1024 threads x (bins / 1024) consecutive bins each
+    const uint32_t per = (bins + 1023) / 1024;
+    const uint32_t b0 = threadIdx.x * per;
+    unsigned int c[MSD_MAX_BINS / 1024];
+    unsigned int sum = 0, big = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k) {
+        c[k] = (k < per && b0 + k < bins) ? mb->hist[b0 + k] : 0;
+        sum += c[k];
+        big = max(big, c[k]);
+    }
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (big > UNIT_CAP - UNIT_W) atomicOr(&s_big, 1u);
+    unsigned int woff = 0;
+    for (uint32_t w = 0; w < warp; ++w) woff += wsum[w];
+    unsigned int run = woff + incl - sum;
+#pragma unroll
+    for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k)
+        if (k < per && b0 + k < bins) { msd_start[b0 + k] = run; run += c[k]; }
+    if (threadIdx.x == 0) msd_start[bins] = (unsigned int)n;
+    __syncthreads();
+    if (s_big) {                                    // every CTA sees the same histogram and takes the same way out
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&ctl->msd_fallback, MSD_FB_BIN);
+        return;
+    }
+    if (blockIdx.x == 0)
+        for (uint32_t i = threadIdx.x; i <= bins; i += blockDim.x) mb->bin_start[i] = msd_start[i];
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const SortItem it = items[i];
+        uint32_t d;
+        unsigned long long low;
+        msd_extract(runs, nruns, it.hi, it.lo, d, low);
+        const uint32_t pos = msd_start[d] + atomicAdd(&mb->cursor[d], 1u);
+        MsdItem o;
+        o.low = low;
+        o.val = it.val;
+        o.bin = d | ((it.lo & 0xFFu) == 8u ? MSD_FLAG8 : 0u);
+        out[pos] = o;
+    }
+}
+
+// ------------------------------------------------------------------ units: sort, merge, rows
+struct __align__(16) UnitSmem {
+    MsdItem buf[2][UNIT_CAP];                    // 64 KB: ping-pong of the passes; afterwards buf[other] holds the keys
+    unsigned int whist[UNIT_WARPS][RADIX_BINS];  // 16 KB: per-warp digit counts; afterwards the counts of the items
+    unsigned int bin_excl[RADIX_BINS];
+    unsigned int scan_tmp[RADIX_BINS / 32];
+    uint8_t stage[UNIT_STAGE + 16];              // key bytes of the unit's rows, in the destination's alignment
+    unsigned int wh[UNIT_WARPS];
+    unsigned long long wb[UNIT_WARPS];
+    unsigned long long prefix_h, prefix_b;
+    unsigned int prefix_part, unit, first, count, dfirst, fallback;
+};
+static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned long long) * UNIT_CAP, "counts fit where the warp histograms were");
+
+__global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
+                                                                RowArrays rows, uint32_t num_reducers, uint32_t op,
+                                                                unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl,
+                                                                MsdBins *mb)
+{
+    extern __shared__ __align__(16) uint8_t unit_smem_raw[];
+    UnitSmem &sm = *(UnitSmem *)unit_smem_raw;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt = lanemask_lt();
+    const unsigned long long n = ctl->n;
+    if (tid == 0) {
+        sm.unit = atomicAdd(&mb->unit_ticket, 1u);   // units are taken in order: a unit only waits for started ones
+        sm.fallback = ctl->msd_fallback;
+    }
+    __syncthreads();
+    const uint32_t unit = sm.unit;
+    if (sm.fallback) return;
+    if (n == 0) {
+        if (unit == 0) {
+            for (uint32_t p = tid; p <= num_reducers; p += UNIT_THREADS) rows.part_begin[p] = 0;
+            if (tid == 0) { ctl->n_out = 0; ctl->key_bytes = 0; rows.key_off[0] = 0; }
+        }
+        return;
+    }
+    const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
+    if (unit >= nunits) return;
+    const uint32_t D = ctl->msd_plan.D, bins = 1u << D, low_bits = ctl->msd_plan.low_bits;
+    if (tid == 0) {
+        // bins whose start lies in [unit * W, (unit + 1) * W): lower bounds over the bin starts
+        const unsigned int *bs = mb->bin_start;
+        auto lower = [&](unsigned long long x) {
+            uint32_t lo = 0, hi = bins;              // first b with bs[b] >= x (bs[bins] = n >= x)
+            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (bs[mid] < x) lo = mid + 1; else hi = mid; }
+            return lo;
+        };
+        const uint32_t ba = lower((unsigned long long)unit * UNIT_W);
+        const unsigned long long xe = (unsigned long long)(unit + 1) * UNIT_W;
+        const uint32_t be = xe >= n ? bins : lower(xe);
+        sm.first = bs[ba];
+        sm.count = bs[be] - bs[ba];
+        sm.dfirst = ba;
+    }
+    __syncthreads();
+    const uint32_t first = sm.first, m = sm.count, dfirst = sm.dfirst;   // m < UNIT_CAP (checked by the scatter kernel)
+
+    // ---- load
+    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+        MsdItem it = in[first + i];
+        it.bin = (it.bin & MSD_FLAG8) | ((it.bin & ~MSD_FLAG8) - dfirst);
+        sm.buf[0][i] = it;
+    }
+    uint32_t maxl = 0;
+    if (m) maxl = (in[first + m - 1].bin & ~MSD_FLAG8) - dfirst;           // bins ascend with the position
+    uint32_t lbits = 0;
+    while (lbits < 32 && (1u << lbits) <= maxl) ++lbits;
+    const uint32_t npass = (low_bits + lbits + 7) / 8;
+    __syncthreads();
+
+    // ---- stable LSD passes in shared memory (ranking as in radix_pass_kernel: ballot-built peer masks)
+    uint32_t cur = 0;
+    for (uint32_t pass = 0; pass < npass; ++pass) {
+        for (uint32_t i = tid; i < UNIT_WARPS * RADIX_BINS; i += UNIT_THREADS) (&sm.whist[0][0])[i] = 0;
+        __syncthreads();
+        MsdItem it[UNIT_ITEMS];
+        uint32_t dg[UNIT_ITEMS], rk[UNIT_ITEMS];
+        const uint32_t wbase = warp * (32 * UNIT_ITEMS);
+#pragma unroll
+        for (int i = 0; i < UNIT_ITEMS; ++i) {
+            const uint32_t idx = wbase + i * 32 + lane;
+            const bool valid = idx < m;
+            if (valid) it[i] = sm.buf[cur][idx];
+            else { it[i].low = 0; it[i].val = 0; it[i].bin = 0; }
+            const uint32_t d = msd_pass_digit(it[i].low, it[i].bin & ~MSD_FLAG8, low_bits, pass);
+            dg[i] = d;
+            const uint32_t act = __ballot_sync(0xFFFFFFFFu, valid);
+            uint32_t peers = act;
+#pragma unroll
+            for (int bit = 0; bit < RADIX_BITS; ++bit) {
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, (d >> bit) & 1u);
+                peers &= ((d >> bit) & 1u) ? bal : ~bal;
+            }
+            uint32_t r = 0;
+            if (valid) {
+                const uint32_t leader = __ffs((int)peers) - 1;
+                uint32_t old = 0;
+                if (lane == leader) { old = sm.whist[warp][d]; sm.whist[warp][d] = old + __popc(peers); }
+                old = __shfl_sync(act, old, leader);
+                r = old + __popc(peers & lt);
+            }
+            rk[i] = r;
+            __syncwarp();
+        }
+        __syncthreads();
+        unsigned int tcount = 0, tincl = 0;
+        if (tid < RADIX_BINS) {
+            unsigned int run = 0;
+#pragma unroll
+            for (int w = 0; w < UNIT_WARPS; ++w) { const unsigned int c = sm.whist[w][tid]; sm.whist[w][tid] = run; run += c; }
+            tcount = run;
+            tincl = run;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, tincl, d); if (lane >= d) tincl += v; }
+            if (lane == 31) sm.scan_tmp[warp] = tincl;
+        }
+        __syncthreads();
+        if (tid < RADIX_BINS) {
+            unsigned int wsum = 0;
+            for (uint32_t w = 0; w < warp; ++w) wsum += sm.scan_tmp[w];
+            sm.bin_excl[tid] = wsum + tincl - tcount;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < UNIT_ITEMS; ++i) {
+            const uint32_t idx = wbase + i * 32 + lane;
+            if (idx < m) sm.buf[cur ^ 1][sm.bin_excl[dg[i]] + sm.whist[warp][dg[i]] + rk[i]] = it[i];
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    MsdItem *sorted = sm.buf[cur];
+    ulonglong2 *skey = (ulonglong2 *)sm.buf[cur ^ 1];       // (k0, k1) of sorted[i], filled below
+    unsigned long long *scnt = (unsigned long long *)&sm.whist[0][0];
+
+    // ---- keys that agree in the whole sort word and have 8+ bytes: ordered by their later bytes.  The
+    // first member of such a group orders it (insertion sort on the entry indices, full key compare).
+    auto same_word = [&](uint32_t a, uint32_t b) { return sorted[a].low == sorted[b].low && sorted[a].bin == sorted[b].bin; };
+    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+        if (!(sorted[i].bin & MSD_FLAG8)) continue;
+        if (i > 0 && same_word(i, i - 1)) continue;
+        uint32_t g = 1;
+        while (i + g < m && g <= TIE_SMALL_GROUP && same_word(i, i + g)) ++g;
+        if (g == 1) continue;
+        if (g > TIE_SMALL_GROUP) { atomicOr(&ctl->msd_fallback, MSD_FB_TIES); sm.fallback = 1; continue; }
+        uint32_t v[TIE_SMALL_GROUP];
+        for (uint32_t a = 0; a < g; ++a) v[a] = sorted[i + a].val;
+        for (uint32_t a = 1; a < g; ++a) {
+            const uint32_t x = v[a];
+            const Key kx = ent.key(x);
+            uint32_t b = a;
+            while (b > 0 && key_less(kx, ent.key(v[b - 1]), x, v[b - 1], bytes, 1)) { v[b] = v[b - 1]; --b; }
+            v[b] = x;
+        }
+        for (uint32_t a = 0; a < g; ++a) sorted[i + a].val = v[a];
+        atomicAdd(&ctl->tie_small, 1u);
+    }
+    __syncthreads();
+    // a unit that declined still takes part in the look-back below (with nothing), so that no later
+    // unit waits for it; the rows are rewritten by the LSD path anyway
+    const bool declined = sm.fallback != 0;
+
+    // ---- entries of the sorted items (one 32-byte gather each), heads, row and byte counts
+    const uint32_t base = tid * UNIT_ITEMS;
+    Key key[UNIT_ITEMS];
+    uint32_t part[UNIT_ITEMS], len[UNIT_ITEMS];
+#pragma unroll
+    for (int j = 0; j < UNIT_ITEMS; ++j) {
+        const uint32_t i = base + j;
+        part[j] = 0; len[j] = 0; key[j].k0 = 0; key[j].k1 = 0;
+        if (i < m) {
+            const ulonglong4 e = ld256(&ent.e[sorted[i].val]);
+            key[j].k0 = e.x; key[j].k1 = e.y;
+            part[j] = (uint32_t)e.w;
+            len[j] = key_len(key[j]);
+            skey[i] = make_ulonglong2(e.x, e.y);
+            scnt[i] = e.z;
+        }
+    }
+    __syncthreads();
+    uint32_t headmask = 0, nh = 0;
+    unsigned long long nb = 0;
+#pragma unroll
+    for (int j = 0; j < UNIT_ITEMS; ++j) {
+        const uint32_t i = base + j;
+        if (i >= m || declined) continue;
+        bool head = i == 0 || !same_word(i, i - 1);   // the first item of a unit starts a bin: always a new key
+        if (!head && (sorted[i].bin & MSD_FLAG8)) {
+            Key pk; pk.k0 = skey[i - 1].x; pk.k1 = skey[i - 1].y;
+            head = !same_key(key[j], pk, bytes);
+        }
+        if (head) { headmask |= 1u << j; ++nh; nb += len[j]; }
+    }
+    uint32_t ih = nh;
+    unsigned long long ib = nb;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t vh = __shfl_up_sync(0xFFFFFFFFu, ih, d);
+        const unsigned long long vb = __shfl_up_sync(0xFFFFFFFFu, ib, d);
+        if (lane >= d) { ih += vh; ib += vb; }
+    }
+    if (lane == 31) { sm.wh[warp] = ih; sm.wb[warp] = ib; }
+    __syncthreads();
+    uint32_t oh = ih - nh, th = 0;
+    unsigned long long ob = ib - nb, tb = 0;
+#pragma unroll
+    for (int w = 0; w < UNIT_WARPS; ++w) {
+        if (w < (int)warp) { oh += sm.wh[w]; ob += sm.wb[w]; }
+        th += sm.wh[w]; tb += sm.wb[w];
+    }
+    // ---- look-back over units: rows before, key bytes before, partition of the last row before.
+    // heads word: flag << 62 | (last partition + 1) << 32 | rows; 0 in the partition field = no row
+    constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62;
+    const unsigned long long my_last = (m && !declined) ? (unsigned long long)(ent.part(sorted[m - 1].val) + 1u) : 0ull;
+    if (warp == 0) {
+        volatile unsigned long long *vheads = st.heads, *vagg = st.bytes_agg, *vinc = st.bytes_inc;
+        unsigned long long ph = 0, pb = 0, pl = 0;
+        if (unit == 0) {
+            if (lane == 0) { vinc[0] = tb; __threadfence(); vheads[0] = F_INC | my_last << 32 | th; }
+        } else {
+            if (lane == 0) { vagg[unit] = tb; __threadfence(); vheads[unit] = F_AGG | my_last << 32 | th; }
+            int t = (int)unit - 1;
+            for (uint32_t polls = 0;; ++polls) {
+                if (polls > LOOKBACK_SPIN_LIMIT) { if (lane == 0) atomicOr(&ctl->err, ERR_LOOKBACK_TIMEOUT); break; }
+                const int idx = t - (int)lane;
+                const unsigned long long w = idx >= 0 ? vheads[idx] : F_INC;
+                const uint32_t flag = (uint32_t)(w >> 62);
+                const uint32_t notready = __ballot_sync(0xFFFFFFFFu, flag == 0);
+                const uint32_t incm = __ballot_sync(0xFFFFFFFFu, flag == 2);
+                const uint32_t stop = incm ? (uint32_t)__ffs((int)incm) - 1u : 31u;
+                const uint32_t use = stop == 31 ? 0xFFFFFFFFu : ((2u << stop) - 1u);
+                if (notready & use) continue;
+                __threadfence();
+                unsigned long long b = 0, h = 0, l = 0;
+                if ((use >> lane) & 1u) {
+                    h = w & 0xFFFFFFFFull;
+                    l = (w >> 32) & 0x3FFFFFFFull;
+                    if (idx >= 0) b = flag == 2 ? vinc[idx] : vagg[idx];
+                }
+                for (int d = 16; d; d >>= 1) {
+                    h += __shfl_xor_sync(0xFFFFFFFFu, h, d);
+                    b += __shfl_xor_sync(0xFFFFFFFFu, b, d);
+                    l = max(l, __shfl_xor_sync(0xFFFFFFFFu, l, d));   // partitions ascend with the units
+                }
+                ph += h; pb += b; pl = max(pl, l);
+                if (incm) break;
+                t -= 32;
+            }
+            if (lane == 0) { vinc[unit] = pb + tb; __threadfence(); vheads[unit] = F_INC | max(pl, my_last) << 32 | (ph + th); }
+        }
+        if (lane == 0) { sm.prefix_h = ph; sm.prefix_b = pb; sm.prefix_part = (unsigned int)pl; }
+    }
+    __syncthreads();
+    if (declined) return;
+    unsigned long long o = sm.prefix_h + oh, boff = sm.prefix_b + ob;
+    const unsigned long long unit_b0 = sm.prefix_b;
+    const bool overflow = unit_b0 + tb > key_bytes_cap;
+    if (overflow && tid == 0) atomicOr(&ctl->err, ERR_KEYS_FULL);
+    const uint32_t mis = (uint32_t)(unit_b0 & 15);
+    const bool staged = !overflow && tb <= UNIT_STAGE;
+    const bool last_unit = unit == nunits - 1;
+#pragma unroll
+    for (int j = 0; j < UNIT_ITEMS; ++j) {
+        const uint32_t i = base + j;
+        if (i >= m) break;
+        if (!((headmask >> j) & 1u)) continue;
+        // the values of the equal keys that follow (the same key from other ranks) merge into this row
+        unsigned long long c = scnt[i];
+        for (uint32_t q = i + 1; q < m; ++q) {
+            if (!same_word(q, i)) break;
+            if (sorted[q].bin & MSD_FLAG8) {
+                Key a; a.k0 = skey[q].x; a.k1 = skey[q].y;
+                if (!same_key(a, key[j], bytes)) break;
+            }
+            c = (op == OP_SUM || op == OP_COUNT) ? c + scnt[q] : max(c, scnt[q]);
+        }
+        rows.part[o] = part[j];
+        rows.count[o] = c;
+        rows.key_off[o] = boff;
+        if (staged) write_key_bytes(sm.stage + mis + (uint32_t)(boff - unit_b0), key[j], len[j], bytes);
+        else if (!overflow) write_key_bytes(rows.key_bytes + boff, key[j], len[j], bytes);
+        // partition starts: rows are partition-sorted; the row before this one is the previous head
+        // of the unit or, for the unit's first row, the last row of the units before (look-back)
+        uint32_t p_first;
+        bool new_part;
+        if (i == 0) {
+            p_first = sm.prefix_part;                   // (last partition before) + 1, or 0 if there is no row before
+            new_part = sm.prefix_part == 0 || sm.prefix_part - 1 != part[j];
+        } else {
+            const uint32_t pp = j > 0 ? part[j - 1] : ent.part(sorted[i - 1].val);
+            p_first = pp + 1;
+            new_part = pp != part[j];
+        }
+        if (new_part)
+            for (uint32_t q = p_first; q <= part[j] && q <= num_reducers; ++q) rows.part_begin[q] = o;
+        boff += len[j];
+        ++o;
+    }
+    // totals and sentinels: the thread that holds the last item of the last unit
+    if (last_unit && m && base < m && base + UNIT_ITEMS >= m) {
+        ctl->n_out = o;
+        ctl->key_bytes = boff;
+        rows.key_off[o] = boff;
+        for (uint32_t q = ent.part(sorted[m - 1].val) + 1u; q <= num_reducers; ++q) rows.part_begin[q] = o;
+    }
+    if (last_unit && m == 0 && tid == 0) {
+        // cannot happen (the last unit holds the last bin start), kept for safety
+        ctl->n_out = sm.prefix_h; ctl->key_bytes = sm.prefix_b; rows.key_off[sm.prefix_h] = sm.prefix_b;
+    }
+    if (staged) {
+        __syncthreads();
+        uint8_t *dst = rows.key_bytes + (unit_b0 - mis);
+        const uint32_t end = mis + (uint32_t)tb;
+        for (uint32_t cb = tid * 16; cb < end; cb += UNIT_THREADS * 16) {
+            if (cb >= mis && cb + 16 <= end) {
+                *(uint4 *)(dst + cb) = *(const uint4 *)(sm.stage + cb);
+            } else {
+                for (uint32_t q = cb < mis ? mis : cb; q < cb + 16 && q < end; ++q) dst[q] = sm.stage[q];
+            }
+        }
+    }
+}
+
+} // namespace mr

@@ -38,6 +38,16 @@ struct __align__(16) SortItem {
     uint32_t val;          // entry index
 };
 
+// plan of the most-significant-digit path (msd_kernels.cuh): the varying bits of the sort word,
+// packed; one run = consecutive varying bits: source bit (0..63 = lo, 64..95 = hi), width,
+// destination bit in the packed low word or in the digit
+constexpr int MSD_MAX_RUNS = 32;
+struct MsdRun { uint8_t shift, width, dst, to_digit; };
+struct MsdPlan {
+    uint32_t nruns, D, low_bits, fallback;
+    MsdRun runs[MSD_MAX_RUNS];
+};
+
 struct Ctl {
     unsigned long long n;            // entries (distinct keys before the merge)
     unsigned long long or_lo, and_lo;
@@ -60,6 +70,9 @@ struct Ctl {
     unsigned int tickets[MAX_PASSES];
     unsigned int ghist[MAX_PASSES][RADIX_BINS];
     long long dbg[16];               // MRGPU_SORT_TIMING builds: clock64 stamps of one tile
+    MsdPlan msd_plan;                // msd_kernels.cuh
+    unsigned int msd_fallback;       // non-zero: the MSD path declined this job (MSD_FB_* bits)
+    unsigned int msd_pad;
 };
 
 // Dense entries: the occupied slots of the global table copied side by side, 32 bytes each

@@ -8,6 +8,7 @@
 
 #include "common.cuh"
 #include "reduce_kernels.cuh"
+#include "msd_kernels.cuh"
 
 using namespace mr;
 
@@ -150,6 +151,27 @@ unsigned long long th_op_roundtrip(uint32_t op, unsigned long long a, unsigned l
     const unsigned long long ea = op_encode(op, a), eb = op_encode(op, b);
     const unsigned long long m = (op == OP_SUM || op == OP_COUNT) ? ea + eb : (ea > eb ? ea : eb);
     return op_decode(op, m);
+}
+
+// the most-significant-digit path's plan for the varying bits (vlo, vhi) of n items:
+// out = {D, low_bits, fallback, nruns}; returns the digit of the sort word (hi, lo), *low = packed low bits
+uint32_t th_msd_extract(uint64_t vlo, uint32_t vhi, uint64_t n, uint32_t hi, uint64_t lo, uint64_t *low, uint32_t *out)
+{
+    MsdPlan p;
+    memset(&p, 0, sizeof p);
+    msd_build_plan(vlo, vhi, n, &p);
+    out[0] = p.D; out[1] = p.low_bits; out[2] = p.fallback; out[3] = p.nruns;
+    uint32_t d = 0;
+    unsigned long long l = 0;
+    if (!p.fallback) msd_extract(p.runs, p.nruns, hi, lo, d, l);
+    *low = l;
+    return d;
+}
+
+// digit of pass `pass` of a unit's shared-memory sort: bits [8 pass, 8 pass + 8) of (local bin : low)
+uint32_t th_msd_pass_digit(uint64_t low, uint32_t lbin, uint32_t low_bits, uint32_t pass)
+{
+    return msd_pass_digit(low, lbin, low_bits, pass);
 }
 
 } // extern "C"
