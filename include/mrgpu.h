@@ -82,8 +82,10 @@ typedef struct mr_job_info {
     uint64_t key_bytes;     /* sum of len(key) over this rank's rows */
     uint64_t map_keys;      /* distinct keys after this rank's combine, before the shuffle */
     uint32_t tie_rounds;    /* extra ordering rounds needed for keys equal in their first 7 bytes */
-    uint32_t flags;
+    uint32_t flags;         /* MR_JOB_* bits: which sort path reduced the job (both give the same rows) */
 } mr_job_info;
+#define MR_JOB_REDUCED_LSD 1u   /* rows came from the global LSD radix path (reduce_kernels.cuh) */
+#define MR_JOB_MSD_DECLINED 2u  /* the shared-memory path (msd_kernels.cuh) was tried first and declined; bits 8.. say why */
 
 /* Device-side layout of the reduced rows, in the reference's final order
  * (partition ascending, key ascending: server.lua:365, utils.lua:214).  All

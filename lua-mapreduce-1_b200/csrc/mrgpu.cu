@@ -75,6 +75,7 @@ __global__ void ctl_owner_reset_kernel(Ctl *ctl)
     ctl->n = 0;
     ctl->or_lo = 0; ctl->and_lo = ~0ull; ctl->or_hi = 0; ctl->and_hi = ~0u;
     ctl->npasses = 0;
+    for (int i = 0; i < 56; ++i) (&ctl->occ[0][0])[i] = 0;
     ctl->n_tie = 0; ctl->tie_overflow = 0; ctl->tie_small = 0; ctl->rows_ticket = 0;
     ctl->n_out = 0; ctl->key_bytes = 0;
     ctl->max_tie_len = 0;
@@ -991,7 +992,7 @@ int launch_msd(mr_ctx *ctx)
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
     ctx->msd_parity ^= 1;
     msd_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 2), 256, MSD_MAX_BINS * 4, s>>>(
-        ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, mb, other, ctx->rows_st, ctx->rows_tiles);
+        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->rows_st, ctx->rows_tiles);
     msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
         ctx->bufs.item[0], (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
@@ -1125,7 +1126,9 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
         CU(cudaStreamSynchronize(ctx->stream));
         int rc = check_device_err(ctx, ctx->h_ctl->err);
         if (rc) return rc;
+        uint32_t flags = ctx->used_msd ? 0u : MR_JOB_REDUCED_LSD;
         if (ctx->used_msd && ctx->h_ctl->msd_fallback) {
+            flags = MR_JOB_REDUCED_LSD | MR_JOB_MSD_DECLINED | (ctx->h_ctl->msd_fallback << 8);
             // the MSD path declined (msd_kernels.cuh, "fallback"): the whole reduce side again on the LSD
             // path, from the untouched sort items; later jobs of this context start there
             ctx->prefer_lsd = true;
@@ -1160,8 +1163,17 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
         ctx->info.key_bytes = ctx->h_ctl->key_bytes;
         if (!ctx->imported) ctx->info.map_keys = ctx->h_ctl->n;
         if (ctx->p2p_sent_pending) { ctx->info.map_keys = ctx->h_ctl->sent; ctx->p2p_sent_pending = false; }
+        if (ctx->shuffle_counted && !ctx->p2p_sent_pending && ctx->info.map_keys == 0 && ctx->cfg.world_size > 0) {
+            // fixed-slot shuffle: the records this rank sent were only ever counted on the device
+            const uint32_t W = ctx->cfg.world_size;
+            CU(cudaMemcpyAsync(ctx->h_stage, ctx->d_shuf, W * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            uint64_t sent = 0;
+            for (uint32_t d = 0; d < W; ++d) sent += ctx->h_stage[d];
+            ctx->info.map_keys = sent;
+        }
         ctx->info.tie_rounds = ctx->tie_rounds;
-        ctx->info.flags = 0;
+        ctx->info.flags = flags;
         if (ctx->map_timed) cudaEventElapsedTime(&ctx->stats.map_ms, ctx->ev_map0, ctx->ev_map1);
         if (ctx->red_timed) cudaEventElapsedTime(&ctx->stats.reduce_ms, ctx->ev_red0, ctx->ev_red1);
         ctx->state = mr_ctx::SYNCED;

@@ -6,9 +6,11 @@
 // job.lua:272-287 -- the same reference code the LSD path of reduce_kernels.cuh replaces; that path
 // stays for what this one declines (see "fallback").
 //
-//   msd_hist_kernel     the varying bits of the 96-bit sort word (partition, 7 key bytes, min(len, 8))
-//                       are packed; their top D bits (D <= 14, chosen so that a bin holds ~64 items)
-//                       are the most-significant digit: one histogram over all items.
+//   msd_hist_kernel     the sort word (partition, 7 key bytes, min(len, 8)) is read as 9 fields; every
+//                       key byte is replaced by its rank among the byte values that occur at its
+//                       position (dense codes whatever the alphabet), and the bin of an item is the
+//                       mixed-radix number of its leading fields, refined until a bin holds ~64 items
+//                       (at most 2^15 bins): one histogram over all items.
 //   msd_scatter_kernel  bin starts (every CTA scans the histogram for itself), then every item goes to
 //                       its bin as {packed low bits, entry index, bin}: items of one bin lie together,
 //                       bins in key order.
@@ -20,8 +22,8 @@
 //                       written straight from the unit, numbered by a decoupled look-back over units.
 //
 // Fallback: the path declines (Ctl::msd_fallback, nothing written that the LSD path would not
-// overwrite) when the packed low bits exceed 64, the varying bits form more than 32 runs, a bin holds
-// more than UNIT_CAP - UNIT_W items (many more keys than 2^14 bins can spread), or a group of keys
+// overwrite) when the packed low bits exceed 64, a bin holds more than UNIT_CAP - UNIT_W items
+// (many more keys than 2^15 bins can spread, or keys that only differ late), or a group of keys
 // equal in their first 7 bytes has more than TIE_SMALL_GROUP members.  mr_job_sync then runs the LSD
 // path; a context that declined once goes straight to the LSD path afterwards.
 #pragma once
@@ -29,9 +31,9 @@
 
 namespace mr {
 
-constexpr int MSD_MAX_BITS = 14;
+constexpr int MSD_MAX_BITS = 15;
 constexpr uint32_t MSD_MAX_BINS = 1u << MSD_MAX_BITS;
-constexpr uint32_t MSD_TARGET_BIN = 64;      // items per bin aimed at
+constexpr uint32_t MSD_TARGET_BIN = 32;      // items per bin aimed at (a bin may hold up to UNIT_CAP - UNIT_W: room for 32x skew)
 constexpr uint32_t UNIT_W = 1024;            // a unit owns the bins that start inside its 1024 positions
 constexpr uint32_t UNIT_CAP = 2048;          // ... so it holds fewer than UNIT_W + largest bin items
 constexpr int UNIT_THREADS = 512;
@@ -39,7 +41,7 @@ constexpr int UNIT_WARPS = UNIT_THREADS / 32;
 constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS; // 4
 constexpr uint32_t UNIT_STAGE = UNIT_CAP * INLINE_MAX;
 
-enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_RUNS = 2u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
+enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 
 // histogram, scatter cursors and bin starts; two of these alternate by job so that each job finds
 // its own zeroed (the histogram kernel of a job clears the other one)
@@ -61,63 +63,84 @@ struct __align__(16) MsdItem {
 constexpr uint32_t MSD_FLAG8 = 1u << 31;
 static_assert(sizeof(MsdItem) == sizeof(SortItem), "the scattered items reuse the second sort buffer");
 
-__host__ __device__ __forceinline__ uint32_t popc64_hd(unsigned long long x)
+__host__ __device__ __forceinline__ uint32_t popc32_hd(uint32_t x)
 {
 #ifdef __CUDA_ARCH__
-    return (uint32_t)__popcll(x);
+    return (uint32_t)__popc(x);
 #else
-    return (uint32_t)__builtin_popcountll(x);
+    return (uint32_t)__builtin_popcount(x);
 #endif
 }
-
-// The plan: packed position j of the j-th varying bit (least significant first: lo bit 0 upwards, then
-// hi), the top D packed bits are the digit.  Runs never straddle the lo/hi boundary nor the
-// low/digit boundary.
-__host__ __device__ inline void msd_build_plan(unsigned long long vlo, uint32_t vhi, unsigned long long n, MsdPlan *p)
+__host__ __device__ __forceinline__ uint32_t bits_for(uint32_t card) // bits that hold the ranks 0..card-1
 {
-    const uint32_t V = popc64_hd(vlo) + popc64_hd(vhi);
-    uint32_t D = 0;
-    while (D < (uint32_t)MSD_MAX_BITS && ((unsigned long long)MSD_TARGET_BIN << D) < n) ++D;
-    if (D > V) D = V;
-    const uint32_t low_bits = V - D;
-    p->D = D;
-    p->low_bits = low_bits;
-    p->fallback = low_bits > 64 ? MSD_FB_WIDE : 0;
-    uint32_t packed = 0, nr = 0;
-    for (int half = 0; half < 2 && !p->fallback; ++half) {
-        unsigned long long v = half ? (unsigned long long)vhi : vlo;
-        const uint32_t base = half ? 64 : 0;
-        while (v) {
-            const uint32_t start = (uint32_t)ffs64(v) - 1;
-            const unsigned long long ones = ~(v >> start);
-            uint32_t w = ones ? (uint32_t)ffs64(ones) - 1 : 64 - start;
-            if (packed < low_bits && packed + w > low_bits) w = low_bits - packed;
-            if (nr == (uint32_t)MSD_MAX_RUNS) { p->fallback |= MSD_FB_RUNS; break; }
-            MsdRun r;
-            r.shift = (uint8_t)(base + start);
-            r.width = (uint8_t)w;
-            r.to_digit = packed >= low_bits;
-            r.dst = (uint8_t)(r.to_digit ? packed - low_bits : packed);
-            p->runs[nr++] = r;
-            packed += w;
-            v &= ~((w >= 64 ? ~0ull : ((1ull << w) - 1)) << start);
-        }
-    }
-    p->nruns = nr;
+    return card <= 1 ? 0u : 32u - (uint32_t)clz32(card - 1);
 }
 
-__host__ __device__ __forceinline__ void msd_extract(const MsdRun *runs, uint32_t nruns, uint32_t hi, unsigned long long lo,
-                                                     uint32_t &digit, unsigned long long &low)
+// The plan from the occupancy masks (occ[p][8] = 256-bit mask of the byte values at key byte p), the
+// partition count and the number of items.
+__host__ __device__ inline void msd_build_plan(const unsigned int (*occ)[8], uint32_t num_reducers, unsigned long long n,
+                                               MsdPlan *p)
 {
-    digit = 0;
-    low = 0;
-    for (uint32_t i = 0; i < nruns; ++i) {
-        const MsdRun r = runs[i];
-        const unsigned long long src = r.shift < 64 ? lo >> r.shift : (unsigned long long)(hi >> (r.shift - 64));
-        const unsigned long long f = src & (r.width >= 64 ? ~0ull : ((1ull << r.width) - 1));
-        if (r.to_digit) digit |= (uint32_t)f << r.dst;
-        else low |= f << r.dst;
+    p->card[0] = num_reducers;
+    for (int f = 0; f < 7; ++f) {
+        uint32_t c = 0;
+        for (int w = 0; w < 8; ++w) c += popc32_hd(occ[f][w]);
+        p->card[1 + f] = c ? c : 1;
     }
+    p->card[8] = 9;
+    uint32_t low_all = 0;
+    for (int f = 0; f < MSD_FIELDS; ++f) { p->width[f] = (uint8_t)bits_for(p->card[f]); low_all += p->width[f]; }
+    unsigned long long T = n / MSD_TARGET_BIN;
+    if (T < 1) T = 1;
+    if (T > MSD_MAX_BINS) T = MSD_MAX_BINS;
+    unsigned long long P = 1;
+    uint32_t k = 0;
+    while (k < (uint32_t)MSD_FIELDS && P * p->card[k] <= T) { P *= p->card[k]; ++k; }
+    unsigned long long e = 1;
+    if (k < (uint32_t)MSD_FIELDS) {
+        e = T / P;
+        if (e < 1) e = 1;
+        if (e > p->card[k]) e = p->card[k];
+    }
+    p->k = k;
+    p->e = (uint32_t)e;
+    p->nbins = (uint32_t)(P * e);
+    uint32_t low_bits = low_all;
+    for (uint32_t f = 0; f < k; ++f) low_bits -= p->width[f];
+    p->low_bits = low_bits;
+    p->fallback = low_bits > 64 ? MSD_FB_WIDE : 0;
+    p->pad[0] = p->pad[1] = p->pad[2] = 0;
+}
+
+// rank of byte value v under a 256-bit occupancy mask: how many occurring values are smaller
+__host__ __device__ __forceinline__ uint32_t msd_rank_of(const unsigned int *occ8, uint32_t v)
+{
+    uint32_t r = 0;
+    for (uint32_t w = 0; w < (v >> 5); ++w) r += popc32_hd(occ8[w]);
+    return r + popc32_hd(occ8[v >> 5] & ((1u << (v & 31)) - 1u));
+}
+
+// bin and packed low word of one sort word (hi = partition, lo = 7 key bytes big-endian << 8 | min(len, 8))
+__host__ __device__ __forceinline__ void msd_extract(const MsdPlan &p, const unsigned char (*lut)[256], uint32_t hi,
+                                                     unsigned long long lo, uint32_t &bin, unsigned long long &low)
+{
+    uint32_t rank[MSD_FIELDS];
+    rank[0] = hi;
+#pragma unroll
+    for (int f = 0; f < 7; ++f) rank[1 + f] = lut[f][(uint32_t)(lo >> (56 - 8 * f)) & 0xFFu];
+    rank[8] = (uint32_t)lo & 0xFFu;
+    uint32_t b = 0;
+    unsigned long long l = 0;
+#pragma unroll
+    for (int f = 0; f < MSD_FIELDS; ++f) {
+        if ((uint32_t)f < p.k) b = b * p.card[f] + rank[f];
+        else {
+            if ((uint32_t)f == p.k) b = b * p.e + (uint32_t)(((unsigned long long)rank[f] * p.e) / p.card[f]);
+            l = (l << p.width[f]) | rank[f];
+        }
+    }
+    bin = b;
+    low = l;
 }
 
 // 8-bit digit `pass` of the virtual number (local bin : low), least significant first
@@ -134,11 +157,13 @@ __host__ __device__ __forceinline__ uint32_t msd_pass_digit(unsigned long long l
 }
 
 // ------------------------------------------------------------------ histogram
-__global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, unsigned long long max_keys, Ctl *ctl,
-                                                       MsdBins *mb, MsdBins *mb_next, RowsStatus st, uint32_t st_words)
+__global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, unsigned long long max_keys, uint32_t num_reducers,
+                                                       Ctl *ctl, MsdBins *mb, MsdBins *mb_next, RowsStatus st, uint32_t st_words)
 {
-    extern __shared__ unsigned int msd_h[];        // [1 << D] (at most MSD_MAX_BINS)
+    extern __shared__ unsigned int msd_h[];        // [nbins] (at most MSD_MAX_BINS)
     __shared__ MsdPlan plan;
+    __shared__ unsigned int s_occ[7][8];
+    __shared__ unsigned char lut[7][256];
     unsigned long long n = ctl->n;
     const bool over = n > max_keys;
     if (over) n = max_keys;
@@ -150,24 +175,23 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
         const uint64_t units = (n + UNIT_W - 1) / UNIT_W + 1;
         for (uint64_t i = g0; i < units && i < st_words; i += gs) { st.heads[i] = 0; st.bytes_agg[i] = 0; st.bytes_inc[i] = 0; }
     }
-    if (threadIdx.x == 0) {
-        unsigned long long vlo = ctl->or_lo ^ ctl->and_lo;
-        uint32_t vhi = ctl->or_hi ^ ctl->and_hi;
-        if (n < 2) { vlo = 0; vhi = 0; }
-        msd_build_plan(vlo, vhi, n, &plan);
-    }
+    if (threadIdx.x < 56) (&s_occ[0][0])[threadIdx.x] = (&ctl->occ[0][0])[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) msd_build_plan(s_occ, num_reducers, n, &plan);
+    for (int f = 0; f < 7; ++f) lut[f][threadIdx.x] = (unsigned char)msd_rank_of(s_occ[f], threadIdx.x);   // 256 threads
     __syncthreads();
     if (blockIdx.x == 0) {
         uint32_t *dst = (uint32_t *)&ctl->msd_plan;
         const uint32_t *src = (const uint32_t *)&plan;
         for (uint32_t i = threadIdx.x; i < sizeof(MsdPlan) / 4; i += blockDim.x) dst[i] = src[i];
+        for (int f = 0; f < 7; ++f) ctl->msd_lut[f][threadIdx.x] = lut[f][threadIdx.x];
         if (threadIdx.x == 0) {
             ctl->msd_fallback = plan.fallback;
             if (over) { ctl->n = max_keys; atomicOr(&ctl->err, ERR_KEYS_FULL); }
         }
     }
     if (plan.fallback || n == 0) return;
-    const uint32_t bins = 1u << plan.D;
+    const uint32_t bins = plan.nbins;
     for (uint32_t i = threadIdx.x; i < bins; i += blockDim.x) msd_h[i] = 0;
     __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -175,7 +199,7 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
         const SortItem it = items[i];
         uint32_t d;
         unsigned long long low;
-        msd_extract(plan.runs, plan.nruns, it.hi, it.lo, d, low);
+        msd_extract(plan, lut, it.hi, it.lo, d, low);
         atomicAdd(&msd_h[d], 1u);
     }
     __syncthreads();
@@ -191,13 +215,16 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
     extern __shared__ unsigned int msd_start[];    // [bins + 1]
     __shared__ unsigned int wsum[32];
     __shared__ unsigned int s_big;
-    __shared__ MsdRun runs[MSD_MAX_RUNS];
+    __shared__ MsdPlan plan;
+    __shared__ unsigned char lut[7][256];
     if (ctl->msd_fallback) return;
     const unsigned long long n = ctl->n;
     if (n == 0) return;
-    const uint32_t D = ctl->msd_plan.D, bins = 1u << D, nruns = ctl->msd_plan.nruns;
-    if (threadIdx.x < nruns) runs[threadIdx.x] = ctl->msd_plan.runs[threadIdx.x];
+    for (uint32_t i = threadIdx.x; i < sizeof(MsdPlan) / 4; i += blockDim.x) ((uint32_t *)&plan)[i] = ((const uint32_t *)&ctl->msd_plan)[i];
+    for (uint32_t i = threadIdx.x; i < 7 * 256 / 4; i += blockDim.x) ((uint32_t *)&lut[0][0])[i] = ((const uint32_t *)&ctl->msd_lut[0][0])[i];
     if (threadIdx.x == 0) s_big = 0;
+    __syncthreads();
+    const uint32_t bins = plan.nbins;
     // exclusive scan of the histogram: 1024 threads x (bins / 1024) consecutive bins each
     const uint32_t per = (bins + 1023) / 1024;
     const uint32_t b0 = threadIdx.x * per;
@@ -214,8 +241,8 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
     if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
     if (big > UNIT_CAP - UNIT_W) atomicOr(&s_big, 1u);
+    __syncthreads();
     unsigned int woff = 0;
     for (uint32_t w = 0; w < warp; ++w) woff += wsum[w];
     unsigned int run = woff + incl - sum;
@@ -235,7 +262,7 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
         const SortItem it = items[i];
         uint32_t d;
         unsigned long long low;
-        msd_extract(runs, nruns, it.hi, it.lo, d, low);
+        msd_extract(plan, lut, it.hi, it.lo, d, low);
         const uint32_t pos = msd_start[d] + atomicAdd(&mb->cursor[d], 1u);
         MsdItem o;
         o.low = low;
@@ -284,7 +311,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     }
     const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
     if (unit >= nunits) return;
-    const uint32_t D = ctl->msd_plan.D, bins = 1u << D, low_bits = ctl->msd_plan.low_bits;
+    const uint32_t bins = ctl->msd_plan.nbins, low_bits = ctl->msd_plan.low_bits;
     if (tid == 0) {
         // bins whose start lies in [unit * W, (unit + 1) * W): lower bounds over the bin starts
         const unsigned int *bs = mb->bin_start;

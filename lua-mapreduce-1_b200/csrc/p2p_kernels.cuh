@@ -201,6 +201,8 @@ __global__ void __launch_bounds__(256) p2p_index_kernel(const uint8_t *buf, cons
 {
     __shared__ unsigned long long s_n, s_base;
     __shared__ bool s_ok;
+    __shared__ unsigned int s_occ[56];
+    occ_clear(s_occ);
     const uint32_t src = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
     const unsigned long long slot_at = (unsigned long long)src * slot_bytes;
     if (threadIdx.x == 0) {
@@ -261,10 +263,11 @@ __global__ void __launch_bounds__(256) p2p_index_kernel(const uint8_t *buf, cons
             SortItem it; it.lo = ck; it.hi = part; it.val = (uint32_t)(ent0 + first + i);
             items[base + i] = it;
             hi_or |= part; hi_and &= part; lo_or |= ck; lo_and &= ck;
+            occ_add(s_occ, ck);
             any = true;
         }
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ);
 }
 
 } // namespace mr

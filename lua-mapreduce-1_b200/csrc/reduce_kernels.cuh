@@ -38,20 +38,25 @@ struct __align__(16) SortItem {
     uint32_t val;          // entry index
 };
 
-// plan of the most-significant-digit path (msd_kernels.cuh): the varying bits of the sort word,
-// packed; one run = consecutive varying bits: source bit (0..63 = lo, 64..95 = hi), width,
-// destination bit in the packed low word or in the digit
-constexpr int MSD_MAX_RUNS = 32;
-struct MsdRun { uint8_t shift, width, dst, to_digit; };
+// Plan of the most-significant-digit path (msd_kernels.cuh).  The sort word is read as 9 fields,
+// most significant first: partition, key bytes 0..6, min(len, 8).  A key byte is replaced by its RANK
+// among the byte values that occur at that position in this job (Ctl::occ), so the codes are dense
+// whatever the alphabet is; the bin of an item is the mixed-radix number of its first k fields times
+// e, plus a monotone e-way split of field k; the rest of the order is the bit-packed ranks of the
+// fields k..8 ("low").
+constexpr int MSD_FIELDS = 9;
 struct MsdPlan {
-    uint32_t nruns, D, low_bits, fallback;
-    MsdRun runs[MSD_MAX_RUNS];
+    uint32_t nbins, k, e, low_bits, fallback;
+    uint32_t card[MSD_FIELDS];      // values a field can take (partition: num_reducers; bytes: occurring values; length: 9)
+    uint8_t width[MSD_FIELDS];      // bits of a field's rank in the packed low word
+    uint8_t pad[3];
 };
 
 struct Ctl {
     unsigned long long n;            // entries (distinct keys before the merge)
     unsigned long long or_lo, and_lo;
     unsigned int or_hi, and_hi;
+    unsigned int occ[7][8];          // byte values that occur at key byte 0..6 (256-bit masks), for the MSD plan
     unsigned int npasses;
     unsigned int err;
     unsigned int n_tie;              // members of tie groups larger than TIE_SMALL_GROUP
@@ -73,6 +78,7 @@ struct Ctl {
     MsdPlan msd_plan;                // msd_kernels.cuh
     unsigned int msd_fallback;       // non-zero: the MSD path declined this job (MSD_FB_* bits)
     unsigned int msd_pad;
+    unsigned char msd_lut[7][256];   // rank of a byte value at key byte 0..6
 };
 
 // Dense entries: the occupied slots of the global table copied side by side, 32 bytes each
@@ -112,9 +118,31 @@ __device__ __forceinline__ ulonglong4 ld256_coherent(const void *p)
 }
 
 // ------------------------------------------------------------------ K3
-__device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
-                                             uint64_t lo_or, uint64_t lo_and, bool any)
+// which byte values occur at each of the 7 key-byte positions of the sort word: per-CTA masks in
+// shared memory (zeroed by occ_clear before the first occ_add), merged into Ctl::occ by orand_commit
+__device__ __forceinline__ void occ_clear(unsigned int *s_occ)
 {
+    if (threadIdx.x < 56) s_occ[threadIdx.x] = 0;
+    __syncthreads();
+}
+__device__ __forceinline__ void occ_add(unsigned int *s_occ, unsigned long long chunk)
+{
+#pragma unroll
+    for (int p = 0; p < 7; ++p) {
+        const uint32_t b = (uint32_t)(chunk >> (56 - 8 * p)) & 0xFFu;
+        const uint32_t bit = 1u << (b & 31);
+        unsigned int *w = &s_occ[p * 8 + (b >> 5)];
+        if (!(*(volatile unsigned int *)w & bit)) atomicOr(w, bit);
+    }
+}
+
+__device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
+                                             uint64_t lo_or, uint64_t lo_and, bool any, const unsigned int *s_occ = nullptr)
+{
+    if (s_occ) {
+        __syncthreads();
+        if (threadIdx.x < 56 && s_occ[threadIdx.x]) atomicOr(&ctl->occ[0][0] + threadIdx.x, s_occ[threadIdx.x]);
+    }
     // warp-reduce, block-reduce, then one set of atomics per CTA (same-address atomics serialise)
     __shared__ uint32_t s_hi_or[8], s_hi_and[8], s_any[8];
     __shared__ unsigned long long s_lo_or[8], s_lo_and[8];
@@ -164,6 +192,8 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
     __shared__ ulonglong4 s_ent[256 * ITEMS];
     __shared__ unsigned int wsum[8];
     __shared__ unsigned long long s_base;
+    __shared__ unsigned int s_occ[56];
+    occ_clear(s_occ);
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t tile_slots = 256 * ITEMS;
     const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
@@ -214,11 +244,12 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
             SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
             items[idx] = it;
             hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
+            occ_add(s_occ, chunk);
             any = true;
         }
         __syncthreads();
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ);
 }
 
 // dense entries -> partition id + sort item (+ which key bits vary at all)
@@ -228,6 +259,8 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
     const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind, EntryArrays ent, SortItem *items,
     uint64_t max_keys, Ctl *ctl)
 {
+    __shared__ unsigned int s_occ[56];
+    occ_clear(s_occ);
     uint32_t hi_or = 0, hi_and = ~0u;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
@@ -242,9 +275,10 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
         SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
         items[idx] = it;
         hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
+        occ_add(s_occ, chunk);
         any = true;
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any);
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ);
 }
 
 // ------------------------------------------------------------------ K5 radix sort

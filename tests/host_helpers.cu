@@ -153,17 +153,22 @@ unsigned long long th_op_roundtrip(uint32_t op, unsigned long long a, unsigned l
     return op_decode(op, m);
 }
 
-// the most-significant-digit path's plan for the varying bits (vlo, vhi) of n items:
-// out = {D, low_bits, fallback, nruns}; returns the digit of the sort word (hi, lo), *low = packed low bits
-uint32_t th_msd_extract(uint64_t vlo, uint32_t vhi, uint64_t n, uint32_t hi, uint64_t lo, uint64_t *low, uint32_t *out)
+// the most-significant-digit path's plan for a job of n items whose key bytes take the values in
+// occ (7 x 256-bit masks): out = {nbins, k, e, low_bits, fallback}; returns the bin of the sort word
+// (hi, lo), *low = its packed low word
+uint32_t th_msd_extract(const uint32_t *occ /* [7][8] */, uint32_t num_reducers, uint64_t n, uint32_t hi, uint64_t lo,
+                        uint64_t *low, uint32_t *out)
 {
     MsdPlan p;
     memset(&p, 0, sizeof p);
-    msd_build_plan(vlo, vhi, n, &p);
-    out[0] = p.D; out[1] = p.low_bits; out[2] = p.fallback; out[3] = p.nruns;
+    msd_build_plan((const unsigned int (*)[8])occ, num_reducers, n, &p);
+    out[0] = p.nbins; out[1] = p.k; out[2] = p.e; out[3] = p.low_bits; out[4] = p.fallback;
+    static unsigned char lut[7][256];
+    for (int f = 0; f < 7; ++f)
+        for (uint32_t v = 0; v < 256; ++v) lut[f][v] = (unsigned char)msd_rank_of(occ + 8 * f, v);
     uint32_t d = 0;
     unsigned long long l = 0;
-    if (!p.fallback) msd_extract(p.runs, p.nruns, hi, lo, d, l);
+    if (!p.fallback) msd_extract(p, lut, hi, lo, d, l);
     *low = l;
     return d;
 }

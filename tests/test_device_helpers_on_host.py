@@ -62,7 +62,7 @@ def lib():
     L.th_op_roundtrip.restype = C.c_uint64
     L.th_op_roundtrip.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64]
     L.th_msd_extract.restype = C.c_uint32
-    L.th_msd_extract.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+    L.th_msd_extract.argtypes = [C.POINTER(C.c_uint32), C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
     L.th_msd_pass_digit.restype = C.c_uint32
     L.th_msd_pass_digit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
     return L
@@ -265,48 +265,42 @@ def test_reducer_encodings_have_identity_zero_and_merge_correctly(lib):
         assert lib.th_op_roundtrip(COUNT, a, b) == 2
 
 
-def test_msd_plan_packs_the_varying_bits_in_key_order_and_unit_passes_sort_like_the_keys(lib):
-    # msd_kernels.cuh: (digit, packed low bits) must order the sort words exactly like (hi, lo) does
-    # among words that agree outside the varying bits; the shared-memory passes of a unit, least
-    # significant first and stable, must order (bin, low) numerically
+def test_msd_plan_bins_and_low_words_order_like_the_keys_and_unit_passes_sort_them(lib):
+    # msd_kernels.cuh: (bin, packed low word) must order the sort words exactly like (partition, key
+    # bytes, length) does; the shared-memory passes of a unit, least significant first and stable, must
+    # order (local bin, low) numerically
+    from helpers import sort_word
     rnd = random.Random(17)
-    for trial in range(200):
-        vlo = rnd.getrandbits(64) & rnd.getrandbits(64) if trial % 3 else rnd.getrandbits(64)
-        vhi = rnd.getrandbits(32) & (0xF if trial % 2 else 0xFFFFFF)
-        if trial % 5 == 0:                     # text-like: 5 low bits of each of 7 key bytes, 4 length bits, 4 partition bits
-            vlo = sum(0x1F << (8 * b) for b in range(1, 8)) | 0xF
-            vhi = 0xF
-        n = rnd.choice([1, 2, 50, 200, 5000, 524219, 3_000_000, 1 << 30])
-        fixed_lo, fixed_hi = rnd.getrandbits(64) & ~vlo, rnd.getrandbits(32) & ~vhi
-        words = [(fixed_hi | rnd.getrandbits(32) & vhi, fixed_lo | rnd.getrandbits(64) & vlo) for _ in range(150)]
-        out = (C.c_uint32 * 4)()
+    alphabets = [b"abcdefghijklmnopqrstuvwxyz", b"ab", bytes(range(256)), b"0123456789", b"xyz_./-ABC\x00\xff"]
+    for trial in range(120):
+        alpha = alphabets[trial % len(alphabets)]
+        R = rnd.choice([1, 7, 10, 15, 31, 1000, 1 << 24])
+        nkeys = rnd.choice([1, 2, 40, 300])
+        keys = {bytes(rnd.choice(alpha) for _ in range(rnd.choice([1, 1, 2, 3, 5, 7, 8, 9, 12, 20]))) for _ in range(nkeys)}
+        words = sorted({(rnd.randrange(R), sort_word(k)) for k in keys})
+        occ = (C.c_uint32 * 56)()
+        for _, w in words:
+            for p in range(7):
+                b = (w >> (56 - 8 * p)) & 0xFF
+                occ[p * 8 + (b >> 5)] |= 1 << (b & 31)
+        n = rnd.choice([len(words), 5000, 524219, 3_000_000, 1 << 30])
+        out = (C.c_uint32 * 5)()
         low = C.c_uint64()
         packed = []
         for hi, lo in words:
-            d = lib.th_msd_extract(vlo, vhi, n, hi, lo, C.byref(low), out)
+            d = lib.th_msd_extract(occ, R, n, hi, lo, C.byref(low), out)
             packed.append((d, low.value))
-        D, low_bits, fallback, nruns = list(out)
-        V = bin(vlo).count("1") + bin(vhi).count("1")
-        want_D = 0
-        while want_D < 14 and (64 << want_D) < n:
-            want_D += 1
-        assert D == min(want_D, V) and low_bits == V - D
-        if low_bits > 64:
-            assert fallback & 1
-            continue
+        nbins, k, e, low_bits, fallback = list(out)
+        assert 1 <= nbins <= max(1, min(n // 32, 1 << 15)) and 0 <= k <= 9 and e >= 1
         if fallback:
-            assert nruns == 32                 # more runs than the plan holds: declined, the LSD path takes the job
+            assert low_bits > 64
             continue
-        assert all(d < (1 << D) and l < (1 << low_bits) for d, l in packed)
-        order_words = sorted(range(len(words)), key=lambda i: words[i])
-        order_packed = sorted(range(len(words)), key=lambda i: packed[i])
-        assert [words[i] for i in order_words] == [words[i] for i in order_packed]
-        assert len(set(packed)) == len(set(words))                                   # injective on the varying bits
-        # a unit: consecutive bins, local bin numbers, LSD passes of 8 bits over (local bin : low)
+        assert all(d < nbins and (low_bits == 64 or l < (1 << low_bits)) for d, l in packed)
+        assert packed == sorted(packed) and len(set(packed)) == len(words)          # same order, nothing merged
         dmin = min(d for d, _ in packed)
         items = [(d - dmin, l) for d, l in packed]
-        maxl = max(b for b, _ in items)
-        lbits = maxl.bit_length()
+        rnd.shuffle(items)
+        lbits = max(b for b, _ in items).bit_length()
         npass = (low_bits + lbits + 7) // 8
         order = list(range(len(items)))
         for p in range(npass):
