@@ -991,7 +991,7 @@ int launch_msd(mr_ctx *ctx)
     CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
     ctx->msd_parity ^= 1;
-    msd_hist_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 2), 256, MSD_MAX_BINS * 4, s>>>(
+    msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 8, ctx->sm_count), 256, MSD_MAX_BINS * 4, s>>>(
         ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->rows_st, ctx->rows_tiles);
     msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
         ctx->bufs.item[0], (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb);

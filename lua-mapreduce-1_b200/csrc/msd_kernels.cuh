@@ -40,6 +40,7 @@ constexpr int UNIT_THREADS = 512;
 constexpr int UNIT_WARPS = UNIT_THREADS / 32;
 constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS; // 4
 constexpr uint32_t UNIT_STAGE = UNIT_CAP * INLINE_MAX;
+constexpr uint32_t UNIT_COUNT_SORT_MAX = 192; // bins up to this size are ordered by counting inside the bin
 
 enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 
@@ -121,8 +122,11 @@ __host__ __device__ __forceinline__ uint32_t msd_rank_of(const unsigned int *occ
 }
 
 // bin and packed low word of one sort word (hi = partition, lo = 7 key bytes big-endian << 8 | min(len, 8))
+// lutk (optional): for a plan whose split field k is a key byte, lutk[v] = rank(v) * e / card[k] -- the
+// same value the division gives, looked up
 __host__ __device__ __forceinline__ void msd_extract(const MsdPlan &p, const unsigned char (*lut)[256], uint32_t hi,
-                                                     unsigned long long lo, uint32_t &bin, unsigned long long &low)
+                                                     unsigned long long lo, uint32_t &bin, unsigned long long &low,
+                                                     const unsigned char *lutk = nullptr)
 {
     uint32_t rank[MSD_FIELDS];
     rank[0] = hi;
@@ -135,7 +139,8 @@ __host__ __device__ __forceinline__ void msd_extract(const MsdPlan &p, const uns
     for (int f = 0; f < MSD_FIELDS; ++f) {
         if ((uint32_t)f < p.k) b = b * p.card[f] + rank[f];
         else {
-            if ((uint32_t)f == p.k) b = b * p.e + (uint32_t)(((unsigned long long)rank[f] * p.e) / p.card[f]);
+            if ((uint32_t)f == p.k) b = b * p.e + (lutk && f >= 1 && f <= 7 ? (uint32_t)lutk[(uint32_t)(lo >> (56 - 8 * (f - 1))) & 0xFFu]
+                                                                           : (uint32_t)(((unsigned long long)rank[f] * p.e) / p.card[f]));
             l = (l << p.width[f]) | rank[f];
         }
     }
@@ -164,6 +169,7 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
     __shared__ MsdPlan plan;
     __shared__ unsigned int s_occ[7][8];
     __shared__ unsigned char lut[7][256];
+    __shared__ unsigned char lutk[256];
     unsigned long long n = ctl->n;
     const bool over = n > max_keys;
     if (over) n = max_keys;
@@ -180,7 +186,13 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
     if (threadIdx.x == 0) msd_build_plan(s_occ, num_reducers, n, &plan);
     for (int f = 0; f < 7; ++f) lut[f][threadIdx.x] = (unsigned char)msd_rank_of(s_occ[f], threadIdx.x);   // 256 threads
     __syncthreads();
+    {
+        const uint32_t k = plan.k;
+        lutk[threadIdx.x] = (k >= 1 && k <= 7) ? (unsigned char)(((uint32_t)lut[k - 1][threadIdx.x] * plan.e) / plan.card[k]) : 0;
+    }
+    __syncthreads();
     if (blockIdx.x == 0) {
+        ctl->msd_lutk[threadIdx.x] = lutk[threadIdx.x];
         uint32_t *dst = (uint32_t *)&ctl->msd_plan;
         const uint32_t *src = (const uint32_t *)&plan;
         for (uint32_t i = threadIdx.x; i < sizeof(MsdPlan) / 4; i += blockDim.x) dst[i] = src[i];
@@ -199,7 +211,7 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
         const SortItem it = items[i];
         uint32_t d;
         unsigned long long low;
-        msd_extract(plan, lut, it.hi, it.lo, d, low);
+        msd_extract(plan, lut, it.hi, it.lo, d, low, lutk);
         atomicAdd(&msd_h[d], 1u);
     }
     __syncthreads();
@@ -217,11 +229,13 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
     __shared__ unsigned int s_big;
     __shared__ MsdPlan plan;
     __shared__ unsigned char lut[7][256];
+    __shared__ unsigned char lutk[256];
     if (ctl->msd_fallback) return;
     const unsigned long long n = ctl->n;
     if (n == 0) return;
     for (uint32_t i = threadIdx.x; i < sizeof(MsdPlan) / 4; i += blockDim.x) ((uint32_t *)&plan)[i] = ((const uint32_t *)&ctl->msd_plan)[i];
     for (uint32_t i = threadIdx.x; i < 7 * 256 / 4; i += blockDim.x) ((uint32_t *)&lut[0][0])[i] = ((const uint32_t *)&ctl->msd_lut[0][0])[i];
+    if (threadIdx.x < 64) ((uint32_t *)lutk)[threadIdx.x] = ((const uint32_t *)ctl->msd_lutk)[threadIdx.x];
     if (threadIdx.x == 0) s_big = 0;
     __syncthreads();
     const uint32_t bins = plan.nbins;
@@ -262,7 +276,7 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
         const SortItem it = items[i];
         uint32_t d;
         unsigned long long low;
-        msd_extract(plan, lut, it.hi, it.lo, d, low);
+        msd_extract(plan, lut, it.hi, it.lo, d, low, lutk);
         const uint32_t pos = msd_start[d] + atomicAdd(&mb->cursor[d], 1u);
         MsdItem o;
         o.low = low;
@@ -282,7 +296,7 @@ struct __align__(16) UnitSmem {
     unsigned int wh[UNIT_WARPS];
     unsigned long long wb[UNIT_WARPS];
     unsigned long long prefix_h, prefix_b;
-    unsigned int prefix_part, unit, first, count, dfirst, fallback;
+    unsigned int prefix_part, unit, first, count, dfirst, fallback, maxbin;
 };
 static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned long long) * UNIT_CAP, "counts fit where the warp histograms were");
 
@@ -326,15 +340,26 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         sm.first = bs[ba];
         sm.count = bs[be] - bs[ba];
         sm.dfirst = ba;
+        sm.maxbin = 0;
     }
     __syncthreads();
     const uint32_t first = sm.first, m = sm.count, dfirst = sm.dfirst;   // m < UNIT_CAP (checked by the scatter kernel)
 
-    // ---- load
-    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
-        MsdItem it = in[first + i];
-        it.bin = (it.bin & MSD_FLAG8) | ((it.bin & ~MSD_FLAG8) - dfirst);
-        sm.buf[0][i] = it;
+    // ---- load; every item learns where its bin lies inside the unit
+    unsigned int *ext = &sm.whist[0][0];            // [i] = bin begin | bin size << 16 (free until the passes / the counts)
+    {
+        uint32_t big = 0;
+        for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+            MsdItem it = in[first + i];
+            const uint32_t d = it.bin & ~MSD_FLAG8;
+            const uint32_t b0 = mb->bin_start[d] - first, sz = mb->bin_start[d + 1] - mb->bin_start[d];
+            it.bin = (it.bin & MSD_FLAG8) | (d - dfirst);
+            sm.buf[0][i] = it;
+            ext[i] = b0 | sz << 16;
+            big = max(big, sz);
+        }
+        for (int d = 16; d; d >>= 1) big = max(big, __shfl_xor_sync(0xFFFFFFFFu, big, d));
+        if (lane == 0 && big) atomicMax(&sm.maxbin, big);
     }
     uint32_t maxl = 0;
     if (m) maxl = (in[first + m - 1].bin & ~MSD_FLAG8) - dfirst;           // bins ascend with the position
@@ -343,16 +368,36 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     const uint32_t npass = (low_bits + lbits + 7) / 8;
     __syncthreads();
 
-    // ---- stable LSD passes in shared memory (ranking as in radix_pass_kernel: ballot-built peer masks)
     uint32_t cur = 0;
-    for (uint32_t pass = 0; pass < npass; ++pass) {
+    const bool small_bins = sm.maxbin <= UNIT_COUNT_SORT_MAX;
+    if (small_bins) {
+        // ---- the usual case, bins of a few dozen items: every item counts the items of its own bin
+        // that come before it (smaller low word, or equal and earlier) -- one pass, one barrier
+        for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+            const MsdItem it = sm.buf[0][i];
+            const uint32_t b0 = ext[i] & 0xFFFFu, sz = ext[i] >> 16;
+            uint32_t rank = 0;
+            for (uint32_t j = b0; j < b0 + sz; ++j) {
+                const unsigned long long lj = sm.buf[0][j].low;
+                rank += (lj < it.low || (lj == it.low && j < i)) ? 1u : 0u;
+            }
+            sm.buf[1][b0 + rank] = it;
+        }
+        __syncthreads();
+        cur = 1;
+    }
+    // ---- otherwise: stable LSD passes in shared memory (ranking as in radix_pass_kernel: ballot-built
+    // peer masks); every warp takes an equal share of the items, a multiple of 32
+    const uint32_t blk = ((m + UNIT_WARPS * 32 - 1) / (UNIT_WARPS * 32)) * 32, rounds = blk / 32;
+    for (uint32_t pass = 0; pass < (small_bins ? 0u : npass); ++pass) {
         for (uint32_t i = tid; i < UNIT_WARPS * RADIX_BINS; i += UNIT_THREADS) (&sm.whist[0][0])[i] = 0;
         __syncthreads();
         MsdItem it[UNIT_ITEMS];
         uint32_t dg[UNIT_ITEMS], rk[UNIT_ITEMS];
-        const uint32_t wbase = warp * (32 * UNIT_ITEMS);
+        const uint32_t wbase = warp * blk;
 #pragma unroll
         for (int i = 0; i < UNIT_ITEMS; ++i) {
+            if ((uint32_t)i >= rounds) break;          // warp-uniform
             const uint32_t idx = wbase + i * 32 + lane;
             const bool valid = idx < m;
             if (valid) it[i] = sm.buf[cur][idx];
@@ -398,6 +443,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < UNIT_ITEMS; ++i) {
+            if ((uint32_t)i >= rounds) break;
             const uint32_t idx = wbase + i * 32 + lane;
             if (idx < m) sm.buf[cur ^ 1][sm.bin_excl[dg[i]] + sm.whist[warp][dg[i]] + rk[i]] = it[i];
         }

@@ -79,6 +79,7 @@ struct Ctl {
     unsigned int msd_fallback;       // non-zero: the MSD path declined this job (MSD_FB_* bits)
     unsigned int msd_pad;
     unsigned char msd_lut[7][256];   // rank of a byte value at key byte 0..6
+    unsigned char msd_lutk[256];     // the e-way split of the plan's field k, when that is a key byte
 };
 
 // Dense entries: the occupied slots of the global table copied side by side, 32 bytes each
