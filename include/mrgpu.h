@@ -143,6 +143,19 @@ int mr_map_records(mr_ctx *ctx, uint64_t split_id, const uint32_t *keys, const u
 int mr_map_records_device(mr_ctx *ctx, uint64_t split_id, const uint32_t *dev_keys,
                           const uint32_t *dev_values, uint64_t n);
 
+/* Reduce-side input from run files: what the reduce job reads from the runs other mappers wrote
+ * (job.lua:253-265; each line `return <key>,{<values>}` is one load(line)(), utils.lua:218-230, and
+ * merge_min_keys concatenates the value lists of equal keys, utils.lua:232-247).  n string keys given
+ * as bytes + offsets (key_off[0] = 0, key i = key_bytes[key_off[i] .. key_off[i+1]), 1 byte or more)
+ * and one value per key -- the host reduces a line's value list with the job's reducer before the
+ * call (a sum for MR_REDUCE_SUM_U64).  The pairs are combined into the same table as the text
+ * splits of this job, so GPU-mapped splits and runs written by reference mappers merge in one
+ * mr_reduce_all.  MR_MAP_TOKENIZE_WS contexts, reducers SUM / MIN / MAX; host pointers, borrowed
+ * for the call (it returns after the copy).  n_tokens of the job counts one per pair.  A context
+ * that ingested pairs cannot mr_job_begin(keep_input). */
+int mr_map_pairs(mr_ctx *ctx, uint64_t split_id, const void *key_bytes, const uint64_t *key_off,
+                 const uint64_t *values, uint64_t n);
+
 /* Runs tokenise + hash-combine over every split staged since the last
  * mr_map_finish, then the partitioner on the distinct keys: job.lua:182-215
  * (emit, combiner, partitionfn) for all staged map jobs at once.  Asynchronous. */

@@ -18,7 +18,7 @@ MR_PARTITION_FNV1_LUA52, MR_PARTITION_MOD_U32 = 0, 1
 # every symbol include/mrgpu.h declares
 EXPORTS = (
     "mr_abi_version", "mr_ctx_create", "mr_ctx_destroy", "mr_last_error", "mr_job_begin",
-    "mr_map_split", "mr_map_split_path", "mr_map_split_device", "mr_map_records", "mr_map_records_device", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
+    "mr_map_split", "mr_map_split_path", "mr_map_split_device", "mr_map_records", "mr_map_records_device", "mr_map_pairs", "mr_map_finish", "mr_reduce_all", "mr_job_sync",
     "mr_device_rows_get", "mr_rows_fetch", "mr_reduce_partition", "mr_result_next",
     "mr_result_release", "mr_shuffle_count", "mr_shuffle_pack", "mr_shuffle_recv_buffer", "mr_shuffle_import",
     "mr_shuffle_pack_fixed", "mr_shuffle_import_fixed",
@@ -98,6 +98,7 @@ def load(build_if_missing=True):
     L.mr_map_split_path.argtypes = [vp, u64, C.c_char_p]
     L.mr_map_records.argtypes = [vp, u64, vp, vp, u64]
     L.mr_map_records_device.argtypes = [vp, u64, vp, vp, u64]
+    L.mr_map_pairs.argtypes = [vp, u64, vp, vp, vp, u64]
     L.mr_map_finish.argtypes = [vp]
     L.mr_reduce_all.argtypes = [vp]
     L.mr_job_sync.argtypes = [vp, C.POINTER(JobInfo)]
@@ -205,6 +206,20 @@ class Context:
     def map_records_ptr(self, split_id, keys_ptr, values_ptr, n, device=False):
         fn = self._L.mr_map_records_device if device else self._L.mr_map_records
         self._ck(fn(self._h, split_id, keys_ptr, values_ptr, n))
+
+    def map_pairs(self, split_id, keys, values):
+        """keys: list of bytes (1 byte or more each); values: one integer per key (a run line's value
+        list already reduced by the caller).  mr_map_pairs: the reduce job's read of other mappers' runs."""
+        n = len(keys)
+        assert n == len(values)
+        if not n:
+            return
+        blob = np.frombuffer(b"".join(keys), dtype=np.uint8)
+        off = np.zeros(n + 1, np.uint64)
+        np.cumsum([len(k) for k in keys], out=off[1:])
+        val = np.ascontiguousarray(values, dtype=np.uint64)
+        self._ck(self._L.mr_map_pairs(self._h, split_id, blob.ctypes.data if blob.size else None, off.ctypes.data,
+                                      val.ctypes.data, n))
 
     def map_finish(self):
         self._ck(self._L.mr_map_finish(self._h))

@@ -354,6 +354,7 @@ struct mr_ctx {
     // state
     enum { IDLE, MAPPED, REDUCED, SYNCED } state = IDLE;
     bool map_dirty = false; // splits staged since the last mr_map_finish
+    bool has_pairs = false; // the arena holds mr_map_pairs blobs (not text: the splits cannot be re-mapped)
     mr_job_info info{};
     uint32_t tie_rounds = 0;
     cudaEvent_t ev_map0 = nullptr, ev_map1 = nullptr, ev_red0 = nullptr, ev_red1 = nullptr, ev_gaps = nullptr;
@@ -604,7 +605,10 @@ int mr_job_begin(mr_ctx *ctx, int keep_input)
 {
     if (!ctx) return MR_ERR_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
+    if (keep_input && ctx->has_pairs)
+        return fail(ctx, MR_ERR_UNSUPPORTED, "mr_job_begin: keep_input is not available after mr_map_pairs (the ingested runs are not kept as text)");
     if (!keep_input) {
+        ctx->has_pairs = false;
         ctx->used = 0; ctx->mapped_segs = 0; ctx->input_bytes = 0; ctx->any_split = false;
         ctx->map_dirty = false;
         ctx->ngaps = 0;
@@ -910,6 +914,62 @@ int mr_map_records_device(mr_ctx *ctx, uint64_t split_id, const uint32_t *dev_ke
     return stage_records(ctx, dev_keys, dev_values, n, cudaMemcpyDeviceToDevice);
 }
 
+int mr_map_pairs(mr_ctx *ctx, uint64_t split_id, const void *key_bytes, const uint64_t *key_off, const uint64_t *values,
+                 uint64_t n)
+{
+    (void)split_id;
+    if (!ctx) return MR_ERR_INVALID;
+    if (ctx->cfg.map_kind != MR_MAP_TOKENIZE_WS)
+        return fail(ctx, MR_ERR_UNSUPPORTED, "mr_map_pairs: string-key pairs go with MR_MAP_TOKENIZE_WS contexts (number keys: mr_map_records)");
+    if (ctx->cfg.reduce_kind == MR_REDUCE_COUNT)
+        return fail(ctx, MR_ERR_UNSUPPORTED, "mr_map_pairs: a count is not its own combiner; ingest counted runs with MR_REDUCE_SUM_U64");
+    if (n && (!key_off || !values || (key_off[n] && !key_bytes))) return fail(ctx, MR_ERR_INVALID, "mr_map_pairs: null pointer");
+    if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_pairs: job already reduced; call mr_job_begin");
+    if (!n) return MR_OK;
+    if (key_off[0] != 0) return fail(ctx, MR_ERR_INVALID, "mr_map_pairs: key_off[0] must be 0");
+    CU(cudaSetDevice(ctx->cfg.device));
+    // text staged so far is tokenised first: the blob below must never be read as text
+    { int rc = run_map_round(ctx); if (rc) return rc; }
+    const uint64_t nbytes = key_off[n];
+    const uint64_t at = round_up(std::max<uint64_t>(ctx->used, ctx->mapped_segs * SEG), 16);
+    const uint64_t off_at = at + round_up(nbytes + 16, 16), val_at = off_at + (n + 1) * 8, blob_end = val_at + n * 8;
+    // the blob ends inside a segment whose last byte is a space, so that the tokeniser, when it
+    // later starts at the next segment, does not take that segment's first token for a continuation
+    uint64_t end = round_up(blob_end + 1, SEG);
+    if (end + SEG > ctx->arena_cap)
+        return fail(ctx, MR_ERR_NOMEM, "mr_map_pairs: arena full (%llu > %llu bytes)", (unsigned long long)end,
+                    (unsigned long long)ctx->arena_cap);
+    cudaStream_t s = ctx->stream;
+    if (nbytes) CU(cudaMemcpyAsync(ctx->d_arena + at, key_bytes, nbytes, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(ctx->d_arena + off_at, key_off, (n + 1) * 8, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(ctx->d_arena + val_at, values, n * 8, cudaMemcpyHostToDevice, s));
+    ctx->stats.h2d_bytes += nbytes + (2 * n + 1) * 8;
+    if (at > ctx->used) { int rc = gap_push(ctx, ctx->used, at - ctx->used); if (rc) return rc; }
+    { int rc = gap_push(ctx, blob_end, end - blob_end); if (rc) return rc; }
+    { int rc = flush_gaps(ctx); if (rc) return rc; }
+    PairsParams p;
+    p.arena = ctx->d_arena;
+    p.bytes_at = at; p.off_at = off_at; p.val_at = val_at; p.n = n;
+    p.gtab = ctx->d_gtab;
+    p.gmask = (uint32_t)(ctx->slots - 1);
+    p.op = ctx->cfg.reduce_kind;
+    p.max_key = MR_MAX_TOKEN_BYTES;
+    p.pairs = &ctx->d_ctl->tokens;
+    p.err = &ctx->d_ctl->err;
+    ctx->table_dirty = true;
+    map_pairs_kernel<<<grid_for(n, 256, ctx->sm_count * 8), 256, 0, s>>>(p);
+    ctx->stats.launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(s)); // the host arrays are only borrowed for the call
+    ctx->used = end;
+    ctx->mapped_segs = end / SEG;
+    ctx->input_bytes += nbytes;
+    ctx->any_split = true;
+    ctx->has_pairs = true;
+    return MR_OK;
+}
+
 int mr_map_finish(mr_ctx *ctx)
 {
     if (!ctx) return MR_ERR_INVALID;
@@ -986,15 +1046,14 @@ int launch_msd(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
     static_assert(sizeof(UnitSmem) <= 113 * 1024, "two units per SM");
-    CU(cudaFuncSetAttribute(msd_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MSD_MAX_BINS * 4)));
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
     CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
     ctx->msd_parity ^= 1;
-    msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 8, ctx->sm_count), 256, MSD_MAX_BINS * 4, s>>>(
-        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->rows_st, ctx->rows_tiles);
-    msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
-        ctx->bufs.item[0], (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb);
+    msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 4, ctx->sm_count * 4), 256, 0, s>>>(
+        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles);
+    msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024 * 4, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
+        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
     msd_unit_kernel<<<units, UNIT_THREADS, sizeof(UnitSmem), s>>>(
         (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
@@ -1082,6 +1141,8 @@ int check_device_err(mr_ctx *ctx, unsigned err)
                     P2P_TIMEOUT_NS / 1000000000ull);
     if (err & ERR_LOOKBACK_TIMEOUT)
         return fail(ctx, MR_ERR_CUDA, "a sort or rows tile waited for its predecessors for seconds without progress (look-back gave up)");
+    if (err & ERR_EMPTY_KEY)
+        return fail(ctx, MR_ERR_INVALID, "mr_map_pairs: an empty key (keys have 1 or more bytes)");
     if (err & ERR_KEYS_FULL)
         return fail(ctx, MR_ERR_NOMEM, "more distinct keys (or key bytes) than max_keys=%llu allows",
                     (unsigned long long)ctx->max_keys);

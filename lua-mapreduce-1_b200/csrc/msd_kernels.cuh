@@ -48,10 +48,9 @@ enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 // its own zeroed (the histogram kernel of a job clears the other one)
 struct MsdBins {
     unsigned int hist[MSD_MAX_BINS];
-    unsigned int cursor[MSD_MAX_BINS];
     unsigned int bin_start[MSD_MAX_BINS + 1];
+    unsigned int unit_bin[MSD_MAX_BINS + 2];   // first bin that starts at or after unit * UNIT_W (n < bins * 1024, so units <= bins)
     unsigned int unit_ticket;
-    unsigned int pad[2];
 };
 static_assert(sizeof(MsdBins) % 16 == 0, "MsdBins is cleared 16 bytes at a time");
 
@@ -162,10 +161,13 @@ __host__ __device__ __forceinline__ uint32_t msd_pass_digit(unsigned long long l
 }
 
 // ------------------------------------------------------------------ histogram
+// tag of an item, left by the histogram kernel for the scatter: bin | 8+ bytes flag << 15 | place inside the bin << 16
+constexpr uint32_t MSD_TAG_FLAG8 = 1u << 15;
+
 __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, unsigned long long max_keys, uint32_t num_reducers,
-                                                       Ctl *ctl, MsdBins *mb, MsdBins *mb_next, RowsStatus st, uint32_t st_words)
+                                                       Ctl *ctl, MsdBins *mb, MsdBins *mb_next, uint32_t *tags, RowsStatus st,
+                                                       uint32_t st_words)
 {
-    extern __shared__ unsigned int msd_h[];        // [nbins] (at most MSD_MAX_BINS)
     __shared__ MsdPlan plan;
     __shared__ unsigned int s_occ[7][8];
     __shared__ unsigned char lut[7][256];
@@ -203,39 +205,46 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
         }
     }
     if (plan.fallback || n == 0) return;
-    const uint32_t bins = plan.nbins;
-    for (uint32_t i = threadIdx.x; i < bins; i += blockDim.x) msd_h[i] = 0;
-    __syncthreads();
+    // one atomic per item: counts the bin and tells the item its place inside it (any order will do:
+    // the unit sorts the bin).  Four items per thread in flight.
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const SortItem it = items[i];
-        uint32_t d;
-        unsigned long long low;
-        msd_extract(plan, lut, it.hi, it.lo, d, low, lutk);
-        atomicAdd(&msd_h[d], 1u);
-    }
-    __syncthreads();
-    for (uint32_t i = threadIdx.x; i < bins; i += blockDim.x) {
-        const unsigned int c = msd_h[i];
-        if (c) atomicAdd(&mb->hist[i], c);
+    for (uint64_t i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+        SortItem it[4];
+        uint32_t d[4], r[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint64_t i = i0 + q * stride;
+            if (i < n) it[q] = items[i];
+            else { it[q].lo = 0; it[q].hi = 0; it[q].val = 0; }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            unsigned long long low;
+            msd_extract(plan, lut, it[q].hi, it[q].lo, d[q], low, lutk);
+            r[q] = i0 + q * stride < n ? atomicAdd(&mb->hist[d[q]], 1u) : 0u;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint64_t i = i0 + q * stride;
+            if (i < n) tags[i] = d[q] | ((it[q].lo & 0xFFu) == 8u ? MSD_TAG_FLAG8 : 0u) | min(r[q], 0xFFFFu) << 16;
+        }
     }
 }
 
 // ------------------------------------------------------------------ scatter
-__global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, MsdItem *out, Ctl *ctl, MsdBins *mb)
+__global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, const uint32_t *tags, MsdItem *out, Ctl *ctl,
+                                                           MsdBins *mb)
 {
     extern __shared__ unsigned int msd_start[];    // [bins + 1]
     __shared__ unsigned int wsum[32];
     __shared__ unsigned int s_big;
     __shared__ MsdPlan plan;
     __shared__ unsigned char lut[7][256];
-    __shared__ unsigned char lutk[256];
     if (ctl->msd_fallback) return;
     const unsigned long long n = ctl->n;
     if (n == 0) return;
     for (uint32_t i = threadIdx.x; i < sizeof(MsdPlan) / 4; i += blockDim.x) ((uint32_t *)&plan)[i] = ((const uint32_t *)&ctl->msd_plan)[i];
     for (uint32_t i = threadIdx.x; i < 7 * 256 / 4; i += blockDim.x) ((uint32_t *)&lut[0][0])[i] = ((const uint32_t *)&ctl->msd_lut[0][0])[i];
-    if (threadIdx.x < 64) ((uint32_t *)lutk)[threadIdx.x] = ((const uint32_t *)ctl->msd_lutk)[threadIdx.x];
     if (threadIdx.x == 0) s_big = 0;
     __syncthreads();
     const uint32_t bins = plan.nbins;
@@ -269,20 +278,38 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&ctl->msd_fallback, MSD_FB_BIN);
         return;
     }
-    if (blockIdx.x == 0)
+    if (blockIdx.x == 0) {
         for (uint32_t i = threadIdx.x; i <= bins; i += blockDim.x) mb->bin_start[i] = msd_start[i];
+        // unit u owns the bins from the first one that starts at or after u * UNIT_W: bin b is that
+        // first bin for every u with start[b-1] < u * UNIT_W <= start[b]
+        const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
+        for (uint32_t b = threadIdx.x; b <= bins; b += blockDim.x) {
+            const uint32_t hi = msd_start[b] / UNIT_W;                                  // last u with u * W <= start[b]
+            const uint32_t lo = b == 0 ? 0u : (msd_start[b - 1] + UNIT_W) / UNIT_W;      // first u with u * W > start[b-1] ... (start[b-1] / W) + 1
+            for (uint32_t u = lo; u <= hi && u <= nunits; ++u) mb->unit_bin[u] = b;
+        }
+    }
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const SortItem it = items[i];
-        uint32_t d;
-        unsigned long long low;
-        msd_extract(plan, lut, it.hi, it.lo, d, low, lutk);
-        const uint32_t pos = msd_start[d] + atomicAdd(&mb->cursor[d], 1u);
-        MsdItem o;
-        o.low = low;
-        o.val = it.val;
-        o.bin = d | ((it.lo & 0xFFu) == 8u ? MSD_FLAG8 : 0u);
-        out[pos] = o;
+    for (uint64_t i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+        SortItem it[4];
+        uint32_t tg[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint64_t i = i0 + q * stride;
+            if (i < n) { it[q] = items[i]; tg[q] = tags[i]; }
+            else { it[q].lo = 0; it[q].hi = 0; it[q].val = 0; tg[q] = 0; }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (i0 + q * stride >= n) continue;
+            uint32_t d;
+            MsdItem o;
+            msd_extract(plan, lut, it[q].hi, it[q].lo, d, o.low, nullptr);   // the low word only; the bin travels in the tag
+            d = tg[q] & 0x7FFFu;
+            o.val = it[q].val;
+            o.bin = d | ((tg[q] & MSD_TAG_FLAG8) ? MSD_FLAG8 : 0u);
+            out[msd_start[d] + (tg[q] >> 16)] = o;
+        }
     }
 }
 
@@ -327,18 +354,12 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     if (unit >= nunits) return;
     const uint32_t bins = ctl->msd_plan.nbins, low_bits = ctl->msd_plan.low_bits;
     if (tid == 0) {
-        // bins whose start lies in [unit * W, (unit + 1) * W): lower bounds over the bin starts
-        const unsigned int *bs = mb->bin_start;
-        auto lower = [&](unsigned long long x) {
-            uint32_t lo = 0, hi = bins;              // first b with bs[b] >= x (bs[bins] = n >= x)
-            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (bs[mid] < x) lo = mid + 1; else hi = mid; }
-            return lo;
-        };
-        const uint32_t ba = lower((unsigned long long)unit * UNIT_W);
-        const unsigned long long xe = (unsigned long long)(unit + 1) * UNIT_W;
-        const uint32_t be = xe >= n ? bins : lower(xe);
-        sm.first = bs[ba];
-        sm.count = bs[be] - bs[ba];
+        // bins whose start lies in [unit * W, (unit + 1) * W) (table left by the scatter kernel)
+        const uint32_t ba = mb->unit_bin[unit];
+        const uint32_t be = unit + 1 >= nunits ? bins : mb->unit_bin[unit + 1];
+        const uint32_t s0 = mb->bin_start[ba];
+        sm.first = s0;
+        sm.count = mb->bin_start[be] - s0;
         sm.dfirst = ba;
         sm.maxbin = 0;
     }

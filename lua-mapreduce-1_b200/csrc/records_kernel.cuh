@@ -72,4 +72,61 @@ __global__ void __launch_bounds__(1024, 1) map_records_kernel(RecordsParams p)
     }
 }
 
+// ------------------------------------------------------------------ (key, value) pairs with string keys
+// What a reducer reads from the run files of other mappers (job.lua:253-265: every line of a run is
+// `return <key>,{<values>}`, utils.lua:218-230): n keys as bytes + offsets and one value per key (the
+// host has already reduced a line's value list to one value).  The pairs go into the same global table
+// the tokeniser fills, so text splits and ingested runs of one job merge like runs of different mappers.
+constexpr uint32_t ERR_EMPTY_KEY = 64u;      // joins the ERR_* bits (16 = ERR_PEER_TIMEOUT, 32 = ERR_LOOKBACK_TIMEOUT)
+
+struct PairsParams {
+    const uint8_t *arena;
+    unsigned long long bytes_at, off_at, val_at, n;   // arena offsets of the key bytes, key offsets [n + 1], values [n]
+    GEntry *gtab;
+    uint32_t gmask, op, max_key;
+    unsigned long long *pairs;
+    unsigned int *err;
+};
+
+// hash of a long key of known length: what scan_long_token gives for the same bytes when they hold no
+// whitespace (so that a key met in a text split and in a run file is the same table entry)
+__host__ __device__ inline uint32_t hash_known_len(const uint8_t *bytes, uint64_t off, uint32_t len)
+{
+    uint64_t h = 0xCBF29CE484222325ull;
+    for (uint32_t i = 0; i < len; i += 8) {
+        const uint32_t nb = len - i < 8 ? len - i : 8;
+        h = (h ^ (load8(bytes, off + i) & low_bytes_mask(nb))) * 0x9E3779B97F4A7C15ull;
+        h ^= h >> 32;
+    }
+    h ^= len;
+    h *= 0xD6E8FEB86659FD93ull;
+    return (uint32_t)(h >> 32);
+}
+
+__global__ void __launch_bounds__(256) map_pairs_kernel(PairsParams p)
+{
+    const unsigned long long *off = (const unsigned long long *)(p.arena + p.off_at);
+    const unsigned long long *val = (const unsigned long long *)(p.arena + p.val_at);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    unsigned long long mine = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += stride) {
+        const uint64_t ko = p.bytes_at + off[i];
+        const uint64_t len64 = off[i + 1] - off[i];
+        if (len64 == 0) { atomicOr(p.err, ERR_EMPTY_KEY); continue; }
+        if (len64 > p.max_key) { atomicOr(p.err, ERR_TOKEN_TOO_LONG); continue; }
+        const uint32_t len = (uint32_t)len64;
+        Key key;
+        if (len <= (uint32_t)INLINE_MAX) {
+            key.k0 = load8(p.arena, ko) & low_bytes_mask(len < 8 ? len : 8);
+            key.k1 = (len > 8 ? load8(p.arena, ko + 8) & low_bytes_mask(len - 8) : 0ull) | (unsigned long long)len << 56;
+        } else {
+            key = make_long_key(ko, len, hash_known_len(p.arena, ko, len));
+        }
+        gtable_add(p.gtab, p.gmask, p.arena, key, op_encode(p.op, val[i]), p.err, p.op);
+        ++mine;
+    }
+    for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(p.pairs, mine);
+}
+
 } // namespace mr

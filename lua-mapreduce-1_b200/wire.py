@@ -158,3 +158,67 @@ def read_pairs(directory, names):
             for line in f.read().split(b"\n"):
                 if line:
                     yield parse_line(line)
+
+
+def write_map_results(rows, directory, mapper_key, map_results_ns="map_results"):
+    """What a map job leaves for the reducers (job.lua:196-221): per partition that received a key,
+    one run `<ns>.P<part>.M<mapper_key>`, keys ascending, one line `return <%q key>,{<value>}` per
+    key (the combiner has already folded a key's values into one, job.lua:198-202).
+    rows: _native.Rows of a world-size-1 context that mapped this mapper's splits (its rows ARE the
+    combined map output, sorted by partition and key).  Returns the file names written."""
+    os.makedirs(directory, exist_ok=True)
+    kb = rows.key_bytes.tobytes()
+    names = []
+    for p in range(len(rows.part_begin) - 1):
+        lo, hi = int(rows.part_begin[p]), int(rows.part_begin[p + 1])
+        if hi == lo:
+            continue
+        name = map_result_name(map_results_ns, p, mapper_key)
+        with open(os.path.join(directory, name), "wb") as f:
+            for i in range(lo, hi):
+                f.write(format_line(kb[int(rows.key_off[i]):int(rows.key_off[i + 1])], [int(rows.count[i])]))
+        names.append(name)
+    return names
+
+
+def list_map_results(directory, part, map_results_ns="map_results"):
+    """The runs of one partition (job.lua:253-260: file names matching ^<path>/map_results.P<p>\\..*)."""
+    prefix = "%s.P%d." % (map_results_ns, part)
+    return sorted(n for n in os.listdir(directory) if n.startswith(prefix))
+
+
+def partitions_with_runs(directory, map_results_ns="map_results"):
+    """server_prepare_reduce (server.lua:294-312): the partitions that have at least one run."""
+    pat = re.compile(r"^%s\.P(\d+)\.M.*$" % re.escape(map_results_ns))
+    return sorted({int(m.group(1)) for m in map(pat.match, os.listdir(directory)) if m})
+
+
+def read_run(path):
+    """One run as (key, values) pairs in file order (utils.lua:218-230: load(line)() per line)."""
+    with open(path, "rb") as f:
+        for line in f.read().split(b"\n"):
+            if line:
+                yield parse_line(line)
+
+
+def ingest_runs(ctx, directory, part, map_results_ns="map_results", fold=sum, batch=1 << 16):
+    """Feeds every run of partition `part` to a context through mr_map_pairs: the reduce job's read
+    side (job.lua:253-265).  A line's value list ({1,1,1} from a mapper whose combiner did not run,
+    utils.lua:242-245) is folded with `fold` (sum for the WordCount reducer) before it goes to the
+    device.  Returns (runs read, pairs ingested)."""
+    names = list_map_results(directory, part, map_results_ns)
+    keys, vals, total = [], [], 0
+    for name in names:
+        for key, values in read_run(os.path.join(directory, name)):
+            if not isinstance(key, bytes):
+                raise TypeError("string keys only (number keys go through mr_map_records)")
+            keys.append(key)
+            vals.append(int(fold(values)))
+            if len(keys) >= batch:
+                ctx.map_pairs(total, keys, vals)
+                total += len(keys)
+                keys, vals = [], []
+    if keys:
+        ctx.map_pairs(total, keys, vals)
+        total += len(keys)
+    return len(names), total

@@ -44,3 +44,29 @@ def sort_word(key):
     for i in range(7):
         w = (w << 8) | (key[i] if i < len(key) else 0)
     return (w << 8) | min(len(key), 8)
+
+
+def merge_iterator(runs):
+    """utils.merge_iterator (utils.lua:206-271) restated: `runs` are iterables of (key, values) in
+    ascending key order; a heap holds one line per run ordered by key (utils.lua:214), the smallest is
+    popped and the value lists of all equal keys are concatenated (merge_min_keys, utils.lua:232-247).
+    Yields (key, values) in ascending key order."""
+    import heapq
+    its = [iter(r) for r in runs]
+    heap = []
+    for which, it in enumerate(its):
+        for key, values in it:
+            heapq.heappush(heap, (key, which, list(values)))
+            break
+    while heap:
+        key, which, values = heapq.heappop(heap)
+        for k2, v2 in its[which]:
+            heapq.heappush(heap, (k2, which, list(v2)))
+            break
+        while heap and heap[0][0] == key:
+            _, w2, v2 = heapq.heappop(heap)
+            values += v2
+            for k3, v3 in its[w2]:
+                heapq.heappush(heap, (k3, w2, list(v3)))
+                break
+        yield key, values

@@ -34,3 +34,22 @@ def test_file_names():
     assert wire.result_name("result", 3, 14) == "result.P03" and wire.result_name("result", 3, 9) == "result.P3"
     assert wire.map_result_name("map_results", 12, "4") == "map_results.P12.M4"
     assert sorted(wire.result_name("r", p, 14) for p in (10, 2, 1)) == ["r.P01", "r.P02", "r.P10"]
+
+
+def test_merge_iterator_restatement_gives_the_reference_known_answer(tmp_path):
+    # utils.lua:360-380: f1 = {1:{1,1}, 2:{1}, 3:{1}}, f2 = {1:{1,1,1,1}, 3:{1}, 4:{1}}
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from helpers import merge_iterator
+    f1 = [(1, [1, 1]), (2, [1]), (3, [1])]
+    f2 = [(1, [1, 1, 1, 1]), (3, [1]), (4, [1])]
+    assert list(merge_iterator([f1, f2])) == [(1, [1] * 6), (2, [1]), (3, [1, 1]), (4, [1])]
+    # and through files in the run format
+    for name, run in (("map_results.P0.M1", f1), ("map_results.P0.M2", f2)):
+        with open(tmp_path / name, "wb") as f:
+            for k, v in run:
+                f.write(wire.format_line(k, v))
+    runs = [wire.read_run(str(tmp_path / n)) for n in wire.list_map_results(str(tmp_path), 0)]
+    assert list(merge_iterator(runs)) == [(1, [1] * 6), (2, [1]), (3, [1, 1]), (4, [1])]
+    assert wire.partitions_with_runs(str(tmp_path)) == [0]
