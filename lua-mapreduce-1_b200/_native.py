@@ -76,6 +76,8 @@ def load(build_if_missing=True):
     if _lib is not None:
         return _lib
     path = _build.LIB_GPU
+    if os.environ.get("MRGPU_LIB"):          # a variant build of the same ABI (scripts/map_variants.py)
+        path, build_if_missing = os.environ["MRGPU_LIB"], False
     if build_if_missing:
         try:
             path = _build.build_gpu()

@@ -87,7 +87,11 @@ __device__ __forceinline__ ulonglong2 lds128(uint32_t saddr)
 {
     // one 16-byte shared-memory load of two table keys (other warps update the table concurrently)
     ulonglong2 r;
+#ifdef MRGPU_V_PLAINLDS
+    asm("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "r"(saddr));
+#else
     asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "r"(saddr));
+#endif
     return r;
 }
 
@@ -163,6 +167,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
     unsigned long long *tkeys = (unsigned long long *)smem;
     unsigned int *tcnt = (unsigned int *)(smem + L::keys_bytes);
     __shared__ unsigned int tused;                       // keys held by the CTA table
+#ifdef MRGPU_V_ONEBYTE
+    __shared__ unsigned int c1[256];                     // tokens of one byte: counted by their byte value, no key, no probe
+    for (uint32_t i = threadIdx.x; i < 256; i += WARPS * 32) c1[i] = 0;
+#endif
     constexpr uint32_t FILL_LIMIT = SLOTS - SLOTS / 8;   // stop trying to insert at 87.5 % load
     const uint32_t tkeys_s = (uint32_t)__cvta_generic_to_shared(tkeys);
 
@@ -204,6 +212,27 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         pending = true;
         __syncwarp();
     };
+#ifdef MRGPU_V_DIRECTMED
+    // a full batch of 32 keys goes from registers straight into flight (no trip through the queue)
+    auto drain_direct = [&](const Key &nk) {
+        if (pending) {
+            bool again = !probe_try(p, pkey, pslot, pv);
+            if (again && (pkey.k1 >> 60) == 15) {
+                Key k = pkey;
+                k.k1 &= ~QDIST_MASK;
+                gtable_add(p.gtab, p.gmask, p.arena, k, 1, p.err);
+                again = false;
+            }
+            const uint32_t am = __ballot_sync(0xFFFFFFFFu, again);
+            if (again) *(ulonglong2 *)&ws->gq[nq + __popc(am & lt)] = make_ulonglong2(pkey.k0, pkey.k1 + (1ull << 60));
+            nq += __popc(am);
+        }
+        pkey = nk;
+        probe_issue(p, pkey, pslot, pv);
+        pending = true;
+        __syncwarp();
+    };
+#endif
     unsigned long long my_tokens = 0;
     const uint64_t gwarp = (uint64_t)blockIdx.x * WARPS + warp, nwarps = (uint64_t)gridDim.x * WARPS;
     MT_DECL;
@@ -245,7 +274,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         const TokenMasks tm = token_masks(m, nxt, carry);
         const unsigned long long w = tm.w;
         const uint32_t starts = tm.starts, s_long = tm.s_long, s_med = tm.s_med, s_short = tm.s_short;
+#ifdef MRGPU_V_ONEBYTE
+        const uint32_t s_one = s_short & ~(uint32_t)(w >> 1);      // a token byte followed by a non-token byte
+        const uint32_t s_sh2 = s_short & ~s_one;
+        const uint32_t packed = __popc(s_sh2) | (__popc(s_med) << 10) | (__popc(s_one) << 20);
+#else
         const uint32_t packed = __popc(s_short) | (__popc(s_med) << 16);
+#endif
         uint32_t incl = packed;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -253,6 +288,22 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             if (lane >= d) incl += v;
         }
         const uint32_t totals = __shfl_sync(0xFFFFFFFFu, incl, 31);
+#ifdef MRGPU_V_ONEBYTE
+        const uint32_t n_short = totals & 0x3FFu, n_med = (totals >> 10) & 0x3FFu, n_one = totals >> 20;
+        uint32_t o_s = (incl - packed) & 0x3FFu;
+        uint32_t o_m = LIST_LAST - (((incl - packed) >> 10) & 0x3FFu);
+        uint32_t o_1 = n_short + ((incl - packed) >> 20);          // the one-byte tokens follow the short ones in the list
+        uint32_t st = starts & ~s_long;
+        while (st) {
+            const uint32_t bit = __ffs((int)st) - 1;
+            st &= st - 1;
+            const uint32_t len = token_len(w, bit); // 1..15
+            const uint16_t e = (uint16_t)((lane * 32 + bit) | (len << 10));
+            if ((s_med >> bit) & 1u) ws->list[o_m--] = e;
+            else if (len == 1) ws->list[o_1++] = e;
+            else ws->list[o_s++] = e;
+        }
+#else
         const uint32_t n_short = totals & 0xFFFFu, n_med = totals >> 16;
         uint32_t o_s = (incl - packed) & 0xFFFFu;
         uint32_t o_m = LIST_LAST - ((incl - packed) >> 16);
@@ -265,6 +316,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             if ((s_med >> bit) & 1u) ws->list[o_m--] = e;
             else ws->list[o_s++] = e;
         }
+#endif
         my_tokens += __popc(starts);
         // tokens of 16+ bytes (rare): queue their arena offsets
         uint32_t lb = __ballot_sync(0xFFFFFFFFu, s_long != 0);
@@ -329,9 +381,29 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             MT(2); // short tokens: key + CTA table
             if (nq >= 32) { drain32(); while (nq >= 64) drain32(); MT(4); }
         }
+#ifdef MRGPU_V_ONEBYTE
+        // ---- 3a'. tokens of one byte: the byte value is the counter index
+        for (uint32_t t0 = 0; t0 < n_one; t0 += 32) {
+            const uint32_t j = t0 + lane;
+            if (j < n_one) {
+                const uint32_t pos = ws->list[n_short + j] & 1023u;
+                atomicAdd(&c1[((const uint8_t *)ws->stage)[pos]], 1u);
+            }
+        }
+#endif
         // ---- 3b. medium tokens (8..15 bytes): 128-bit inline key, straight to the global queue
         for (uint32_t t0 = 0; t0 < n_med; t0 += 32) {
             const uint32_t j = t0 + lane;
+#ifdef MRGPU_V_DIRECTMED
+            if (n_med - t0 >= 32 && nq < 64) {
+                const uint32_t e = ws->list[LIST_LAST - j];
+                const uint32_t pos = e & 1023u, len = e >> 10;
+                const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
+                const Key key = medium_key(ws->stage[wi], ws->stage[wi + 1], ws->stage[wi + 2], ws->stage[wi + 3], ws->stage[wi + 4], bs, len);
+                drain_direct(key);
+                continue;
+            }
+#endif
             if (j < n_med) {
                 const uint32_t e = ws->list[LIST_LAST - j];
                 const uint32_t pos = e & 1023u, len = e >> 10;
@@ -361,6 +433,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
     for (int d = 16; d; d >>= 1) my_tokens += __shfl_xor_sync(0xFFFFFFFFu, my_tokens, d);
     if (lane == 0 && my_tokens) atomicAdd(p.tokens, my_tokens);
     __syncthreads();
+#ifdef MRGPU_V_ONEBYTE
+    for (uint32_t i = tid; i < 256; i += WARPS * 32)
+        if (c1[i]) {
+            Key k;
+            k.k0 = i;
+            k.k1 = 1ull << 56;
+            gtable_add(p.gtab, p.gmask, p.arena, k, c1[i], p.err);
+        }
+#endif
     // flush the CTA table
     for (uint32_t i = tid; i < SLOTS; i += WARPS * 32) {
         const unsigned long long sk = tkeys[i];

@@ -1329,7 +1329,7 @@ int mr_result_next(mr_result *res, const char **key, uint64_t *klen, uint64_t *c
 
 void mr_result_release(mr_result *res) { delete res; }
 
-#if defined(MRGPU_SORT_TIMING) || defined(MRGPU_MAP_TIMING)
+#if defined(MRGPU_SORT_TIMING) || defined(MRGPU_MAP_TIMING) || defined(MRGPU_UNIT_TIMING)
 extern "C" const long long *mr_debug_stamps(mr_ctx *ctx) { return ctx->h_ctl->dbg; }
 #endif
 

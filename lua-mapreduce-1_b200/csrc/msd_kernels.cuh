@@ -327,6 +327,14 @@ struct __align__(16) UnitSmem {
 };
 static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned long long) * UNIT_CAP, "counts fit where the warp histograms were");
 
+#ifdef MRGPU_UNIT_TIMING   // build with -DMRGPU_UNIT_TIMING=<unit>: globaltimer stamps of that unit's phases in Ctl::dbg
+#define UT(k) do { if (threadIdx.x == 0 && sm.unit == (MRGPU_UNIT_TIMING)) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); ctl->dbg[k] = (long long)t_; } } while (0)
+#define UT0 do { if (threadIdx.x == 0 && sm.unit == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); ctl->dbg[15] = (long long)t_; } } while (0)
+#else
+#define UT(k) do { } while (0)
+#define UT0 do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
                                                                 RowArrays rows, uint32_t num_reducers, uint32_t op,
                                                                 unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl,
@@ -342,6 +350,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     }
     __syncthreads();
     const uint32_t unit = sm.unit;
+    UT0; UT(0);
     if (sm.fallback) return;
     if (n == 0) {
         if (unit == 0) {
@@ -365,6 +374,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     }
     __syncthreads();
     const uint32_t first = sm.first, m = sm.count, dfirst = sm.dfirst;   // m < UNIT_CAP (checked by the scatter kernel)
+    UT(1);
 
     // ---- load; every item learns where its bin lies inside the unit
     unsigned int *ext = &sm.whist[0][0];            // [i] = bin begin | bin size << 16 (free until the passes / the counts)
@@ -388,6 +398,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     while (lbits < 32 && (1u << lbits) <= maxl) ++lbits;
     const uint32_t npass = (low_bits + lbits + 7) / 8;
     __syncthreads();
+    UT(2);
 
     uint32_t cur = 0;
     const bool small_bins = sm.maxbin <= UNIT_COUNT_SORT_MAX;
@@ -472,6 +483,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         cur ^= 1;
     }
     MsdItem *sorted = sm.buf[cur];
+    UT(3);
     ulonglong2 *skey = (ulonglong2 *)sm.buf[cur ^ 1];       // (k0, k1) of sorted[i], filled below
     unsigned long long *scnt = (unsigned long long *)&sm.whist[0][0];
 
@@ -501,6 +513,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     // a unit that declined still takes part in the look-back below (with nothing), so that no later
     // unit waits for it; the rows are rewritten by the LSD path anyway
     const bool declined = sm.fallback != 0;
+    UT(4);
 
     // ---- entries of the sorted items (one 32-byte gather each), heads, row and byte counts
     const uint32_t base = tid * UNIT_ITEMS;
@@ -520,6 +533,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         }
     }
     __syncthreads();
+    UT(5);
     uint32_t headmask = 0, nh = 0;
     unsigned long long nb = 0;
 #pragma unroll
@@ -550,6 +564,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         if (w < (int)warp) { oh += sm.wh[w]; ob += sm.wb[w]; }
         th += sm.wh[w]; tb += sm.wb[w];
     }
+    UT(6);
     // ---- look-back over units: rows before, key bytes before, partition of the last row before.
     // heads word: flag << 62 | (last partition + 1) << 32 | rows; 0 in the partition field = no row
     constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62;
@@ -594,6 +609,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     }
     __syncthreads();
     if (declined) return;
+    UT(7);
     unsigned long long o = sm.prefix_h + oh, boff = sm.prefix_b + ob;
     const unsigned long long unit_b0 = sm.prefix_b;
     const bool overflow = unit_b0 + tb > key_bytes_cap;
@@ -651,6 +667,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     }
     if (staged) {
         __syncthreads();
+        UT(8);
         uint8_t *dst = rows.key_bytes + (unit_b0 - mis);
         const uint32_t end = mis + (uint32_t)tb;
         for (uint32_t cb = tid * 16; cb < end; cb += UNIT_THREADS * 16) {
@@ -661,6 +678,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
             }
         }
     }
+    UT(9);
 }
 
 } // namespace mr
