@@ -129,13 +129,34 @@ __device__ __forceinline__ void probe_issue(const MapParams &p, const Key &qkey,
     v = __ldcg((const ulonglong2 *)&p.gtab[slot]);
 }
 
-// returns true when the key has been counted
-__device__ __forceinline__ bool probe_try(const MapParams &p, const Key &qkey, uint32_t slot, ulonglong2 v)
+#ifdef MRGPU_V_ASYNCCLAIM
+// an empty slot is claimed WITHOUT waiting for the compare-and-swap's answer (a round trip to L2 with the
+// whole warp stalled): the key is probed again at the same slot on the next round, where it finds
+// itself or the key that won the race
+__device__ __forceinline__ void cas128_noret(GEntry *slot, const Key &desired)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .b128 cmp, des, res;\n\t"
+        "mov.b128 cmp, {%0, %1};\n\t"
+        "mov.b128 des, {%2, %3};\n\t"
+        "atom.global.cas.b128 res, [%4], cmp, des;\n\t"
+        "}\n"
+        :: "l"(0ull), "l"(0ull), "l"(desired.k0), "l"(desired.k1), "l"(slot)
+        : "memory");
+}
+#endif
+
+// returns true when the key has been counted; *same_slot (optional): probe this slot again
+__device__ __forceinline__ bool probe_try(const MapParams &p, const Key &qkey, uint32_t slot, ulonglong2 v, bool *same_slot = nullptr)
 {
     Key key = qkey, cur;
     key.k1 &= ~QDIST_MASK;
     cur.k0 = v.x; cur.k1 = v.y;
     if (cur.k1 == 0) {
+#ifdef MRGPU_V_ASYNCCLAIM
+        if (same_slot) { cas128_noret(&p.gtab[slot], key); *same_slot = true; return false; }
+#endif
         cur = cas128(&p.gtab[slot], key);
         if (cur.k1 == 0) cur = key; // the slot is ours
     }
@@ -196,15 +217,16 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         const ulonglong2 kv = *(const ulonglong2 *)&ws->gq[nq + lane];
         __syncwarp();
         if (pending) {
-            bool again = !probe_try(p, pkey, pslot, pv);
-            if (again && (pkey.k1 >> 60) == 15) { // very long probe chain: finish it synchronously
+            bool same = false;
+            bool again = !probe_try(p, pkey, pslot, pv, &same);
+            if (again && !same && (pkey.k1 >> 60) == 15) { // very long probe chain: finish it synchronously
                 Key k = pkey;
                 k.k1 &= ~QDIST_MASK;
                 gtable_add(p.gtab, p.gmask, p.arena, k, 1, p.err);
                 again = false;
             }
             const uint32_t am = __ballot_sync(0xFFFFFFFFu, again);
-            if (again) *(ulonglong2 *)&ws->gq[nq + __popc(am & lt)] = make_ulonglong2(pkey.k0, pkey.k1 + (1ull << 60));
+            if (again) *(ulonglong2 *)&ws->gq[nq + __popc(am & lt)] = make_ulonglong2(pkey.k0, pkey.k1 + (same ? 0ull : 1ull << 60));
             nq += __popc(am);
         }
         pkey.k0 = kv.x; pkey.k1 = kv.y;

@@ -1045,7 +1045,7 @@ int launch_sort(mr_ctx *ctx)
 int launch_msd(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
-    static_assert(sizeof(UnitSmem) <= 113 * 1024, "two units per SM");
+    static_assert(sizeof(UnitSmem) <= 55 * 1024, "four units per SM");
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
     CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);

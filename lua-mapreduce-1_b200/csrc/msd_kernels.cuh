@@ -9,12 +9,12 @@
 //   msd_hist_kernel     the sort word (partition, 7 key bytes, min(len, 8)) is read as 9 fields; every
 //                       key byte is replaced by its rank among the byte values that occur at its
 //                       position (dense codes whatever the alphabet), and the bin of an item is the
-//                       mixed-radix number of its leading fields, refined until a bin holds ~64 items
+//                       mixed-radix number of its leading fields, refined until a bin holds ~8 items
 //                       (at most 2^15 bins): one histogram over all items.
 //   msd_scatter_kernel  bin starts (every CTA scans the histogram for itself), then every item goes to
 //                       its bin as {packed low bits, entry index, bin}: items of one bin lie together,
 //                       bins in key order.
-//   msd_unit_kernel     units of consecutive whole bins (about 1024 items, never more than 2048) are
+//   msd_unit_kernel     units of consecutive whole bins (about 512 items, never more than 1024) are
 //                       sorted in SHARED memory (stable LSD passes on the packed low bits and the bin
 //                       number), keys that agree in their first 7 bytes are ordered by their later
 //                       bytes, equal keys (the same key from several ranks) are merged, and the rows --
@@ -33,13 +33,13 @@ namespace mr {
 
 constexpr int MSD_MAX_BITS = 15;
 constexpr uint32_t MSD_MAX_BINS = 1u << MSD_MAX_BITS;
-constexpr uint32_t MSD_TARGET_BIN = 32;      // items per bin aimed at (a bin may hold up to UNIT_CAP - UNIT_W: room for 32x skew)
-constexpr uint32_t UNIT_W = 1024;            // a unit owns the bins that start inside its 1024 positions
-constexpr uint32_t UNIT_CAP = 2048;          // ... so it holds fewer than UNIT_W + largest bin items
-constexpr int UNIT_THREADS = 512;
+constexpr uint32_t MSD_TARGET_BIN = 8;       // items per bin aimed at (a bin may hold up to UNIT_CAP - UNIT_W: room for 64x skew)
+constexpr uint32_t UNIT_W = 512;             // a unit owns the bins that start inside its 512 positions
+constexpr uint32_t UNIT_CAP = 1024;          // ... so it holds fewer than UNIT_W + largest bin items
+constexpr int UNIT_THREADS = 256;
 constexpr int UNIT_WARPS = UNIT_THREADS / 32;
 constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS; // 4
-constexpr uint32_t UNIT_STAGE = UNIT_CAP * INLINE_MAX;
+constexpr uint32_t UNIT_STAGE = 12 * 1024 - 16;   // key bytes of a unit staged for coalesced stores (more: written directly)
 constexpr uint32_t UNIT_COUNT_SORT_MAX = 192; // bins up to this size are ordered by counting inside the bin
 
 enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
@@ -49,7 +49,7 @@ enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 struct MsdBins {
     unsigned int hist[MSD_MAX_BINS];
     unsigned int bin_start[MSD_MAX_BINS + 1];
-    unsigned int unit_bin[MSD_MAX_BINS + 2];   // first bin that starts at or after unit * UNIT_W (n < bins * 1024, so units <= bins)
+    unsigned int unit_bin[MSD_MAX_BINS + 2];   // first bin that starts at or after unit * UNIT_W (n <= bins * UNIT_W when no bin is too large, so units <= bins)
     unsigned int unit_ticket;
 };
 static_assert(sizeof(MsdBins) % 16 == 0, "MsdBins is cleared 16 bytes at a time");
@@ -566,44 +566,57 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     }
     UT(6);
     // ---- look-back over units: rows before, key bytes before, partition of the last row before.
-    // heads word: flag << 62 | (last partition + 1) << 32 | rows; 0 in the partition field = no row
-    constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62;
+    // Two self-validating words per unit, each led by the same 2-bit state (1 aggregate, 2 inclusive):
+    //   A = state << 62 | (last partition + 1) << 32 | rows      (0 in the partition field = no row)
+    //   B = state << 62 | key bytes
+    // A reader takes a pair only when both states agree, so no fence orders the two stores; 128
+    // predecessors are read per round trip.
+    constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62, F_VAL = (1ull << 62) - 1;
     const unsigned long long my_last = (m && !declined) ? (unsigned long long)(ent.part(sorted[m - 1].val) + 1u) : 0ull;
     if (warp == 0) {
-        volatile unsigned long long *vheads = st.heads, *vagg = st.bytes_agg, *vinc = st.bytes_inc;
+        volatile unsigned long long *vA = st.heads, *vB = st.bytes_agg;
         unsigned long long ph = 0, pb = 0, pl = 0;
         if (unit == 0) {
-            if (lane == 0) { vinc[0] = tb; __threadfence(); vheads[0] = F_INC | my_last << 32 | th; }
+            if (lane == 0) { vB[0] = F_INC | tb; vA[0] = F_INC | my_last << 32 | th; }
         } else {
-            if (lane == 0) { vagg[unit] = tb; __threadfence(); vheads[unit] = F_AGG | my_last << 32 | th; }
+            if (lane == 0) { vB[unit] = F_AGG | tb; vA[unit] = F_AGG | my_last << 32 | th; }
             int t = (int)unit - 1;
-            for (uint32_t polls = 0;; ++polls) {
+            bool done = false;
+            for (uint32_t polls = 0; !done; ++polls) {
                 if (polls > LOOKBACK_SPIN_LIMIT) { if (lane == 0) atomicOr(&ctl->err, ERR_LOOKBACK_TIMEOUT); break; }
-                const int idx = t - (int)lane;
-                const unsigned long long w = idx >= 0 ? vheads[idx] : F_INC;
-                const uint32_t flag = (uint32_t)(w >> 62);
-                const uint32_t notready = __ballot_sync(0xFFFFFFFFu, flag == 0);
-                const uint32_t incm = __ballot_sync(0xFFFFFFFFu, flag == 2);
-                const uint32_t stop = incm ? (uint32_t)__ffs((int)incm) - 1u : 31u;
-                const uint32_t use = stop == 31 ? 0xFFFFFFFFu : ((2u << stop) - 1u);
-                if (notready & use) continue;
-                __threadfence();
-                unsigned long long b = 0, h = 0, l = 0;
-                if ((use >> lane) & 1u) {
-                    h = w & 0xFFFFFFFFull;
-                    l = (w >> 32) & 0x3FFFFFFFull;
-                    if (idx >= 0) b = flag == 2 ? vinc[idx] : vagg[idx];
+                unsigned long long wa[4], wb[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int idx = t - q * 32 - (int)lane;
+                    wa[q] = idx >= 0 ? vA[idx] : F_INC;
+                    wb[q] = idx >= 0 ? vB[idx] : F_INC;
                 }
-                for (int d = 16; d; d >>= 1) {
-                    h += __shfl_xor_sync(0xFFFFFFFFu, h, d);
-                    b += __shfl_xor_sync(0xFFFFFFFFu, b, d);
-                    l = max(l, __shfl_xor_sync(0xFFFFFFFFu, l, d));   // partitions ascend with the units
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t fa = (uint32_t)(wa[q] >> 62), fb = (uint32_t)(wb[q] >> 62);
+                    const bool ok = fa == fb && fa != 0;
+                    const uint32_t notready = __ballot_sync(0xFFFFFFFFu, !ok);
+                    const uint32_t incm = __ballot_sync(0xFFFFFFFFu, ok && fa == 2);
+                    const uint32_t stop = incm ? (uint32_t)__ffs((int)incm) - 1u : 31u;
+                    const uint32_t use = stop == 31 ? 0xFFFFFFFFu : ((2u << stop) - 1u);
+                    if (notready & use) break;                 // a needed predecessor has not published: read again from here
+                    unsigned long long bb = 0, h = 0, l = 0;
+                    if ((use >> lane) & 1u) {
+                        h = wa[q] & 0xFFFFFFFFull;
+                        l = (wa[q] >> 32) & 0x3FFFFFFFull;
+                        bb = wb[q] & F_VAL;
+                    }
+                    for (int d = 16; d; d >>= 1) {
+                        h += __shfl_xor_sync(0xFFFFFFFFu, h, d);
+                        bb += __shfl_xor_sync(0xFFFFFFFFu, bb, d);
+                        l = max(l, __shfl_xor_sync(0xFFFFFFFFu, l, d));   // partitions ascend with the units
+                    }
+                    ph += h; pb += bb; pl = max(pl, l);
+                    if (incm) { done = true; break; }
+                    t -= 32;
                 }
-                ph += h; pb += b; pl = max(pl, l);
-                if (incm) break;
-                t -= 32;
             }
-            if (lane == 0) { vinc[unit] = pb + tb; __threadfence(); vheads[unit] = F_INC | max(pl, my_last) << 32 | (ph + th); }
+            if (lane == 0) { vB[unit] = F_INC | (pb + tb); vA[unit] = F_INC | max(pl, my_last) << 32 | (ph + th); }
         }
         if (lane == 0) { sm.prefix_h = ph; sm.prefix_b = pb; sm.prefix_part = (unsigned int)pl; }
     }

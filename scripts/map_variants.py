@@ -16,6 +16,7 @@ VARIANTS = {
     "onebyte": ["-DMRGPU_V_ONEBYTE"],
     "directmed": ["-DMRGPU_V_DIRECTMED"],
     "all3": ["-DMRGPU_V_PLAINLDS", "-DMRGPU_V_ONEBYTE", "-DMRGPU_V_DIRECTMED"],
+    "asyncclaim": ["-DMRGPU_V_ASYNCCLAIM"],
 }
 
 

@@ -291,7 +291,7 @@ def test_msd_plan_bins_and_low_words_order_like_the_keys_and_unit_passes_sort_th
             d = lib.th_msd_extract(occ, R, n, hi, lo, C.byref(low), out)
             packed.append((d, low.value))
         nbins, k, e, low_bits, fallback = list(out)
-        assert 1 <= nbins <= max(1, min(n // 32, 1 << 15)) and 0 <= k <= 9 and e >= 1
+        assert 1 <= nbins <= max(1, min(n // 8, 1 << 15)) and 0 <= k <= 9 and e >= 1
         if fallback:
             assert low_bits > 64
             continue
