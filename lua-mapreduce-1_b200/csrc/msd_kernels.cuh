@@ -278,12 +278,13 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&ctl->msd_fallback, MSD_FB_BIN);
         return;
     }
-    if (blockIdx.x == 0) {
-        for (uint32_t i = threadIdx.x; i <= bins; i += blockDim.x) mb->bin_start[i] = msd_start[i];
+    {
+        const uint32_t g0 = blockIdx.x * blockDim.x + threadIdx.x, gs = gridDim.x * blockDim.x;
+        for (uint32_t i = g0; i <= bins; i += gs) mb->bin_start[i] = msd_start[i];
         // unit u owns the bins from the first one that starts at or after u * UNIT_W: bin b is that
         // first bin for every u with start[b-1] < u * UNIT_W <= start[b]
         const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
-        for (uint32_t b = threadIdx.x; b <= bins; b += blockDim.x) {
+        for (uint32_t b = g0; b <= bins; b += gs) {
             const uint32_t hi = msd_start[b] / UNIT_W;                                  // last u with u * W <= start[b]
             const uint32_t lo = b == 0 ? 0u : (msd_start[b - 1] + UNIT_W) / UNIT_W;      // first u with u * W > start[b-1] ... (start[b-1] / W) + 1
             for (uint32_t u = lo; u <= hi && u <= nunits; ++u) mb->unit_bin[u] = b;
@@ -319,7 +320,7 @@ struct __align__(16) UnitSmem {
     unsigned int whist[UNIT_WARPS][RADIX_BINS];  // 16 KB: per-warp digit counts; afterwards the counts of the items
     unsigned int bin_excl[RADIX_BINS];
     unsigned int scan_tmp[RADIX_BINS / 32];
-    uint8_t stage[UNIT_STAGE + 16];              // key bytes of the unit's rows, in the destination's alignment
+    uint8_t stage[UNIT_STAGE + 16];              // key bytes of the unit's rows, back to back from offset 0
     unsigned int wh[UNIT_WARPS];
     unsigned long long wb[UNIT_WARPS];
     unsigned long long prefix_h, prefix_b;
@@ -335,7 +336,7 @@ static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned 
 #define UT0 do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
+__global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
                                                                 RowArrays rows, uint32_t num_reducers, uint32_t op,
                                                                 unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl,
                                                                 MsdBins *mb)
@@ -405,13 +406,29 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     if (small_bins) {
         // ---- the usual case, bins of a few dozen items: every item counts the items of its own bin
         // that come before it (smaller low word, or equal and earlier) -- one pass, one barrier
+        const bool narrow = low_bits <= 32;            // (the usual case: the bin already fixes the leading fields)
         for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
             const MsdItem it = sm.buf[0][i];
             const uint32_t b0 = ext[i] & 0xFFFFu, sz = ext[i] >> 16;
             uint32_t rank = 0;
-            for (uint32_t j = b0; j < b0 + sz; ++j) {
-                const unsigned long long lj = sm.buf[0][j].low;
-                rank += (lj < it.low || (lj == it.low && j < i)) ? 1u : 0u;
+            if (narrow) {
+                const uint32_t mine = (uint32_t)it.low;
+                const uint32_t *lo32 = (const uint32_t *)&sm.buf[0][0];   // low word of item j at [4 * j]
+                uint32_t j = b0;
+                for (; j + 4 <= b0 + sz; j += 4) {
+                    const uint32_t l0 = lo32[4 * j], l1 = lo32[4 * j + 4], l2 = lo32[4 * j + 8], l3 = lo32[4 * j + 12];
+                    rank += (l0 < mine || (l0 == mine && j < i)) + (l1 < mine || (l1 == mine && j + 1 < i)) +
+                            (l2 < mine || (l2 == mine && j + 2 < i)) + (l3 < mine || (l3 == mine && j + 3 < i));
+                }
+                for (; j < b0 + sz; ++j) {
+                    const uint32_t lj = lo32[4 * j];
+                    rank += (lj < mine || (lj == mine && j < i)) ? 1u : 0u;
+                }
+            } else {
+                for (uint32_t j = b0; j < b0 + sz; ++j) {
+                    const unsigned long long lj = sm.buf[0][j].low;
+                    rank += (lj < it.low || (lj == it.low && j < i)) ? 1u : 0u;
+                }
             }
             sm.buf[1][b0 + rank] = it;
         }
@@ -530,22 +547,38 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
             len[j] = key_len(key[j]);
             skey[i] = make_ulonglong2(e.x, e.y);
             scnt[i] = e.z;
+            sorted[i].val = part[j];        // the entry index has done its work: the slot now holds the partition
         }
     }
     __syncthreads();
     UT(5);
+    // heads, and for every head the merged value of the equal keys that follow it (the same key from
+    // other ranks: merge_min_keys, utils.lua:232-247, with the job's reducer)
     uint32_t headmask = 0, nh = 0;
     unsigned long long nb = 0;
+    unsigned long long cval[UNIT_ITEMS];
 #pragma unroll
     for (int j = 0; j < UNIT_ITEMS; ++j) {
         const uint32_t i = base + j;
+        cval[j] = 0;
         if (i >= m || declined) continue;
         bool head = i == 0 || !same_word(i, i - 1);   // the first item of a unit starts a bin: always a new key
         if (!head && (sorted[i].bin & MSD_FLAG8)) {
             Key pk; pk.k0 = skey[i - 1].x; pk.k1 = skey[i - 1].y;
             head = !same_key(key[j], pk, bytes);
         }
-        if (head) { headmask |= 1u << j; ++nh; nb += len[j]; }
+        if (!head) continue;
+        headmask |= 1u << j; ++nh; nb += len[j];
+        unsigned long long c = scnt[i];
+        for (uint32_t q = i + 1; q < m; ++q) {
+            if (!same_word(q, i)) break;
+            if (sorted[q].bin & MSD_FLAG8) {
+                Key a; a.k0 = skey[q].x; a.k1 = skey[q].y;
+                if (!same_key(a, key[j], bytes)) break;
+            }
+            c = (op == OP_SUM || op == OP_COUNT) ? c + scnt[q] : max(c, scnt[q]);
+        }
+        cval[j] = c;
     }
     uint32_t ih = nh;
     unsigned long long ib = nb;
@@ -564,6 +597,15 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         if (w < (int)warp) { oh += sm.wh[w]; ob += sm.wb[w]; }
         th += sm.wh[w]; tb += sm.wb[w];
     }
+    // the unit's key bytes are laid out in shared memory now (offsets inside the unit are known; where the
+    // unit starts in the output is not yet), so that this work overlaps the wait for the units before
+    const bool staged = !declined && tb <= UNIT_STAGE;
+    if (staged) {
+        unsigned long long lb = ob;
+#pragma unroll
+        for (int j = 0; j < UNIT_ITEMS; ++j)
+            if ((headmask >> j) & 1u) { write_key_bytes(sm.stage + (uint32_t)lb, key[j], len[j], bytes); lb += len[j]; }
+    }
     UT(6);
     // ---- look-back over units: rows before, key bytes before, partition of the last row before.
     // Two self-validating words per unit, each led by the same 2-bit state (1 aggregate, 2 inclusive):
@@ -572,7 +614,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     // A reader takes a pair only when both states agree, so no fence orders the two stores; 128
     // predecessors are read per round trip.
     constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62, F_VAL = (1ull << 62) - 1;
-    const unsigned long long my_last = (m && !declined) ? (unsigned long long)(ent.part(sorted[m - 1].val) + 1u) : 0ull;
+    const unsigned long long my_last = (m && !declined) ? (unsigned long long)(sorted[m - 1].val + 1u) : 0ull;
     if (warp == 0) {
         volatile unsigned long long *vA = st.heads, *vB = st.bytes_agg;
         unsigned long long ph = 0, pb = 0, pl = 0;
@@ -627,29 +669,16 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
     const unsigned long long unit_b0 = sm.prefix_b;
     const bool overflow = unit_b0 + tb > key_bytes_cap;
     if (overflow && tid == 0) atomicOr(&ctl->err, ERR_KEYS_FULL);
-    const uint32_t mis = (uint32_t)(unit_b0 & 15);
-    const bool staged = !overflow && tb <= UNIT_STAGE;
     const bool last_unit = unit == nunits - 1;
 #pragma unroll
     for (int j = 0; j < UNIT_ITEMS; ++j) {
         const uint32_t i = base + j;
         if (i >= m) break;
         if (!((headmask >> j) & 1u)) continue;
-        // the values of the equal keys that follow (the same key from other ranks) merge into this row
-        unsigned long long c = scnt[i];
-        for (uint32_t q = i + 1; q < m; ++q) {
-            if (!same_word(q, i)) break;
-            if (sorted[q].bin & MSD_FLAG8) {
-                Key a; a.k0 = skey[q].x; a.k1 = skey[q].y;
-                if (!same_key(a, key[j], bytes)) break;
-            }
-            c = (op == OP_SUM || op == OP_COUNT) ? c + scnt[q] : max(c, scnt[q]);
-        }
         rows.part[o] = part[j];
-        rows.count[o] = c;
+        rows.count[o] = cval[j];
         rows.key_off[o] = boff;
-        if (staged) write_key_bytes(sm.stage + mis + (uint32_t)(boff - unit_b0), key[j], len[j], bytes);
-        else if (!overflow) write_key_bytes(rows.key_bytes + boff, key[j], len[j], bytes);
+        if (!staged && !overflow) write_key_bytes(rows.key_bytes + boff, key[j], len[j], bytes);
         // partition starts: rows are partition-sorted; the row before this one is the previous head
         // of the unit or, for the unit's first row, the last row of the units before (look-back)
         uint32_t p_first;
@@ -658,7 +687,7 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
             p_first = sm.prefix_part;                   // (last partition before) + 1, or 0 if there is no row before
             new_part = sm.prefix_part == 0 || sm.prefix_part - 1 != part[j];
         } else {
-            const uint32_t pp = j > 0 ? part[j - 1] : ent.part(sorted[i - 1].val);
+            const uint32_t pp = j > 0 ? part[j - 1] : sorted[i - 1].val;
             p_first = pp + 1;
             new_part = pp != part[j];
         }
@@ -672,22 +701,27 @@ __global__ void __launch_bounds__(UNIT_THREADS) msd_unit_kernel(const MsdItem *i
         ctl->n_out = o;
         ctl->key_bytes = boff;
         rows.key_off[o] = boff;
-        for (uint32_t q = ent.part(sorted[m - 1].val) + 1u; q <= num_reducers; ++q) rows.part_begin[q] = o;
+        for (uint32_t q = sorted[m - 1].val + 1u; q <= num_reducers; ++q) rows.part_begin[q] = o;
     }
     if (last_unit && m == 0 && tid == 0) {
         // cannot happen (the last unit holds the last bin start), kept for safety
         ctl->n_out = sm.prefix_h; ctl->key_bytes = sm.prefix_b; rows.key_off[sm.prefix_h] = sm.prefix_b;
     }
-    if (staged) {
-        __syncthreads();
+    if (staged && !overflow) {
+        // the staged bytes start at the unit's first output byte, whose alignment is only known now:
+        // whole 16-byte chunks of the OUTPUT are assembled from five staged words and one funnel shift each
         UT(8);
-        uint8_t *dst = rows.key_bytes + (unit_b0 - mis);
-        const uint32_t end = mis + (uint32_t)tb;
+        const uint32_t mis = (uint32_t)(unit_b0 & 15);
+        uint8_t *dst = rows.key_bytes + (unit_b0 - mis);                       // 16-byte aligned
+        const uint32_t end = mis + (uint32_t)tb;                               // in dst coordinates
+        const uint32_t *sw = (const uint32_t *)sm.stage;
         for (uint32_t cb = tid * 16; cb < end; cb += UNIT_THREADS * 16) {
             if (cb >= mis && cb + 16 <= end) {
-                *(uint4 *)(dst + cb) = *(const uint4 *)(sm.stage + cb);
+                const uint32_t so = cb - mis, wi = so >> 2, sh = (so & 3) * 8;
+                const uint32_t x0 = sw[wi], x1 = sw[wi + 1], x2 = sw[wi + 2], x3 = sw[wi + 3], x4 = sw[wi + 4];
+                *(uint4 *)(dst + cb) = make_uint4(funnel_r(x0, x1, sh), funnel_r(x1, x2, sh), funnel_r(x2, x3, sh), funnel_r(x3, x4, sh));
             } else {
-                for (uint32_t q = cb < mis ? mis : cb; q < cb + 16 && q < end; ++q) dst[q] = sm.stage[q];
+                for (uint32_t q = cb < mis ? mis : cb; q < cb + 16 && q < end; ++q) dst[q] = sm.stage[q - mis];
             }
         }
     }
