@@ -1048,12 +1048,15 @@ int launch_msd(mr_ctx *ctx)
     static_assert(sizeof(UnitSmem) <= 55 * 1024, "four units per SM");
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
     CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
+    // no shuffle: the items are the table's entries, one per distinct key, so every item becomes a row
+    const bool distinct = !ctx->imported && getenv("MRGPU_MSD_LOOKBACK") == nullptr;
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
     ctx->msd_parity ^= 1;
     msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 4, ctx->sm_count * 4), 256, 0, s>>>(
-        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles);
+        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles,
+        ctx->ent, distinct);
     msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024 * 4, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
-        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb);
+        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb, ctx->rows_st, distinct);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
     msd_unit_kernel<<<units, UNIT_THREADS, sizeof(UnitSmem), s>>>(
         (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,

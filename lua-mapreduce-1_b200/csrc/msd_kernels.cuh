@@ -47,6 +47,7 @@ enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 // histogram, scatter cursors and bin starts; two of these alternate by job so that each job finds
 // its own zeroed (the histogram kernel of a job clears the other one)
 struct MsdBins {
+    unsigned long long hist_bytes[MSD_MAX_BINS];   // key bytes per bin (jobs whose items are all distinct keys)
     unsigned int hist[MSD_MAX_BINS];
     unsigned int bin_start[MSD_MAX_BINS + 1];
     unsigned int unit_bin[MSD_MAX_BINS + 2];   // first bin that starts at or after unit * UNIT_W (n <= bins * UNIT_W when no bin is too large, so units <= bins)
@@ -166,7 +167,7 @@ constexpr uint32_t MSD_TAG_FLAG8 = 1u << 15;
 
 __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, unsigned long long max_keys, uint32_t num_reducers,
                                                        Ctl *ctl, MsdBins *mb, MsdBins *mb_next, uint32_t *tags, RowsStatus st,
-                                                       uint32_t st_words)
+                                                       uint32_t st_words, EntryArrays ent, bool distinct)
 {
     __shared__ MsdPlan plan;
     __shared__ unsigned int s_occ[7][8];
@@ -228,12 +229,23 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
             const uint64_t i = i0 + q * stride;
             if (i < n) tags[i] = d[q] | ((it[q].lo & 0xFFu) == 8u ? MSD_TAG_FLAG8 : 0u) | min(r[q], 0xFFFFu) << 16;
         }
+        if (distinct) {
+            // every item will be a row: the key bytes per bin let the scatter kernel number the units'
+            // rows and bytes in advance, so that no unit waits for another (msd_scatter_kernel)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (i0 + q * stride >= n) continue;
+                uint32_t len = (uint32_t)it[q].lo & 0xFFu;                 // min(len, 8)
+                if (len == 8) len = key_len(ent.key(it[q].val));
+                atomicAdd(&mb->hist_bytes[d[q]], (unsigned long long)len);
+            }
+        }
     }
 }
 
 // ------------------------------------------------------------------ scatter
 __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, const uint32_t *tags, MsdItem *out, Ctl *ctl,
-                                                           MsdBins *mb)
+                                                           MsdBins *mb, RowsStatus st, bool distinct)
 {
     extern __shared__ unsigned int msd_start[];    // [bins + 1]
     __shared__ unsigned int wsum[32];
@@ -288,6 +300,51 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
             const uint32_t hi = msd_start[b] / UNIT_W;                                  // last u with u * W <= start[b]
             const uint32_t lo = b == 0 ? 0u : (msd_start[b - 1] + UNIT_W) / UNIT_W;      // first u with u * W > start[b-1] ... (start[b-1] / W) + 1
             for (uint32_t u = lo; u <= hi && u <= nunits; ++u) mb->unit_bin[u] = b;
+        }
+    }
+    if (distinct && blockIdx.x == 0 && plan.k >= 1) {
+        // Jobs whose items are all distinct keys (no shuffle: every table entry is one row).  The rows,
+        // key bytes and last partition before every unit follow from the histograms, so the look-back
+        // words of all units are written here as finished inclusive prefixes and no unit waits.
+        __shared__ unsigned long long wbs[32];
+        __shared__ unsigned int wln[32];
+        unsigned long long hb[MSD_MAX_BINS / 1024], bsum = 0;
+        unsigned int ln = 0;                            // (last non-empty bin of my range) + 1
+#pragma unroll
+        for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k) {
+            hb[k] = (k < per && b0 + k < bins) ? mb->hist_bytes[b0 + k] : 0ull;
+            bsum += hb[k];
+            if (c[k]) ln = b0 + k + 1;
+        }
+        unsigned long long bincl = bsum;
+        unsigned int lincl = ln;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long v = __shfl_up_sync(0xFFFFFFFFu, bincl, d);
+            const unsigned int l = __shfl_up_sync(0xFFFFFFFFu, lincl, d);
+            if (lane >= d) { bincl += v; lincl = max(lincl, l); }
+        }
+        if (lane == 31) { wbs[warp] = bincl; wln[warp] = lincl; }
+        __syncthreads();
+        unsigned long long brun = bincl - bsum;
+        unsigned int lne = __shfl_up_sync(0xFFFFFFFFu, lincl, 1);
+        if (lane == 0) lne = 0;
+        for (uint32_t w = 0; w < warp; ++w) { brun += wbs[w]; lne = max(lne, wln[w]); }
+        const uint32_t bpp = bins / plan.card[0];       // bins per partition (the partition is the leading field)
+        const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
+        constexpr unsigned long long F_INC = 2ull << 62;
+#pragma unroll
+        for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k) {
+            const uint32_t b = b0 + k;
+            if (k < per && b < bins && b > 0) {
+                const uint32_t s1 = msd_start[b], s0 = msd_start[b - 1];
+                const uint32_t u = s1 / UNIT_W;         // the one unit boundary inside (s0, s1], if any (a bin holds at most UNIT_W items)
+                if (u >= 1 && u < nunits && (unsigned long long)u * UNIT_W > s0) {
+                    st.bytes_agg[u - 1] = F_INC | brun;
+                    st.heads[u - 1] = F_INC | (unsigned long long)(lne ? (lne - 1) / bpp + 1 : 0u) << 32 | s1;
+                }
+            }
+            if (k < per && b < bins) { brun += hb[k]; if (c[k]) lne = b + 1; }
         }
     }
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;

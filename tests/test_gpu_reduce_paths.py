@@ -128,3 +128,21 @@ def test_number_keys_group_by():
             ctx.close()
         assert_rows_equal(got, want, "group-by")
         assert flags == (LSD if force else 0)
+
+
+def test_units_numbered_in_advance_or_by_look_back_give_the_same_rows():
+    # a job without a shuffle has only distinct keys: the scatter kernel numbers every unit's rows and bytes
+    # in advance; MRGPU_MSD_LOOKBACK makes the units find their numbers by look-back, as jobs after a shuffle do
+    splits, _ = corpus.generate(lines=[4000, 3500, 1, 0, 2800])
+    splits.append(corpus.TORTURE)
+    want = O.run_naive(splits, 10)
+    for lookback in (False, True):
+        if lookback:
+            os.environ["MRGPU_MSD_LOOKBACK"] = "1"
+        try:
+            (rows, flags, _), (rows2, flags2, _) = run(splits, 10, False, jobs=2)
+        finally:
+            os.environ.pop("MRGPU_MSD_LOOKBACK", None)
+        assert flags == 0 and flags2 == 0
+        assert_rows_equal(rows, want, f"lookback={lookback}")
+        assert_rows_equal(rows2, want, f"lookback={lookback}, second job")
