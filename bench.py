@@ -167,6 +167,27 @@ class Env:
     pass
 
 
+def bind_to_gpu_numa(index):
+    """N > 1: run this rank on the CPUs next to its GPU (NVML's CPU affinity of the device) before any
+    pinned buffer is allocated, so that first-touch places the staging memory on the GPU's own NUMA
+    node and eight ranks' host-to-device copies do not all cross one memory controller.  Returns a
+    short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} cpus {min(cpus)}-{max(cpus)}"
+    except Exception as e:          # no NVML, no permission: keep the inherited affinity
+        return f"unchanged ({type(e).__name__})"
+    return "unchanged"
+
+
 def parity_check(env, ctx, union_splits, info, balanced):
     """Every rank digests the rows it owns; the sums over ranks must equal the oracle's for the union
     corpus (run on rank 0 with all host threads).  Collective.  Returns the dict for the JSON line."""
@@ -368,10 +389,17 @@ def run_workload(env, args, splits, tokens_local, union_splits, steps, warmup, w
         wall_ms = (time.perf_counter() - w0) * 1e3
         e2e_ms = max(e0.elapsed_time(e1), wall_ms) / n_e2e
         t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+        per_rank = [e2e_ms]
         if world > 1:
+            gathered = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(gathered, t)
+            per_rank = [float(g.item()) for g in gathered]
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         out["e2e"] = {"value": tokens_total / (float(t.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                      "d2h_bytes_per_step": d2h, "steps": n_e2e, "ms_per_step": float(t.item())}
+                      "d2h_bytes_per_step": d2h, "steps": n_e2e, "ms_per_step": float(t.item()),
+                      "ms_per_step_by_rank": [round(x, 3) for x in per_rank],
+                      "h2d_GBs_by_rank": [round(h2d / (x * 1e-3) / 1e9, 1) for x in per_rank],
+                      "host_placement": getattr(env, "numa", "not bound")}
     ctx.close()
     del bufs
     return out
@@ -433,6 +461,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the data plane has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(env.local_rank)
     env.dev = torch.device("cuda", env.local_rank)
+    env.numa = bind_to_gpu_numa(env.local_rank) if world > 1 and not os.environ.get("MRGPU_NO_NUMA_BIND") else "not bound"
     if world > 1:
         dist.init_process_group("nccl", device_id=env.dev)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node N for --gpus N"

@@ -997,7 +997,7 @@ int launch_compact(mr_ctx *ctx)
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
     compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(
         ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
-        ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners());
+        ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners(), (uint32_t *)ctx->d_ties);
     ctx->table_dirty = false;
     ctx->stats.launches += 1;
     CU(cudaGetLastError());
@@ -1049,18 +1049,18 @@ int launch_msd(mr_ctx *ctx)
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
     CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
     // no shuffle: the items are the table's entries, one per distinct key, so every item becomes a row
+    // (the compaction kernel left the key lengths in d_ties, which only the LSD path's tie kernels use)
     const bool distinct = !ctx->imported && getenv("MRGPU_MSD_LOOKBACK") == nullptr;
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
     ctx->msd_parity ^= 1;
     msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 4, ctx->sm_count * 4), 256, 0, s>>>(
-        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles,
-        ctx->ent, distinct);
+        ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles);
     msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024 * 4, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
-        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb, ctx->rows_st, distinct);
+        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb, distinct ? (const uint32_t *)ctx->d_ties : nullptr);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
     msd_unit_kernel<<<units, UNIT_THREADS, sizeof(UnitSmem), s>>>(
         (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
-        ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb);
+        ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb, distinct);
     ctx->stats.launches += 3;
     if (ctx->cfg.reduce_kind == MR_REDUCE_MIN_U64) {
         rows_decode_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->rows, ctx->cfg.reduce_kind, ctx->d_ctl);

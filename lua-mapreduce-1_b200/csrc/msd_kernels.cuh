@@ -47,7 +47,6 @@ enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 // histogram, scatter cursors and bin starts; two of these alternate by job so that each job finds
 // its own zeroed (the histogram kernel of a job clears the other one)
 struct MsdBins {
-    unsigned long long hist_bytes[MSD_MAX_BINS];   // key bytes per bin (jobs whose items are all distinct keys)
     unsigned int hist[MSD_MAX_BINS];
     unsigned int bin_start[MSD_MAX_BINS + 1];
     unsigned int unit_bin[MSD_MAX_BINS + 2];   // first bin that starts at or after unit * UNIT_W (n <= bins * UNIT_W when no bin is too large, so units <= bins)
@@ -59,9 +58,11 @@ static_assert(sizeof(MsdBins) % 16 == 0, "MsdBins is cleared 16 bytes at a time"
 struct __align__(16) MsdItem {
     unsigned long long low;  // packed varying bits below the digit
     uint32_t val;            // entry index
-    uint32_t bin;            // digit | MSD_FLAG8 when the key has 8 or more bytes (its order may need later bytes)
+    uint32_t bin;            // bin | key length << 15 (jobs of distinct keys) | MSD_FLAG8 when the key has 8 or more bytes
 };
 constexpr uint32_t MSD_FLAG8 = 1u << 31;
+constexpr uint32_t MSD_BIN_MASK = MSD_MAX_BINS - 1;      // bits 0..14: the bin
+constexpr uint32_t MSD_LEN_SHIFT = 15, MSD_LEN_MAX = 0xFFFFu; // bits 15..30: min(key length, 65535), only in jobs of distinct keys
 static_assert(sizeof(MsdItem) == sizeof(SortItem), "the scattered items reuse the second sort buffer");
 
 __host__ __device__ __forceinline__ uint32_t popc32_hd(uint32_t x)
@@ -167,7 +168,7 @@ constexpr uint32_t MSD_TAG_FLAG8 = 1u << 15;
 
 __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, unsigned long long max_keys, uint32_t num_reducers,
                                                        Ctl *ctl, MsdBins *mb, MsdBins *mb_next, uint32_t *tags, RowsStatus st,
-                                                       uint32_t st_words, EntryArrays ent, bool distinct)
+                                                       uint32_t st_words)
 {
     __shared__ MsdPlan plan;
     __shared__ unsigned int s_occ[7][8];
@@ -229,23 +230,12 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
             const uint64_t i = i0 + q * stride;
             if (i < n) tags[i] = d[q] | ((it[q].lo & 0xFFu) == 8u ? MSD_TAG_FLAG8 : 0u) | min(r[q], 0xFFFFu) << 16;
         }
-        if (distinct) {
-            // every item will be a row: the key bytes per bin let the scatter kernel number the units'
-            // rows and bytes in advance, so that no unit waits for another (msd_scatter_kernel)
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (i0 + q * stride >= n) continue;
-                uint32_t len = (uint32_t)it[q].lo & 0xFFu;                 // min(len, 8)
-                if (len == 8) len = key_len(ent.key(it[q].val));
-                atomicAdd(&mb->hist_bytes[d[q]], (unsigned long long)len);
-            }
-        }
     }
 }
 
 // ------------------------------------------------------------------ scatter
 __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, const uint32_t *tags, MsdItem *out, Ctl *ctl,
-                                                           MsdBins *mb, RowsStatus st, bool distinct)
+                                                           MsdBins *mb, const uint32_t *lens)
 {
     extern __shared__ unsigned int msd_start[];    // [bins + 1]
     __shared__ unsigned int wsum[32];
@@ -302,51 +292,6 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
             for (uint32_t u = lo; u <= hi && u <= nunits; ++u) mb->unit_bin[u] = b;
         }
     }
-    if (distinct && blockIdx.x == 0 && plan.k >= 1) {
-        // Jobs whose items are all distinct keys (no shuffle: every table entry is one row).  The rows,
-        // key bytes and last partition before every unit follow from the histograms, so the look-back
-        // words of all units are written here as finished inclusive prefixes and no unit waits.
-        __shared__ unsigned long long wbs[32];
-        __shared__ unsigned int wln[32];
-        unsigned long long hb[MSD_MAX_BINS / 1024], bsum = 0;
-        unsigned int ln = 0;                            // (last non-empty bin of my range) + 1
-#pragma unroll
-        for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k) {
-            hb[k] = (k < per && b0 + k < bins) ? mb->hist_bytes[b0 + k] : 0ull;
-            bsum += hb[k];
-            if (c[k]) ln = b0 + k + 1;
-        }
-        unsigned long long bincl = bsum;
-        unsigned int lincl = ln;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned long long v = __shfl_up_sync(0xFFFFFFFFu, bincl, d);
-            const unsigned int l = __shfl_up_sync(0xFFFFFFFFu, lincl, d);
-            if (lane >= d) { bincl += v; lincl = max(lincl, l); }
-        }
-        if (lane == 31) { wbs[warp] = bincl; wln[warp] = lincl; }
-        __syncthreads();
-        unsigned long long brun = bincl - bsum;
-        unsigned int lne = __shfl_up_sync(0xFFFFFFFFu, lincl, 1);
-        if (lane == 0) lne = 0;
-        for (uint32_t w = 0; w < warp; ++w) { brun += wbs[w]; lne = max(lne, wln[w]); }
-        const uint32_t bpp = bins / plan.card[0];       // bins per partition (the partition is the leading field)
-        const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
-        constexpr unsigned long long F_INC = 2ull << 62;
-#pragma unroll
-        for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k) {
-            const uint32_t b = b0 + k;
-            if (k < per && b < bins && b > 0) {
-                const uint32_t s1 = msd_start[b], s0 = msd_start[b - 1];
-                const uint32_t u = s1 / UNIT_W;         // the one unit boundary inside (s0, s1], if any (a bin holds at most UNIT_W items)
-                if (u >= 1 && u < nunits && (unsigned long long)u * UNIT_W > s0) {
-                    st.bytes_agg[u - 1] = F_INC | brun;
-                    st.heads[u - 1] = F_INC | (unsigned long long)(lne ? (lne - 1) / bpp + 1 : 0u) << 32 | s1;
-                }
-            }
-            if (k < per && b < bins) { brun += hb[k]; if (c[k]) lne = b + 1; }
-        }
-    }
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
         SortItem it[4];
@@ -366,6 +311,7 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
             d = tg[q] & 0x7FFFu;
             o.val = it[q].val;
             o.bin = d | ((tg[q] & MSD_TAG_FLAG8) ? MSD_FLAG8 : 0u);
+            if (lens) o.bin |= min(lens[i0 + q * stride], MSD_LEN_MAX) << MSD_LEN_SHIFT;   // jobs of distinct keys: the key's length rides along
             out[msd_start[d] + (tg[q] >> 16)] = o;
         }
     }
@@ -381,7 +327,8 @@ struct __align__(16) UnitSmem {
     unsigned int wh[UNIT_WARPS];
     unsigned long long wb[UNIT_WARPS];
     unsigned long long prefix_h, prefix_b;
-    unsigned int prefix_part, unit, first, count, dfirst, fallback, maxbin;
+    unsigned int prefix_part, unit, first, count, dfirst, fallback, maxbin, inexact;
+    unsigned long long sumlen;
 };
 static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned long long) * UNIT_CAP, "counts fit where the warp histograms were");
 
@@ -396,7 +343,7 @@ static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned 
 __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
                                                                 RowArrays rows, uint32_t num_reducers, uint32_t op,
                                                                 unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl,
-                                                                MsdBins *mb)
+                                                                MsdBins *mb, bool distinct)
 {
     extern __shared__ __align__(16) uint8_t unit_smem_raw[];
     UnitSmem &sm = *(UnitSmem *)unit_smem_raw;
@@ -429,6 +376,8 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
         sm.count = mb->bin_start[be] - s0;
         sm.dfirst = ba;
         sm.maxbin = 0;
+        sm.inexact = 0;
+        sm.sumlen = 0;
     }
     __syncthreads();
     const uint32_t first = sm.first, m = sm.count, dfirst = sm.dfirst;   // m < UNIT_CAP (checked by the scatter kernel)
@@ -438,25 +387,101 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
     unsigned int *ext = &sm.whist[0][0];            // [i] = bin begin | bin size << 16 (free until the passes / the counts)
     {
         uint32_t big = 0;
+        unsigned long long lsum = 0;
+        bool inexact = false;
         for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
             MsdItem it = in[first + i];
-            const uint32_t d = it.bin & ~MSD_FLAG8;
+            const uint32_t d = it.bin & MSD_BIN_MASK;
+            const uint32_t l16 = (it.bin >> MSD_LEN_SHIFT) & MSD_LEN_MAX;
+            lsum += l16;
+            inexact |= l16 == MSD_LEN_MAX || l16 == 0;
             const uint32_t b0 = mb->bin_start[d] - first, sz = mb->bin_start[d + 1] - mb->bin_start[d];
             it.bin = (it.bin & MSD_FLAG8) | (d - dfirst);
             sm.buf[0][i] = it;
             ext[i] = b0 | sz << 16;
             big = max(big, sz);
         }
-        for (int d = 16; d; d >>= 1) big = max(big, __shfl_xor_sync(0xFFFFFFFFu, big, d));
+        for (int d = 16; d; d >>= 1) {
+            big = max(big, __shfl_xor_sync(0xFFFFFFFFu, big, d));
+            lsum += __shfl_xor_sync(0xFFFFFFFFu, lsum, d);
+        }
         if (lane == 0 && big) atomicMax(&sm.maxbin, big);
+        if (lane == 0 && lsum) atomicAdd(&sm.sumlen, lsum);
+        if (inexact) sm.inexact = 1;
     }
     uint32_t maxl = 0;
-    if (m) maxl = (in[first + m - 1].bin & ~MSD_FLAG8) - dfirst;           // bins ascend with the position
+    if (m) maxl = (in[first + m - 1].bin & MSD_BIN_MASK) - dfirst;           // bins ascend with the position
     uint32_t lbits = 0;
     while (lbits < 32 && (1u << lbits) <= maxl) ++lbits;
     const uint32_t npass = (low_bits + lbits + 7) / 8;
     __syncthreads();
     UT(2);
+
+    // ---- look-back over units: rows before, key bytes before, partition of the last row before.
+    // Two self-validating words per unit, each led by the same 2-bit state (1 aggregate, 2 inclusive):
+    //   A = state << 62 | (last partition + 1) << 32 | rows      (0 in the partition field = no row)
+    //   B = state << 62 | key bytes
+    // A reader takes a pair only when both states agree, so no fence orders the two stores; 128
+    // predecessors are read per round trip.
+    constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62, F_VAL = (1ull << 62) - 1;
+    auto lookback = [&](unsigned long long th_, unsigned long long tb_, unsigned long long last_) {   // warp 0
+        {
+            volatile unsigned long long *vA = st.heads, *vB = st.bytes_agg;
+            unsigned long long ph = 0, pb = 0, pl = 0;
+            if (unit == 0) {
+                if (lane == 0) { vB[0] = F_INC | tb_; vA[0] = F_INC | last_ << 32 | th_; }
+            } else {
+                if (lane == 0) { vB[unit] = F_AGG | tb_; vA[unit] = F_AGG | last_ << 32 | th_; }
+                int t = (int)unit - 1;
+                bool done = false;
+                for (uint32_t polls = 0; !done; ++polls) {
+                    if (polls > LOOKBACK_SPIN_LIMIT) { if (lane == 0) atomicOr(&ctl->err, ERR_LOOKBACK_TIMEOUT); break; }
+                    unsigned long long wa[4], wb[4];
+    #pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int idx = t - q * 32 - (int)lane;
+                        wa[q] = idx >= 0 ? vA[idx] : F_INC;
+                        wb[q] = idx >= 0 ? vB[idx] : F_INC;
+                    }
+    #pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t fa = (uint32_t)(wa[q] >> 62), fb = (uint32_t)(wb[q] >> 62);
+                        const bool ok = fa == fb && fa != 0;
+                        const uint32_t notready = __ballot_sync(0xFFFFFFFFu, !ok);
+                        const uint32_t incm = __ballot_sync(0xFFFFFFFFu, ok && fa == 2);
+                        const uint32_t stop = incm ? (uint32_t)__ffs((int)incm) - 1u : 31u;
+                        const uint32_t use = stop == 31 ? 0xFFFFFFFFu : ((2u << stop) - 1u);
+                        if (notready & use) break;                 // a needed predecessor has not published: read again from here
+                        unsigned long long bb = 0, h = 0, l = 0;
+                        if ((use >> lane) & 1u) {
+                            h = wa[q] & 0xFFFFFFFFull;
+                            l = (wa[q] >> 32) & 0x3FFFFFFFull;
+                            bb = wb[q] & F_VAL;
+                        }
+                        for (int d = 16; d; d >>= 1) {
+                            h += __shfl_xor_sync(0xFFFFFFFFu, h, d);
+                            bb += __shfl_xor_sync(0xFFFFFFFFu, bb, d);
+                            l = max(l, __shfl_xor_sync(0xFFFFFFFFu, l, d));   // partitions ascend with the units
+                        }
+                        ph += h; pb += bb; pl = max(pl, l);
+                        if (incm) { done = true; break; }
+                        t -= 32;
+                    }
+                }
+                if (lane == 0) { vB[unit] = F_INC | (pb + tb_); vA[unit] = F_INC | max(pl, last_) << 32 | (ph + th_); }
+            }
+            if (lane == 0) { sm.prefix_h = ph; sm.prefix_b = pb; sm.prefix_part = (unsigned int)pl; }
+        }
+    };
+    // Jobs without a shuffle hold every key once: each item will be a row, its key length came along
+    // with it, and the partition is the leading field of the bin -- so the unit publishes its rows and
+    // bytes NOW and the wait for the units before it overlaps the sorting below.
+    const uint32_t plan_k = ctl->msd_plan.k;
+    const bool early = distinct && plan_k >= 1 && !sm.inexact && !sm.fallback;
+    if (early && warp == 0) {
+        const uint32_t bpp = bins / ctl->msd_plan.card[0];
+        lookback(m, sm.sumlen, m ? (unsigned long long)((dfirst + maxl) / bpp + 1u) : 0ull);
+    }
 
     uint32_t cur = 0;
     const bool small_bins = sm.maxbin <= UNIT_COUNT_SORT_MAX;
@@ -664,61 +689,10 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
             if ((headmask >> j) & 1u) { write_key_bytes(sm.stage + (uint32_t)lb, key[j], len[j], bytes); lb += len[j]; }
     }
     UT(6);
-    // ---- look-back over units: rows before, key bytes before, partition of the last row before.
-    // Two self-validating words per unit, each led by the same 2-bit state (1 aggregate, 2 inclusive):
-    //   A = state << 62 | (last partition + 1) << 32 | rows      (0 in the partition field = no row)
-    //   B = state << 62 | key bytes
-    // A reader takes a pair only when both states agree, so no fence orders the two stores; 128
-    // predecessors are read per round trip.
-    constexpr unsigned long long F_AGG = 1ull << 62, F_INC = 2ull << 62, F_VAL = (1ull << 62) - 1;
+    // jobs after a shuffle (the same key may have arrived from several ranks): the unit knows its rows
+    // only now, after sorting and merging
     const unsigned long long my_last = (m && !declined) ? (unsigned long long)(sorted[m - 1].val + 1u) : 0ull;
-    if (warp == 0) {
-        volatile unsigned long long *vA = st.heads, *vB = st.bytes_agg;
-        unsigned long long ph = 0, pb = 0, pl = 0;
-        if (unit == 0) {
-            if (lane == 0) { vB[0] = F_INC | tb; vA[0] = F_INC | my_last << 32 | th; }
-        } else {
-            if (lane == 0) { vB[unit] = F_AGG | tb; vA[unit] = F_AGG | my_last << 32 | th; }
-            int t = (int)unit - 1;
-            bool done = false;
-            for (uint32_t polls = 0; !done; ++polls) {
-                if (polls > LOOKBACK_SPIN_LIMIT) { if (lane == 0) atomicOr(&ctl->err, ERR_LOOKBACK_TIMEOUT); break; }
-                unsigned long long wa[4], wb[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int idx = t - q * 32 - (int)lane;
-                    wa[q] = idx >= 0 ? vA[idx] : F_INC;
-                    wb[q] = idx >= 0 ? vB[idx] : F_INC;
-                }
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const uint32_t fa = (uint32_t)(wa[q] >> 62), fb = (uint32_t)(wb[q] >> 62);
-                    const bool ok = fa == fb && fa != 0;
-                    const uint32_t notready = __ballot_sync(0xFFFFFFFFu, !ok);
-                    const uint32_t incm = __ballot_sync(0xFFFFFFFFu, ok && fa == 2);
-                    const uint32_t stop = incm ? (uint32_t)__ffs((int)incm) - 1u : 31u;
-                    const uint32_t use = stop == 31 ? 0xFFFFFFFFu : ((2u << stop) - 1u);
-                    if (notready & use) break;                 // a needed predecessor has not published: read again from here
-                    unsigned long long bb = 0, h = 0, l = 0;
-                    if ((use >> lane) & 1u) {
-                        h = wa[q] & 0xFFFFFFFFull;
-                        l = (wa[q] >> 32) & 0x3FFFFFFFull;
-                        bb = wb[q] & F_VAL;
-                    }
-                    for (int d = 16; d; d >>= 1) {
-                        h += __shfl_xor_sync(0xFFFFFFFFu, h, d);
-                        bb += __shfl_xor_sync(0xFFFFFFFFu, bb, d);
-                        l = max(l, __shfl_xor_sync(0xFFFFFFFFu, l, d));   // partitions ascend with the units
-                    }
-                    ph += h; pb += bb; pl = max(pl, l);
-                    if (incm) { done = true; break; }
-                    t -= 32;
-                }
-            }
-            if (lane == 0) { vB[unit] = F_INC | (pb + tb); vA[unit] = F_INC | max(pl, my_last) << 32 | (ph + th); }
-        }
-        if (lane == 0) { sm.prefix_h = ph; sm.prefix_b = pb; sm.prefix_part = (unsigned int)pl; }
-    }
+    if (!early && warp == 0) lookback(th, tb, my_last);
     __syncthreads();
     if (declined) return;
     UT(7);

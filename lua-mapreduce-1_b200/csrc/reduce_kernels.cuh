@@ -187,7 +187,7 @@ constexpr int COMPACT_ITEMS = 4;
 // although only a fraction of the slots is occupied.
 __global__ void __launch_bounds__(256) compact_partition_kernel(
     GEntry *gt, uint64_t nslots, const uint8_t *bytes, uint32_t num_reducers, uint32_t partition_kind,
-    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, OwnerMap owners)
+    EntryArrays ent, SortItem *items, uint64_t max_keys, Ctl *ctl, OwnerMap owners, uint32_t *lens)
 {
     constexpr int ITEMS = COMPACT_ITEMS;
     __shared__ ulonglong4 s_ent[256 * ITEMS];
@@ -244,6 +244,7 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
             ((ulonglong4 *)ent.e)[idx] = v;
             SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
             items[idx] = it;
+            lens[idx] = key_len(key);              // for the MSD path of jobs without a shuffle (msd_kernels.cuh)
             hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
             occ_add(s_occ, chunk);
             any = true;
