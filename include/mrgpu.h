@@ -47,11 +47,14 @@ enum mr_map_kind {
     MR_MAP_RECORDS_U32 = 1, /* a mapfn that emits (number key, number value) records: emit, job.lua:83-97 */
     MR_MAP_BIGRAM_WS = 2    /* mapfn.lua:3-9 emitting (w_i .. " " .. w_{i+1}, 1) for neighbours inside a line */
 };
-enum mr_reduce_kind {       /* reducefn = combinerfn; all associative, commutative, idempotent (job.lua:104-106) */
+enum mr_reduce_kind {       /* reducefn = combinerfn; all associative, commutative, idempotent (job.lua:104-106).  The
+                             * reference calls such a reducer only for keys with more than one value and otherwise
+                             * always (job.lua:264-284, examples/WordCount/reducefn2.lua); for these four the rows
+                             * are the same either way. */
     MR_REDUCE_SUM_U64 = 0,  /* examples/WordCount/reducefn.lua:1-5: emit(sum of values) */
-    MR_REDUCE_MIN_U64 = 1,  /* emit(math.min(unpack(values)))   -- records jobs only */
-    MR_REDUCE_MAX_U64 = 2,  /* emit(math.max(unpack(values)))   -- records jobs only */
-    MR_REDUCE_COUNT = 3     /* emit(number of values): a mapfn emitting (key, 1) with the sum reducer */
+    MR_REDUCE_MIN_U64 = 1,  /* emit(math.min(unpack(values))): number keys (mr_map_records) or string keys with values (mr_map_pairs) */
+    MR_REDUCE_MAX_U64 = 2,  /* emit(math.max(unpack(values))): the same */
+    MR_REDUCE_COUNT = 3     /* emit(number of values): records, or tokenised text (where it equals the sum of the emitted ones) */
 };
 enum mr_partition_kind {
     MR_PARTITION_FNV1_LUA52 = 0, /* examples/WordCount/partitionfn.lua:8-16 (string keys) */

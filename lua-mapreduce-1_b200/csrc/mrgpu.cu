@@ -499,7 +499,12 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     const bool text_job = (cfg->map_kind == MR_MAP_TOKENIZE_WS || cfg->map_kind == MR_MAP_BIGRAM_WS) &&
                           cfg->partition_kind == MR_PARTITION_FNV1_LUA52;
     const bool rec_job = cfg->map_kind == MR_MAP_RECORDS_U32 && cfg->partition_kind == MR_PARTITION_MOD_U32;
-    const bool red_ok = cfg->reduce_kind == MR_REDUCE_SUM_U64 || (rec_job && cfg->reduce_kind <= MR_REDUCE_COUNT);
+    // text jobs: every token is emit(word, 1), so a count IS the sum; a minimum / maximum of ones says
+    // nothing, so those reducers take their values from mr_map_pairs only (string keys with values)
+    const bool red_ok = cfg->reduce_kind == MR_REDUCE_SUM_U64 || (rec_job && cfg->reduce_kind <= MR_REDUCE_COUNT) ||
+                        (text_job && cfg->reduce_kind == MR_REDUCE_COUNT) ||
+                        (cfg->map_kind == MR_MAP_TOKENIZE_WS && text_job &&
+                         (cfg->reduce_kind == MR_REDUCE_MIN_U64 || cfg->reduce_kind == MR_REDUCE_MAX_U64));
     if (!(text_job || rec_job) || !red_ok)
         return fail(nullptr, MR_ERR_UNSUPPORTED, "mr_ctx_create: unsupported map/reduce/partition kind");
     if (cfg->num_reducers == 0 || cfg->num_reducers > (1u << 24))
@@ -688,6 +693,8 @@ static int stage_split(mr_ctx *ctx, const void *bytes, uint64_t n, cudaMemcpyKin
     if (!ctx) return MR_ERR_INVALID;
     if (ctx->cfg.map_kind == MR_MAP_RECORDS_U32)
         return fail(ctx, MR_ERR_INVALID, "mr_map_split: this context maps records, use mr_map_records");
+    if (ctx->cfg.reduce_kind == MR_REDUCE_MIN_U64 || ctx->cfg.reduce_kind == MR_REDUCE_MAX_U64)
+        return fail(ctx, MR_ERR_UNSUPPORTED, "mr_map_split: a tokenised split emits (word, 1); a min/max context takes (key, value) pairs (mr_map_pairs)");
     if (n && !bytes) return fail(ctx, MR_ERR_INVALID, "mr_map_split: null bytes");
     if (ctx->state != mr_ctx::IDLE && ctx->state != mr_ctx::MAPPED)
         return fail(ctx, MR_ERR_INVALID, "mr_map_split: job already reduced; call mr_job_begin");

@@ -110,3 +110,43 @@ def test_runs_written_by_gpu_mappers_feed_the_reference_merge(tmp_path):
         for key, values in merge_iterator(runs):
             got.append((p, key, sum(values)))
     assert got == [(int(p), k, int(c)) for p, k, c in zip(want.part, want.keys(), want.count)]
+
+
+def test_min_and_max_over_string_keys_with_values():
+    # f-3: reducers other than the sum on string keys.  A tokenised split only ever emits (word, 1), so a
+    # min/max context is fed (key, value) pairs -- e.g. runs whose lines carry the values to fold
+    import random
+    rnd = random.Random(6)
+    keys = [bytes(rnd.choice(b"abcdefgh") for _ in range(rnd.randrange(1, 24))) for _ in range(3000)]
+    pairs = [(rnd.choice(keys), rnd.randrange(0, 1 << 40)) for _ in range(40000)]
+    for kind, fold in ((_native.MR_REDUCE_MIN_U64, min), (_native.MR_REDUCE_MAX_U64, max)):
+        want = {}
+        for k, v in pairs:
+            want[k] = fold(want[k], v) if k in want else v
+        ctx = _native.Context(R, 1 << 23, max_keys=1 << 16, reduce_kind=kind)
+        try:
+            with pytest.raises(_native.NativeError) as e:
+                ctx.map_split(0, b"text is refused here")
+            assert e.value.code == _native.MR_ERR_UNSUPPORTED
+            for b in range(0, len(pairs), 7000):
+                chunk = pairs[b:b + 7000]
+                ctx.map_pairs(b, [k for k, _ in chunk], [v for _, v in chunk])
+            rows = ctx.rows()
+        finally:
+            ctx.close()
+        got = dict(zip(rows.keys(), (int(c) for c in rows.count)))
+        assert got == want
+        order = [(wire_part(k), k) for k in rows.keys()]
+        assert order == sorted(order) and [p for p, _ in order] == [int(p) for p in rows.part]
+    # a count over tokenised text is the sum of the ones
+    ctx = _native.Context(R, 1 << 20, max_keys=1 << 12, reduce_kind=_native.MR_REDUCE_COUNT)
+    try:
+        ctx.map_split(0, b"a b a c a b")
+        rows = ctx.rows()
+        assert dict(zip(rows.keys(), (int(c) for c in rows.count))) == {b"a": 3, b"b": 2, b"c": 1}
+    finally:
+        ctx.close()
+
+
+def wire_part(key):
+    return O.partition(key, R)
