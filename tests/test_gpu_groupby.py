@@ -117,7 +117,16 @@ def test_other_reducers(kind, op):
         assert int(got.count.sum()) == n
 
 
-def test_reducers_other_than_sum_need_a_records_job():
+def test_min_and_max_need_values_to_fold():
+    # on a text context they are fed (key, value) pairs (tests/test_gpu_run_files.py); a tokenised split
+    # only emits ones, and bigram contexts have no pair input at all
+    ctx = _native.Context(10, 1 << 20, reduce_kind=_native.MR_REDUCE_MAX_U64)
+    try:
+        with pytest.raises(_native.NativeError) as e:
+            ctx.map_split(0, b"a b")
+        assert e.value.code == _native.MR_ERR_UNSUPPORTED
+    finally:
+        ctx.close()
     with pytest.raises(_native.NativeError) as e:
-        _native.Context(10, 1 << 20, reduce_kind=_native.MR_REDUCE_MAX_U64)
+        _native.Context(10, 1 << 20, reduce_kind=_native.MR_REDUCE_MAX_U64, map_kind=_native.MR_MAP_BIGRAM_WS)
     assert e.value.code == _native.MR_ERR_UNSUPPORTED
