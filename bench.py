@@ -405,7 +405,7 @@ def run_workload(env, args, splits, tokens_local, union_splits, steps, warmup, w
     return out
 
 
-def run_reference(args):
+def run_reference(args, out):
     """The reference's CPU path (oracle staged = job.lua + utils.merge_iterator restated in C; the Lua +
     MongoDB original cannot run in this image), on all host cores, on the SAME workload as our arm at
     N = 1: every step maps and reduces all 197 splits of config 2."""
@@ -427,7 +427,7 @@ def run_reference(args):
     value = tokens / dt
     sample_txt = (f"all {len(splits)} splits of config 2 ({tokens} tokens) per step, {args.steps} steps, oracle staged path "
                   f"(job.lua + merge_iterator restated in C), {threads} OpenMP threads as workers")
-    print(json.dumps({
+    out.write(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
@@ -440,13 +440,25 @@ def run_reference(args):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample_txt},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }))
+    }) + "\n")
 
 
 def main():
     args = parse()
-    if args.impl == "reference":
-        return run_reference(args)
+    # stdout carries ONE JSON line: whatever libraries print there while the job runs (NCCL's version
+    # banner, for one) goes to stderr; the line itself is written to the saved descriptor at the end
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    try:
+        if args.impl == "reference":
+            return run_reference(args, real_stdout)
+        return run_ours(args, real_stdout)
+    finally:
+        real_stdout.flush()
+
+
+def run_ours(args, out):
 
     import torch
     import torch.distributed as dist
@@ -557,7 +569,7 @@ def main():
                "sample": f"all {len(splits)} splits of config 2 once ({m['tokens_local']} tokens, {dt:.2f} s), "
                          "oracle staged path with OpenMP threads as workers"}
 
-    print(json.dumps({
+    out.write(json.dumps({
         "metric": METRIC, "value": m["tokens_total"] / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/u64", "data": "synthetic",
@@ -568,7 +580,7 @@ def main():
                    "l2": "input per rank (294 MB) is larger than L2 (126 MB); no flush between steps"},
         "roofline": roofline, "nvlink": nvlink, "cpu_baseline": cpu, "e2e": m["e2e"], "gpu_launches": m["launches"],
         "clocks": m["clocks"], "parity_check": m["parity"], "strong_config3": strong,
-    }))
+    }) + "\n")
     if world > 1:
         dist.destroy_process_group()
 

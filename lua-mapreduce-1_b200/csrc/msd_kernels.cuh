@@ -24,7 +24,7 @@
 // Fallback: the path declines (Ctl::msd_fallback, nothing written that the LSD path would not
 // overwrite) when the packed low bits exceed 64, a bin holds more than UNIT_CAP - UNIT_W items
 // (many more keys than 2^15 bins can spread, or keys that only differ late), or a group of keys
-// equal in their first 7 bytes has more than TIE_SMALL_GROUP members.  mr_job_sync then runs the LSD
+// equal in their first 7 bytes has more than MSD_TIE_GROUP members (copies of a key from several ranks count).  mr_job_sync then runs the LSD
 // path; a context that declined once goes straight to the LSD path afterwards.
 #pragma once
 #include "reduce_kernels.cuh"
@@ -41,6 +41,7 @@ constexpr int UNIT_WARPS = UNIT_THREADS / 32;
 constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS; // 4
 constexpr uint32_t UNIT_STAGE = 12 * 1024 - 16;   // key bytes of a unit staged for coalesced stores (more: written directly)
 constexpr uint32_t UNIT_COUNT_SORT_MAX = 192; // bins up to this size are ordered by counting inside the bin
+constexpr uint32_t MSD_TIE_GROUP = 64;        // keys equal in their first 7 bytes (copies of one key included) a unit orders itself
 
 enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
 
@@ -586,36 +587,54 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
     ulonglong2 *skey = (ulonglong2 *)sm.buf[cur ^ 1];       // (k0, k1) of sorted[i], filled below
     unsigned long long *scnt = (unsigned long long *)&sm.whist[0][0];
 
-    // ---- keys that agree in the whole sort word and have 8+ bytes: ordered by their later bytes.  The
-    // first member of such a group orders it (insertion sort on the entry indices, full key compare).
     auto same_word = [&](uint32_t a, uint32_t b) { return sorted[a].low == sorted[b].low && sorted[a].bin == sorted[b].bin; };
+    // ---- entries of the sorted items: one 32-byte gather each; key, value and partition stay in shared
+    // memory at the item's sorted position (the entry index has done its work: its slot takes the partition)
+    const uint32_t base = tid * UNIT_ITEMS;
+    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+        const ulonglong4 e = ld256(&ent.e[sorted[i].val]);
+        skey[i] = make_ulonglong2(e.x, e.y);
+        scnt[i] = e.z;
+        sorted[i].val = (uint32_t)e.w;
+    }
+    __syncthreads();
+    UT(4);
+    // ---- keys that agree in the whole sort word and have 8+ bytes are ordered by their later bytes: the
+    // first member of such a group orders it in place (insertion sort, full-key compares out of shared
+    // memory).  Equal keys -- the same key from several ranks -- stay where they are and merge below.
     for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
         if (!(sorted[i].bin & MSD_FLAG8)) continue;
         if (i > 0 && same_word(i, i - 1)) continue;
         uint32_t g = 1;
-        while (i + g < m && g <= TIE_SMALL_GROUP && same_word(i, i + g)) ++g;
+        while (i + g < m && g <= MSD_TIE_GROUP && same_word(i, i + g)) ++g;
         if (g == 1) continue;
-        if (g > TIE_SMALL_GROUP) { atomicOr(&ctl->msd_fallback, MSD_FB_TIES); sm.fallback = 1; continue; }
-        uint32_t v[TIE_SMALL_GROUP];
-        for (uint32_t a = 0; a < g; ++a) v[a] = sorted[i + a].val;
+        if (g > MSD_TIE_GROUP) { atomicOr(&ctl->msd_fallback, MSD_FB_TIES); sm.fallback = 1; continue; }
+        bool moved = false;
         for (uint32_t a = 1; a < g; ++a) {
-            const uint32_t x = v[a];
-            const Key kx = ent.key(x);
+            const ulonglong2 kx2 = skey[i + a];
+            Key kx; kx.k0 = kx2.x; kx.k1 = kx2.y;
+            const unsigned long long cx = scnt[i + a];
+            const uint32_t px = sorted[i + a].val;
             uint32_t b = a;
-            while (b > 0 && key_less(kx, ent.key(v[b - 1]), x, v[b - 1], bytes, 1)) { v[b] = v[b - 1]; --b; }
-            v[b] = x;
+            while (b > 0) {
+                Key kb; kb.k0 = skey[i + b - 1].x; kb.k1 = skey[i + b - 1].y;
+                if (!key_less(kx, kb, 1, 0, bytes, 1)) break;      // equal keys: "not less" (entry order 1 > 0), so they stay
+                skey[i + b] = skey[i + b - 1]; scnt[i + b] = scnt[i + b - 1]; sorted[i + b].val = sorted[i + b - 1].val;
+                --b;
+            }
+            if (b != a) { skey[i + b] = kx2; scnt[i + b] = cx; sorted[i + b].val = px; moved = true; }
+            else if (!moved) {
+                Key kp; kp.k0 = skey[i + a - 1].x; kp.k1 = skey[i + a - 1].y;
+                moved = !same_key(kx, kp, bytes);             // different keys that already stood in order
+            }
         }
-        for (uint32_t a = 0; a < g; ++a) sorted[i + a].val = v[a];
-        atomicAdd(&ctl->tie_small, 1u);
+        if (moved) atomicAdd(&ctl->tie_small, 1u);
     }
     __syncthreads();
     // a unit that declined still takes part in the look-back below (with nothing), so that no later
     // unit waits for it; the rows are rewritten by the LSD path anyway
     const bool declined = sm.fallback != 0;
-    UT(4);
-
-    // ---- entries of the sorted items (one 32-byte gather each), heads, row and byte counts
-    const uint32_t base = tid * UNIT_ITEMS;
+    UT(5);
     Key key[UNIT_ITEMS];
     uint32_t part[UNIT_ITEMS], len[UNIT_ITEMS];
 #pragma unroll
@@ -623,17 +642,11 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
         const uint32_t i = base + j;
         part[j] = 0; len[j] = 0; key[j].k0 = 0; key[j].k1 = 0;
         if (i < m) {
-            const ulonglong4 e = ld256(&ent.e[sorted[i].val]);
-            key[j].k0 = e.x; key[j].k1 = e.y;
-            part[j] = (uint32_t)e.w;
+            key[j].k0 = skey[i].x; key[j].k1 = skey[i].y;
+            part[j] = sorted[i].val;
             len[j] = key_len(key[j]);
-            skey[i] = make_ulonglong2(e.x, e.y);
-            scnt[i] = e.z;
-            sorted[i].val = part[j];        // the entry index has done its work: the slot now holds the partition
         }
     }
-    __syncthreads();
-    UT(5);
     // heads, and for every head the merged value of the equal keys that follow it (the same key from
     // other ranks: merge_min_keys, utils.lua:232-247, with the job's reducer)
     uint32_t headmask = 0, nh = 0;
