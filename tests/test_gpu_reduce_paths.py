@@ -92,11 +92,16 @@ def test_small_tie_groups_are_ordered_inside_the_unit():
 
 
 def test_large_tie_groups_make_the_shared_memory_path_decline():
+    # ~250 keys per partition agree in their first 7 bytes: more than a unit orders by itself (64)
     rnd = random.Random(2)
-    keys = sorted({b"prefix_" + bytes(rnd.choice(b"abc") for _ in range(rnd.randrange(1, 12))) for _ in range(600)})
-    text = b" ".join(rnd.choice(keys) for _ in range(4000))
+    keys = sorted({b"prefix_" + bytes(rnd.choice(b"abcde") for _ in range(rnd.randrange(1, 12))) for _ in range(2500)})
+    text = b" ".join(rnd.choice(keys) for _ in range(12000))
     fa = both([text], 10, expect_msd=False)
-    assert (fa >> 8) & 8                            # MSD_FB_TIES
+    assert (fa >> 8) & (8 | 4)                      # MSD_FB_TIES (or a bin too large for a unit)
+    # up to 64 of them are the unit's own business
+    keys = keys[:300]
+    text = b" ".join(rnd.choice(keys) for _ in range(3000))
+    both([text], 10, expect_msd=True)
 
 
 def test_binary_keys_of_every_byte_value():
