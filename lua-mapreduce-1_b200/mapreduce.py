@@ -76,6 +76,13 @@ def _field(m, name):
     return getattr(m, name, None)
 
 
+def _shared_dir(storage):
+    """utils.get_storage_from (utils.lua:273-285): "shared:/path" names a directory every worker sees."""
+    if isinstance(storage, str) and storage.startswith("shared:"):
+        return storage[len("shared:"):]
+    return None
+
+
 def _make_job(key, value):
     # utils.lua:87-98
     return {"_id": key, "value": value, "worker": None, "status": WAITING, "repetitions": 0,
@@ -127,7 +134,7 @@ class server:
                 b.map_jobs, b.red_jobs, b.results = [], [], {}
                 b.task = {"status": TASK_WAIT, "iteration": it,
                           "params": {"mods": self.mods, "init_args": self.init_args,
-                                     "result_ns": self.result_ns}}
+                                     "result_ns": self.result_ns, "storage": self.storage}}
                 # server_prepare_map, server.lua:249-276
                 keys = set()
 
@@ -306,7 +313,8 @@ class worker:
             # contexts of two workers of one board -- each would reduce and publish only what it
             # mapped itself.  So a second worker is refused, loudly, before it touches a job.
             # (N GPUs: N ranks of ONE worker group with a shuffle, parallel.py / mr_shuffle_*.)
-            owner = task.setdefault("data_worker", self.name)
+            shared_dir = _shared_dir(task["params"].get("storage"))
+            owner = self.name if shared_dir else task.setdefault("data_worker", self.name)
             if owner != self.name:
                 raise RuntimeError(
                     f"{self.name}: worker {owner} already runs this task's data plane; a board takes one "
@@ -326,6 +334,10 @@ class worker:
             self.ctx_kinds = kinds
         ctx = self.ctx
         records = kinds[0] == _native.MR_MAP_RECORDS_U32
+        if shared_dir:
+            if records or kinds[0] != _native.MR_MAP_TOKENIZE_WS:
+                raise NotImplementedError("storage 'shared:' carries string-key runs (word count); number keys and bigrams keep storage 'hbm'")
+            return self._run_task_shared(task, map_jobs, red_jobs, results, ctx, R, shared_dir)
         # Map affinity across iterations (task.lua:279-293: in iteration > 1 a worker prefers the map
         # jobs it ran before): when the waiting map jobs are exactly the ones whose splits this
         # worker still holds in HBM, the splits are not staged again (mr_job_begin(keep_input)).
@@ -403,6 +415,90 @@ class worker:
                     rows = [(int.from_bytes(k, "big"), c) for k, c in rows]
                 with b.lock:
                     results[job["value"]["result"]] = (lambda r=rows: iter(r))
+                self._mark(job, WRITTEN, written_time=time.time(), cpu_time=time.process_time() - c0,
+                           real_time=time.time() - t0)
+            except Exception as e:
+                self._broken(job, e)
+        with b.lock:
+            while not all(j["status"] in (WRITTEN, FAILED) for j in red_jobs):
+                b.lock.wait(DEFAULT_SLEEP)
+        self._done_task = task
+
+    def _run_task_shared(self, task, map_jobs, red_jobs, results, ctx, R, path):
+        """storage = "shared:<dir>": the reference's own arrangement (fs.lua 'shared', job.lua:208-221 and
+        253-265).  Any number of workers share the board: a worker maps the splits it claims and leaves
+        one run `map_results.P<p>.M<worker>` per partition in <dir>; reduce jobs, one per partition that
+        has runs (server.lua:294-324), go to whichever worker takes them: it reads all runs of its
+        partition into its context (mr_map_pairs), reduces, publishes the result and removes the runs."""
+        import os
+        from . import wire
+        b = self.board
+        params = task["params"]
+        ns = "map_results.it%d" % task["iteration"]
+        ctx.job_begin()
+        mine = []
+        while True:
+            job = self._take(map_jobs)
+            if job is None:
+                with b.lock:
+                    if all(j["status"] in (FINISHED, WRITTEN, FAILED) for j in map_jobs):
+                        break
+                    b.lock.wait(DEFAULT_SLEEP)
+                continue
+            t0, c0 = time.time(), time.process_time()
+            try:
+                value = job["value"]
+                if isinstance(value, (bytes, bytearray, memoryview)) or hasattr(value, "ctypes"):
+                    ctx.map_split(len(mine), value)
+                else:
+                    ctx.map_split_path(len(mine), value)
+                self._mark(job, FINISHED, finished_time=time.time())
+                mine.append((job, t0, c0))
+            except Exception as e:
+                self._broken(job, e)
+        self.kept_input = False
+        if mine:
+            try:
+                ctx.map_finish()
+                ctx.reduce_all()
+                self.last_info = ctx.job_sync()
+                wire.write_map_results(ctx.rows(), path, mapper_key=self.name, map_results_ns=ns)
+            except Exception as e:
+                for job, _, _ in mine:
+                    self._broken(job, e)
+                raise
+            for job, t0, c0 in mine:
+                self._mark(job, WRITTEN, written_time=time.time(), cpu_time=time.process_time() - c0,
+                           real_time=time.time() - t0)
+        # ---- reduce phase: the first worker to see it lists the partitions that have runs
+        with b.lock:
+            while task["status"] == TASK_MAP:
+                b.lock.wait(DEFAULT_SLEEP)
+            if not task.get("reduce_ready"):
+                parts = wire.partitions_with_runs(path, ns)
+                width = len(str(max(parts))) if parts else 1
+                for p in parts:
+                    name = f"{params['result_ns']}.P{p:0{width}d}"
+                    red_jobs.append(_make_job(p, {"partition": p, "result": name}))
+                task["reduce_ready"] = True
+                b.lock.notify_all()
+        while True:
+            job = self._take(red_jobs)
+            if job is None:
+                break
+            t0, c0 = time.time(), time.process_time()
+            try:
+                p = job["value"]["partition"]
+                names = wire.list_map_results(path, p, ns)
+                ctx.job_begin()
+                wire.ingest_runs(ctx, path, p, ns)
+                ctx.reduce_all()
+                ctx.job_sync()
+                rows = list(ctx.partition_cursor(p))
+                with b.lock:
+                    results[job["value"]["result"]] = (lambda r=rows: iter(r))
+                for n in names:                       # job.lua:293: the consumed runs are deleted
+                    os.remove(os.path.join(path, n))
                 self._mark(job, WRITTEN, written_time=time.time(), cpu_time=time.process_time() - c0,
                            real_time=time.time() - t0)
             except Exception as e:

@@ -184,12 +184,16 @@ def write_map_results(rows, directory, mapper_key, map_results_ns="map_results")
 def list_map_results(directory, part, map_results_ns="map_results"):
     """The runs of one partition (job.lua:253-260: file names matching ^<path>/map_results.P<p>\\..*)."""
     prefix = "%s.P%d." % (map_results_ns, part)
+    if not os.path.isdir(directory):
+        return []
     return sorted(n for n in os.listdir(directory) if n.startswith(prefix))
 
 
 def partitions_with_runs(directory, map_results_ns="map_results"):
     """server_prepare_reduce (server.lua:294-312): the partitions that have at least one run."""
     pat = re.compile(r"^%s\.P(\d+)\.M.*$" % re.escape(map_results_ns))
+    if not os.path.isdir(directory):
+        return []
     return sorted({int(m.group(1)) for m in map(pat.match, os.listdir(directory)) if m})
 
 

@@ -139,3 +139,53 @@ def test_loop_iterations_keep_the_splits_resident(tmp_path):
     assert runs == [expect, expect, expect]
     assert w.kept_input is True and int(w.ctx.stats().h2d_bytes) == 0     # last iteration copied nothing
     w.ctx.close()
+
+
+def test_three_gpu_workers_share_a_board_through_run_files(tmp_path):
+    # storage "shared:<dir>": N workers per board as in the reference; GPU mappers write the reference's
+    # run files, GPU reducers read them back (mr_map_pairs) -- whoever claims what, the result is whole
+    splits, _ = corpus.generate(lines=[500, 650, 1, 400, 300, 0, 720, 210])
+    splits[2] = np.frombuffer(corpus.TORTURE, dtype=np.uint8)
+    paths = []
+    for i, s in enumerate(splits):
+        p = tmp_path / f"split{i}.txt"
+        p.write_bytes(s.tobytes())
+        paths.append(str(p))
+    want = O.run_staged(splits, 15, 2)
+    seen = []
+
+    class Final:
+        init = staticmethod(lambda arg=None: None)
+
+        @staticmethod
+        def finalfn(pairs_iterator):
+            seen.append([(k, v[0]) for k, v in pairs_iterator])
+            return True
+
+    store = tmp_path / "store"
+    s = mapreduce.server.new("localhost", "wordcount-gpu-shared")
+    s.configure({"taskfn": WordCount, "mapfn": WordCount, "partitionfn": WordCount, "reducefn": WordCount,
+                 "combinerfn": WordCount, "finalfn": Final, "storage": f"shared:{store}",
+                 "init_args": {"files": paths, "num_reducers": 15}})
+    workers = [mapreduce.worker.new("localhost", "wordcount-gpu-shared").configure(
+        {"max_iter": 4000, "arena_bytes": 1 << 24, "max_keys": 1 << 18}) for _ in range(3)]
+    errors = []
+
+    def go(w):
+        try:
+            w.execute()
+        except Exception as e:
+            errors.append(e)
+    threads = [threading.Thread(target=go, args=(w,), daemon=True) for w in workers]
+    for t in threads:
+        t.start()
+    stats = s.loop()
+    for t in threads:
+        t.join(60)
+        assert not t.is_alive()
+    assert not errors, errors
+    assert seen == [list(zip(want.keys(), (int(c) for c in want.count)))]
+    assert stats["red_jobs"] == len(set(want.part.tolist())) and stats["failed_map_jobs"] == 0
+    for w in workers:
+        if w.ctx is not None:
+            w.ctx.close()

@@ -2,6 +2,7 @@
 the device; this is test code) lets the job board, the BROKEN -> retry -> FAILED rules, the
 "loop" iterations with map affinity and the worker's bookkeeping run without a GPU.  The data plane
 itself is covered by the -m gpu tests."""
+import os
 import threading
 import time
 import types
@@ -31,6 +32,11 @@ class StandInContext:
             self.splits = []
         self.h2d = 0
         self.rows_ = None
+        self.pairs = {}
+
+    def map_pairs(self, split_id, keys, values):
+        for k, v in zip(keys, values):
+            self.pairs[k] = self.pairs.get(k, 0) + int(v)
 
     def _stage(self, data):
         if type(self).fail_next_splits > 0:
@@ -52,13 +58,23 @@ class StandInContext:
     def reduce_all(self):
         time.sleep(self.delay)
         self.rows_ = O.run_naive(self.splits, self.num_reducers)
+        if getattr(self, "pairs", None):        # ingested runs merge with the tokenised splits (mr_map_pairs)
+            merged = dict(zip(self.rows_.keys(), (int(c) for c in self.rows_.count)))
+            for k, v in self.pairs.items():
+                merged[k] = merged.get(k, 0) + v
+            order = sorted(merged, key=lambda k: (O.partition(k, self.num_reducers), k))
+            off = np.concatenate([[0], np.cumsum([len(k) for k in order])]).astype(np.uint64)
+            self.rows_ = O.Rows([O.partition(k, self.num_reducers) for k in order], [merged[k] for k in order], off,
+                                np.frombuffer(b"".join(order), dtype=np.uint8), self.rows_.tokens + len(self.pairs))
 
     def job_sync(self):
         return types.SimpleNamespace(n_tokens=self.rows_.tokens, n_keys=self.rows_.n)
 
     def rows(self):
         pb = np.searchsorted(self.rows_.part, np.arange(self.num_reducers + 1))
-        return types.SimpleNamespace(part_begin=pb.astype(np.uint64))
+        r = self.rows_
+        return types.SimpleNamespace(part_begin=pb.astype(np.uint64), part=r.part, count=r.count, key_off=r.key_off,
+                                     key_bytes=r.key_bytes)
 
     def partition_cursor(self, p):
         for part, key, count in zip(self.rows_.part, self.rows_.keys(), self.rows_.count):
@@ -198,3 +214,40 @@ def test_a_second_worker_on_the_board_is_refused_and_the_result_is_whole(tmp_pat
     assert runs == [list(zip(want.keys(), (int(c) for c in want.count)))]       # whole, not one worker's share
     assert len(errors) == 1 and "already runs this task's data plane" in str(errors[0])
     assert stand_in.created == 1                                                 # the refused worker never made a context
+
+
+def test_many_workers_share_a_board_through_run_files(tmp_path, stand_in):
+    # storage "shared:<dir>": the reference's deployment -- N workers per board, mappers and reducers meet
+    # through map_results.P<p>.M<worker> files (job.lua:208-221, 253-265).  Whoever claims what, the result
+    # is whole, every reduce job read every run of its partition, and the runs are gone afterwards.
+    texts = [b"a b a\n", b"b c\n", b"c d a\n", b"e \"q\" back\\slash\n", b"", b"a " * 50] * 5
+    want = O.run_naive(texts, 15)
+    expect = list(zip(want.keys(), (int(c) for c in want.count)))
+    store = tmp_path / "runs"
+    stand_in.default_delay = 0.01
+    for loops in (1, 2):
+        runs = []
+        db = f"cpu-shared-{loops}"
+        s = mapreduce.server.new("localhost", db)
+        s.configure({"taskfn": WordCount, "mapfn": WordCount, "partitionfn": WordCount, "reducefn": WordCount,
+                     "combinerfn": WordCount, "finalfn": final_collect(runs, loops=loops), "storage": f"shared:{store}",
+                     "init_args": {"files": write_splits(tmp_path, texts), "num_reducers": 15}})
+        workers = [mapreduce.worker.new("localhost", db).configure({"max_iter": 4000, "max_tasks": loops}) for _ in range(3)]
+        errors = []
+
+        def go(w):
+            try:
+                w.execute()
+            except Exception as e:
+                errors.append(e)
+        threads = [threading.Thread(target=go, args=(w,), daemon=True) for w in workers]
+        for t in threads:
+            t.start()
+        stats = s.loop()
+        for t in threads:
+            t.join(30)
+            assert not t.is_alive()
+        assert not errors, errors
+        assert runs == [expect] * loops
+        assert stats["red_jobs"] == len(set(int(p) for p in want.part))
+        assert [n for n in os.listdir(store) if n.startswith("map_results")] == []      # consumed runs are removed
