@@ -347,6 +347,10 @@ def run_workload(env, args, splits, tokens_local, union_splits, steps, warmup, w
     clocks = sampler.stop() if rank == 0 else None
     info = ctx.job_sync()
     assert info.n_tokens == tokens_local and int(info.n_keys) == rows_n
+    flags = torch.tensor([int(info.flags) & 3], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(flags, op=dist.ReduceOp.MAX)
+    reduce_path = "lsd radix (reduce_kernels.cuh) on at least one rank" if int(flags.item()) & 1 else "msd units (msd_kernels.cuh) on every rank"
     ms_total = t_start.elapsed_time(t_end)
     map_ms = [ev[s][0].elapsed_time(ev[s][1]) for s in range(steps)]
     red_ms = [ev[s][1].elapsed_time(ev[s][2]) for s in range(steps)]
@@ -360,7 +364,7 @@ def run_workload(env, args, splits, tokens_local, union_splits, steps, warmup, w
            "tokens_total": tokens_total, "bytes_total": bytes_total, "rows_total": rows_total,
            "keybytes_total": keybytes_total, "tokens_local": tokens_local, "bytes_local": bytes_local,
            "rows_n": rows_n, "key_bytes": key_bytes, "launches": launches, "clocks": clocks, "parity": parity,
-           "owners": owners, "shuffle_kind": shuffle_kind[0], "shuffle_stats": shuffle_stats, "e2e": None,
+           "owners": owners, "shuffle_kind": shuffle_kind[0], "reduce_path": reduce_path, "shuffle_stats": shuffle_stats, "e2e": None,
            "nsplits_local": len(splits)}
 
     # ---- end to end through the public API: host buffers in, rows out, every step
@@ -508,7 +512,7 @@ def run_ours(args, out):
                   "distinct_keys": s3["rows_total"], "splits_on_rank0": s3["nsplits_local"],
                   "ms_per_step": s3["ms_step"], "value": s3["tokens_total"] / (s3["ms_step"] * 1e-3), "unit": UNIT,
                   "steps": steps3, "warmup": warm3, "map_ms_max": s3["map_ms_max"],
-                  "exchange_and_reduce_ms_rank0": s3["red_ms"],
+                  "exchange_and_reduce_ms_rank0": s3["red_ms"], "reduce_path": s3["reduce_path"],
                   "efficiency_vs_n1_ms": "t_1 / (N * ms_per_step), t_1 = this field of the N=1 line",
                   "parity_check": s3["parity"]}
 
@@ -577,6 +581,7 @@ def run_ours(args, out):
                    "tokens": m["tokens_total"], "input_bytes": m["bytes_total"], "distinct_keys": m["rows_total"],
                    "partitions": R, "seed": hex(SEED), "parallelism": f"splits sharded over {world} rank(s), "
                    f"owner = {m['owners']}" + (f", shuffle = {m['shuffle_kind']}" if world > 1 else ""),
+                   "reduce_path": m["reduce_path"],
                    "l2": "input per rank (294 MB) is larger than L2 (126 MB); no flush between steps"},
         "roofline": roofline, "nvlink": nvlink, "cpu_baseline": cpu, "e2e": m["e2e"], "gpu_launches": m["launches"],
         "clocks": m["clocks"], "parity_check": m["parity"], "strong_config3": strong,

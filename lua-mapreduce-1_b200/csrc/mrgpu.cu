@@ -44,7 +44,7 @@ __global__ void ctl_job_reset_kernel(Ctl *ctl)
     uint32_t *w = (uint32_t *)ctl;
     for (uint32_t i = threadIdx.x; i < sizeof(Ctl) / 4; i += blockDim.x) w[i] = 0;
     __syncthreads();
-    if (threadIdx.x == 0) { ctl->and_lo = ~0ull; ctl->and_hi = ~0u; }
+    if (threadIdx.x == 0) { ctl->and_lo = ~0ull; ctl->and_hi = ~0u; ctl->part_min = ~0u; }
 }
 
 __global__ void ctl_init_kernel(Ctl *ctl)
@@ -52,6 +52,7 @@ __global__ void ctl_init_kernel(Ctl *ctl)
     // everything else was zeroed by the memset before this launch
     ctl->and_lo = ~0ull;
     ctl->and_hi = ~0u;
+    ctl->part_min = ~0u;
 }
 
 __global__ void ctl_set_n_kernel(Ctl *ctl, unsigned long long n) { ctl->n = n; }
@@ -74,6 +75,7 @@ __global__ void ctl_owner_reset_kernel(Ctl *ctl)
 {
     ctl->n = 0;
     ctl->or_lo = 0; ctl->and_lo = ~0ull; ctl->or_hi = 0; ctl->and_hi = ~0u;
+    ctl->part_min = ~0u; ctl->part_max = 0;
     ctl->npasses = 0;
     for (int i = 0; i < 56; ++i) (&ctl->occ[0][0])[i] = 0;
     ctl->n_tie = 0; ctl->tie_overflow = 0; ctl->tie_small = 0; ctl->rows_ticket = 0;

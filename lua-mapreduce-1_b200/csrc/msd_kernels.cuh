@@ -81,10 +81,13 @@ __host__ __device__ __forceinline__ uint32_t bits_for(uint32_t card) // bits tha
 
 // The plan from the occupancy masks (occ[p][8] = 256-bit mask of the byte values at key byte p), the
 // partition count and the number of items.
-__host__ __device__ inline void msd_build_plan(const unsigned int (*occ)[8], uint32_t num_reducers, unsigned long long n,
-                                               MsdPlan *p)
+__host__ __device__ inline void msd_build_plan(const unsigned int (*occ)[8], uint32_t part_min, uint32_t part_max,
+                                               unsigned long long n, MsdPlan *p)
 {
-    p->card[0] = num_reducers;
+    // the partitions PRESENT, not num_reducers: a rank of many owns a key range of one or two partitions,
+    // and bins spent on the others would leave its own too crowded
+    p->part_base = part_min <= part_max ? part_min : 0;
+    p->card[0] = part_min <= part_max ? part_max - part_min + 1 : 1;
     for (int f = 0; f < 7; ++f) {
         uint32_t c = 0;
         for (int w = 0; w < 8; ++w) c += popc32_hd(occ[f][w]);
@@ -113,6 +116,7 @@ __host__ __device__ inline void msd_build_plan(const unsigned int (*occ)[8], uin
     p->low_bits = low_bits;
     p->fallback = low_bits > 64 ? MSD_FB_WIDE : 0;
     p->pad[0] = p->pad[1] = p->pad[2] = 0;
+    p->pad2 = 0;
 }
 
 // rank of byte value v under a 256-bit occupancy mask: how many occurring values are smaller
@@ -131,7 +135,7 @@ __host__ __device__ __forceinline__ void msd_extract(const MsdPlan &p, const uns
                                                      const unsigned char *lutk = nullptr)
 {
     uint32_t rank[MSD_FIELDS];
-    rank[0] = hi;
+    rank[0] = hi - p.part_base;
 #pragma unroll
     for (int f = 0; f < 7; ++f) rank[1 + f] = lut[f][(uint32_t)(lo >> (56 - 8 * f)) & 0xFFu];
     rank[8] = (uint32_t)lo & 0xFFu;
@@ -188,7 +192,7 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
     }
     if (threadIdx.x < 56) (&s_occ[0][0])[threadIdx.x] = (&ctl->occ[0][0])[threadIdx.x];
     __syncthreads();
-    if (threadIdx.x == 0) msd_build_plan(s_occ, num_reducers, n, &plan);
+    if (threadIdx.x == 0) msd_build_plan(s_occ, ctl->part_min, ctl->part_max, n, &plan);
     for (int f = 0; f < 7; ++f) lut[f][threadIdx.x] = (unsigned char)msd_rank_of(s_occ[f], threadIdx.x);   // 256 threads
     __syncthreads();
     {
@@ -481,7 +485,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
     const bool early = distinct && plan_k >= 1 && !sm.inexact && !sm.fallback;
     if (early && warp == 0) {
         const uint32_t bpp = bins / ctl->msd_plan.card[0];
-        lookback(m, sm.sumlen, m ? (unsigned long long)((dfirst + maxl) / bpp + 1u) : 0ull);
+        lookback(m, sm.sumlen, m ? (unsigned long long)((dfirst + maxl) / bpp + ctl->msd_plan.part_base + 1u) : 0ull);
     }
 
     uint32_t cur = 0;

@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(256) p2p_index_kernel(const uint8_t *buf, cons
         s_n = mine; s_base = base; s_ok = ok;
     }
     __syncthreads();
-    uint32_t hi_or = 0, hi_and = ~0u;
+    uint32_t hi_or = 0, hi_and = ~0u, pmin = ~0u, pmax = 0;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
     if (s_ok && s_n) {
@@ -263,11 +263,12 @@ __global__ void __launch_bounds__(256) p2p_index_kernel(const uint8_t *buf, cons
             SortItem it; it.lo = ck; it.hi = part; it.val = (uint32_t)(ent0 + first + i);
             items[base + i] = it;
             hi_or |= part; hi_and &= part; lo_or |= ck; lo_and &= ck;
+            pmin = min(pmin, part); pmax = max(pmax, part);
             occ_add(s_occ, ck);
             any = true;
         }
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ);
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ, pmin, pmax);
 }
 
 } // namespace mr

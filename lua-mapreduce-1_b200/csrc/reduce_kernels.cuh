@@ -46,16 +46,18 @@ struct __align__(16) SortItem {
 // fields k..8 ("low").
 constexpr int MSD_FIELDS = 9;
 struct MsdPlan {
-    uint32_t nbins, k, e, low_bits, fallback;
+    uint32_t nbins, k, e, low_bits, fallback, part_base;   // part_base: the smallest partition present (field 0 counts from it)
     uint32_t card[MSD_FIELDS];      // values a field can take (partition: num_reducers; bytes: occurring values; length: 9)
     uint8_t width[MSD_FIELDS];      // bits of a field's rank in the packed low word
     uint8_t pad[3];
+    uint32_t pad2;
 };
 
 struct Ctl {
     unsigned long long n;            // entries (distinct keys before the merge)
     unsigned long long or_lo, and_lo;
     unsigned int or_hi, and_hi;
+    unsigned int part_min, part_max; // smallest / largest partition among the sort items (starts at ~0 / 0), for the MSD plan
     unsigned int occ[7][8];          // byte values that occur at key byte 0..6 (256-bit masks), for the MSD plan
     unsigned int npasses;
     unsigned int err;
@@ -138,11 +140,17 @@ __device__ __forceinline__ void occ_add(unsigned int *s_occ, unsigned long long 
 }
 
 __device__ __forceinline__ void orand_commit(Ctl *ctl, uint32_t hi_or, uint32_t hi_and,
-                                             uint64_t lo_or, uint64_t lo_and, bool any, const unsigned int *s_occ = nullptr)
+                                             uint64_t lo_or, uint64_t lo_and, bool any, const unsigned int *s_occ = nullptr,
+                                             uint32_t pmin = ~0u, uint32_t pmax = 0)
 {
     if (s_occ) {
         __syncthreads();
         if (threadIdx.x < 56 && s_occ[threadIdx.x]) atomicOr(&ctl->occ[0][0] + threadIdx.x, s_occ[threadIdx.x]);
+        for (int d = 16; d; d >>= 1) {
+            pmin = min(pmin, __shfl_xor_sync(0xFFFFFFFFu, pmin, d));
+            pmax = max(pmax, __shfl_xor_sync(0xFFFFFFFFu, pmax, d));
+        }
+        if ((threadIdx.x & 31) == 0 && pmin <= pmax) { atomicMin(&ctl->part_min, pmin); atomicMax(&ctl->part_max, pmax); }
     }
     // warp-reduce, block-reduce, then one set of atomics per CTA (same-address atomics serialise)
     __shared__ uint32_t s_hi_or[8], s_hi_and[8], s_any[8];
@@ -198,7 +206,7 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t tile_slots = 256 * ITEMS;
     const uint64_t ntiles = (nslots + tile_slots - 1) / tile_slots;
-    uint32_t hi_or = 0, hi_and = ~0u;
+    uint32_t hi_or = 0, hi_and = ~0u, pmin = ~0u, pmax = 0;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
     for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -246,12 +254,13 @@ __global__ void __launch_bounds__(256) compact_partition_kernel(
             items[idx] = it;
             lens[idx] = key_len(key);              // for the MSD path of jobs without a shuffle (msd_kernels.cuh)
             hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
+            pmin = min(pmin, part); pmax = max(pmax, part);
             occ_add(s_occ, chunk);
             any = true;
         }
         __syncthreads();
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ);
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ, pmin, pmax);
 }
 
 // dense entries -> partition id + sort item (+ which key bits vary at all)
@@ -263,7 +272,7 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
 {
     __shared__ unsigned int s_occ[56];
     occ_clear(s_occ);
-    uint32_t hi_or = 0, hi_and = ~0u;
+    uint32_t hi_or = 0, hi_and = ~0u, pmin = ~0u, pmax = 0;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
     const uint64_t n = ctl->n < max_keys ? ctl->n : max_keys;
@@ -277,10 +286,11 @@ __global__ void __launch_bounds__(256) partition_entries_kernel(
         SortItem it; it.lo = chunk; it.hi = part; it.val = (uint32_t)idx;
         items[idx] = it;
         hi_or |= part; hi_and &= part; lo_or |= chunk; lo_and &= chunk;
+        pmin = min(pmin, part); pmax = max(pmax, part);
         occ_add(s_occ, chunk);
         any = true;
     }
-    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ);
+    orand_commit(ctl, hi_or, hi_and, lo_or, lo_and, any, s_occ, pmin, pmax);
 }
 
 // ------------------------------------------------------------------ K5 radix sort
@@ -700,7 +710,7 @@ __global__ void __launch_bounds__(256) rekey_kernel(SortBufs bufs, uint32_t roun
 {
     const SortItem *src = bufs.item[ctl->npasses & 1];
     SortItem *dst = bufs.item[0];
-    uint32_t hi_or = 0, hi_and = ~0u;
+    uint32_t hi_or = 0, hi_and = ~0u, pmin = ~0u, pmax = 0;
     uint64_t lo_or = 0, lo_and = ~0ull;
     bool any = false;
     const uint64_t n = ctl->n < max_keys ? ctl->n : max_keys;

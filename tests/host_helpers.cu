@@ -161,7 +161,7 @@ uint32_t th_msd_extract(const uint32_t *occ /* [7][8] */, uint32_t num_reducers,
 {
     MsdPlan p;
     memset(&p, 0, sizeof p);
-    msd_build_plan((const unsigned int (*)[8])occ, num_reducers, n, &p);
+    msd_build_plan((const unsigned int (*)[8])occ, 0, num_reducers - 1, n, &p);
     out[0] = p.nbins; out[1] = p.k; out[2] = p.e; out[3] = p.low_bits; out[4] = p.fallback;
     static unsigned char lut[7][256];
     for (int f = 0; f < 7; ++f)
