@@ -347,10 +347,12 @@ def run_workload(env, args, splits, tokens_local, union_splits, steps, warmup, w
     clocks = sampler.stop() if rank == 0 else None
     info = ctx.job_sync()
     assert info.n_tokens == tokens_local and int(info.n_keys) == rows_n
-    flags = torch.tensor([int(info.flags) & 3], dtype=torch.int64, device=dev)
+    flags = torch.tensor([int(info.flags) & 3, int(info.flags) >> 8], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(flags, op=dist.ReduceOp.MAX)
-    reduce_path = "lsd radix (reduce_kernels.cuh) on at least one rank" if int(flags.item()) & 1 else "msd units (msd_kernels.cuh) on every rank"
+    reduce_path = "msd units (msd_kernels.cuh) on every rank"
+    if int(flags[0].item()) & 1:
+        reduce_path = f"lsd radix (reduce_kernels.cuh) on at least one rank (msd decline bits {int(flags[1].item())})"
     ms_total = t_start.elapsed_time(t_end)
     map_ms = [ev[s][0].elapsed_time(ev[s][1]) for s in range(steps)]
     red_ms = [ev[s][1].elapsed_time(ev[s][2]) for s in range(steps)]

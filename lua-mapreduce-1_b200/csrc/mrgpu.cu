@@ -312,7 +312,8 @@ struct mr_ctx {
     Ctl *h_ctl = nullptr; // pinned
     MsdBins *d_msd = nullptr; // [2], alternating by job (msd_kernels.cuh)
     uint32_t msd_parity = 0;
-    bool prefer_lsd = false;  // the MSD path declined a job of this context: later jobs take the LSD path at once
+    bool prefer_lsd = false;  // MRGPU_REDUCE=lsd: always the LSD path
+    uint32_t lsd_jobs_left = 0; // the MSD path declined a job: the next few jobs take the LSD path at once, then it is tried again
     bool used_msd = false;    // this job's reduce side was launched on the MSD path
     unsigned long long *h_stage = nullptr; // pinned, [MAX_WORLD + 1]
     const uint8_t *bytes_base = nullptr;
@@ -1177,9 +1178,10 @@ int mr_reduce_all(mr_ctx *ctx)
     CU(cudaEventRecord(ctx->ev_red0, ctx->stream));
     int rc;
     if (!ctx->imported) { if ((rc = launch_compact(ctx))) return rc; }
-    if (!ctx->prefer_lsd) {
+    if (!ctx->prefer_lsd && ctx->lsd_jobs_left == 0) {
         if ((rc = launch_msd(ctx))) return rc;
     } else {
+        if (ctx->lsd_jobs_left) --ctx->lsd_jobs_left;
         if ((rc = launch_sort(ctx))) return rc;
         if ((rc = launch_rows(ctx, true))) return rc;
     }
@@ -1204,7 +1206,7 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
             flags = MR_JOB_REDUCED_LSD | MR_JOB_MSD_DECLINED | (ctx->h_ctl->msd_fallback << 8);
             // the MSD path declined (msd_kernels.cuh, "fallback"): the whole reduce side again on the LSD
             // path, from the untouched sort items; later jobs of this context start there
-            ctx->prefer_lsd = true;
+            ctx->lsd_jobs_left = 3;   // a job shape that does not fit usually comes back; but owners, sizes and keys change
             ctx->used_msd = false;
             CU(cudaMemsetAsync(&ctx->d_ctl->n_tie, 0, offsetof(Ctl, n_out) - offsetof(Ctl, n_tie), ctx->stream));
             if ((rc = launch_sort(ctx))) return rc;
@@ -1853,6 +1855,7 @@ int mr_shuffle_set_owners(mr_ctx *ctx, uint32_t n, const uint32_t *part, const u
     CU(cudaStreamSynchronize(ctx->stream)); // earlier jobs may still read the old splitters
     ctx->split_part.assign(part, part + n);
     ctx->split_word.assign(word, word + n);
+    ctx->lsd_jobs_left = 0;   // other keys will arrive here from now on: the shared-memory reduce path gets a fresh try
     if (n) {
         CU(cudaMemcpy(ctx->d_split_part, part, n * sizeof(uint32_t), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(ctx->d_split_word, word, n * sizeof(uint64_t), cudaMemcpyHostToDevice));

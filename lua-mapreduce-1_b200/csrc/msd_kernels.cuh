@@ -25,7 +25,7 @@
 // overwrite) when the packed low bits exceed 64, a bin holds more than UNIT_CAP - UNIT_W items
 // (many more keys than 2^15 bins can spread, or keys that only differ late), or a group of keys
 // equal in their first 7 bytes has more than MSD_TIE_GROUP members (copies of a key from several ranks count).  mr_job_sync then runs the LSD
-// path; a context that declined once goes straight to the LSD path afterwards.
+// path, and so do the context's next three jobs before the MSD path is tried again.
 #pragma once
 #include "reduce_kernels.cuh"
 

@@ -152,7 +152,11 @@ def corpus_shards(W):
     return shards
 
 
-@pytest.mark.parametrize("transport", ["p2p", "fixed", "exact"])
+# (The peer-to-peer windows are left to boxes with one GPU per rank -- tests/mp_gpu_parity.py and the parity
+# check inside bench.py at N = 2, 4, 8: an owner's kernel waits ON the GPU for its peers' records, and
+# ranks that share one GPU can starve each other's kernels for as long as that wait lasts.  What
+# happens after the records have arrived is the same code for all three transports.)
+@pytest.mark.parametrize("transport", ["fixed", "exact"])
 @pytest.mark.parametrize("balanced", [False, True])
 def test_two_ranks_on_one_device(transport, balanced):
     shards = corpus_shards(2)
@@ -180,6 +184,6 @@ def test_long_keys_meet_at_their_owner():
     def text(seed):
         r = np.random.RandomState(seed)
         return b" ".join(words[j] for j in r.randint(0, len(words), size=5000))
-    for transport in ("p2p", "fixed", "exact"):
+    for transport in ("fixed", "exact"):
         want, sent = run_ranks([[text(1)], [text(2)]], 10, transport, balanced=True, jobs=1)
         assert sent > 1.8 * want.n

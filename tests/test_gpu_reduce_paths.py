@@ -54,7 +54,7 @@ def both(splits, R, expect_msd=True, **kw):
     if expect_msd:
         assert fa == 0 and fa2 == 0, f"the shared-memory path declined: flags {fa:#x}"
     else:
-        assert fa & DECLINED and fa2 == LSD      # declined once, later jobs go straight to the LSD path
+        assert fa & DECLINED and fa2 == LSD      # declined once: the next jobs go straight to the LSD path
     return fa
 
 
