@@ -313,7 +313,7 @@ struct mr_ctx {
     MsdBins *d_msd = nullptr; // [2], alternating by job (msd_kernels.cuh)
     uint32_t msd_parity = 0;
     bool prefer_lsd = false;  // MRGPU_REDUCE=lsd: always the LSD path
-    uint32_t lsd_jobs_left = 0; // the MSD path declined a job: the next few jobs take the LSD path at once, then it is tried again
+    uint32_t lsd_jobs_left = 0; // non-zero: the MSD path declined a job of this context; its jobs take the LSD path at once until the owners change
     bool used_msd = false;    // this job's reduce side was launched on the MSD path
     unsigned long long *h_stage = nullptr; // pinned, [MAX_WORLD + 1]
     const uint8_t *bytes_base = nullptr;
@@ -1055,22 +1055,33 @@ int launch_sort(mr_ctx *ctx)
 int launch_msd(mr_ctx *ctx)
 {
     cudaStream_t s = ctx->stream;
-    static_assert(sizeof(UnitSmem) <= 55 * 1024, "four units per SM");
+    using SmemD = UnitSmem<UNIT_CAP_DISTINCT>;
+    using SmemS = UnitSmem<UNIT_CAP_SHUFFLED>;
+    static_assert(sizeof(SmemD) <= 55 * 1024, "four units per SM");
+    static_assert(sizeof(SmemS) <= 74 * 1024, "three units per SM");
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
-    CU(cudaFuncSetAttribute(msd_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UnitSmem)));
+    CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_DISTINCT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemD)));
+    CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_SHUFFLED, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemS)));
     // no shuffle: the items are the table's entries, one per distinct key, so every item becomes a row
     // (the compaction kernel left the key lengths in d_ties, which only the LSD path's tie kernels use)
     const bool distinct = !ctx->imported && getenv("MRGPU_MSD_LOOKBACK") == nullptr;
+    const bool small_units = !ctx->imported;   // after a shuffle every key arrives once per rank: larger units
     MsdBins *mb = ctx->d_msd + ctx->msd_parity, *other = ctx->d_msd + (ctx->msd_parity ^ 1);
     ctx->msd_parity ^= 1;
     msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 4, ctx->sm_count * 4), 256, 0, s>>>(
         ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles);
     msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024 * 4, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
-        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb, distinct ? (const uint32_t *)ctx->d_ties : nullptr);
+        ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb, distinct ? (const uint32_t *)ctx->d_ties : nullptr,
+        (small_units ? UNIT_CAP_DISTINCT : UNIT_CAP_SHUFFLED) - UNIT_W);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
-    msd_unit_kernel<<<units, UNIT_THREADS, sizeof(UnitSmem), s>>>(
-        (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
-        ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb, distinct);
+    if (small_units)
+        msd_unit_kernel<UNIT_CAP_DISTINCT, 4><<<units, UNIT_THREADS, sizeof(SmemD), s>>>(
+            (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
+            ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb, distinct);
+    else
+        msd_unit_kernel<UNIT_CAP_SHUFFLED, 3><<<units, UNIT_THREADS, sizeof(SmemS), s>>>(
+            (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
+            ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb, distinct);
     ctx->stats.launches += 3;
     if (ctx->cfg.reduce_kind == MR_REDUCE_MIN_U64) {
         rows_decode_kernel<<<grid_for(ctx->max_keys, 256, ctx->sm_count * 4), 256, 0, s>>>(ctx->rows, ctx->cfg.reduce_kind, ctx->d_ctl);
@@ -1181,7 +1192,6 @@ int mr_reduce_all(mr_ctx *ctx)
     if (!ctx->prefer_lsd && ctx->lsd_jobs_left == 0) {
         if ((rc = launch_msd(ctx))) return rc;
     } else {
-        if (ctx->lsd_jobs_left) --ctx->lsd_jobs_left;
         if ((rc = launch_sort(ctx))) return rc;
         if ((rc = launch_rows(ctx, true))) return rc;
     }
@@ -1206,7 +1216,7 @@ int mr_job_sync(mr_ctx *ctx, mr_job_info *info)
             flags = MR_JOB_REDUCED_LSD | MR_JOB_MSD_DECLINED | (ctx->h_ctl->msd_fallback << 8);
             // the MSD path declined (msd_kernels.cuh, "fallback"): the whole reduce side again on the LSD
             // path, from the untouched sort items; later jobs of this context start there
-            ctx->lsd_jobs_left = 3;   // a job shape that does not fit usually comes back; but owners, sizes and keys change
+            ctx->lsd_jobs_left = ~0u; // a job shape that does not fit comes back: the LSD path from now on (new owners reset this)
             ctx->used_msd = false;
             CU(cudaMemsetAsync(&ctx->d_ctl->n_tie, 0, offsetof(Ctl, n_out) - offsetof(Ctl, n_tie), ctx->stream));
             if ((rc = launch_sort(ctx))) return rc;

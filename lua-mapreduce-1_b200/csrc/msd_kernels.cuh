@@ -25,7 +25,8 @@
 // overwrite) when the packed low bits exceed 64, a bin holds more than UNIT_CAP - UNIT_W items
 // (many more keys than 2^15 bins can spread, or keys that only differ late), or a group of keys
 // equal in their first 7 bytes has more than MSD_TIE_GROUP members (copies of a key from several ranks count).  mr_job_sync then runs the LSD
-// path, and so do the context's next three jobs before the MSD path is tried again.
+// path, and so do the context's later jobs (every job is then complete without a host round trip) until
+// its owner ranks are set anew.
 #pragma once
 #include "reduce_kernels.cuh"
 
@@ -33,12 +34,14 @@ namespace mr {
 
 constexpr int MSD_MAX_BITS = 15;
 constexpr uint32_t MSD_MAX_BINS = 1u << MSD_MAX_BITS;
-constexpr uint32_t MSD_TARGET_BIN = 8;       // items per bin aimed at (a bin may hold up to UNIT_CAP - UNIT_W: room for 64x skew)
+constexpr uint32_t MSD_TARGET_BIN = 8;       // items per bin aimed at (a bin may hold up to the unit size - UNIT_W: room for 64x skew)
 constexpr uint32_t UNIT_W = 512;             // a unit owns the bins that start inside its 512 positions
-constexpr uint32_t UNIT_CAP = 1024;          // ... so it holds fewer than UNIT_W + largest bin items
+// ... so it holds fewer than UNIT_W + largest bin items.  Two sizes of unit: jobs without a shuffle
+// (every key once) get four 1024-item units per SM; after a shuffle a key arrives from every rank, bins
+// are that much fuller where the vocabulary is crowded, and the units hold 1536 (three per SM).
+constexpr uint32_t UNIT_CAP_DISTINCT = 1024, UNIT_CAP_SHUFFLED = 1536;
 constexpr int UNIT_THREADS = 256;
 constexpr int UNIT_WARPS = UNIT_THREADS / 32;
-constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS; // 4
 constexpr uint32_t UNIT_STAGE = 12 * 1024 - 16;   // key bytes of a unit staged for coalesced stores (more: written directly)
 constexpr uint32_t UNIT_COUNT_SORT_MAX = 192; // bins up to this size are ordered by counting inside the bin
 constexpr uint32_t MSD_TIE_GROUP = 64;        // keys equal in their first 7 bytes (copies of one key included) a unit orders itself
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
 
 // ------------------------------------------------------------------ scatter
 __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, const uint32_t *tags, MsdItem *out, Ctl *ctl,
-                                                           MsdBins *mb, const uint32_t *lens)
+                                                           MsdBins *mb, const uint32_t *lens, uint32_t max_bin)
 {
     extern __shared__ unsigned int msd_start[];    // [bins + 1]
     __shared__ unsigned int wsum[32];
@@ -271,7 +274,7 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
     if (lane == 31) wsum[warp] = incl;
-    if (big > UNIT_CAP - UNIT_W) atomicOr(&s_big, 1u);
+    if (big > max_bin) atomicOr(&s_big, 1u);
     __syncthreads();
     unsigned int woff = 0;
     for (uint32_t w = 0; w < warp; ++w) woff += wsum[w];
@@ -323,9 +326,10 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
 }
 
 // ------------------------------------------------------------------ units: sort, merge, rows
+template <uint32_t UNIT_CAP>
 struct __align__(16) UnitSmem {
-    MsdItem buf[2][UNIT_CAP];                    // 64 KB: ping-pong of the passes; afterwards buf[other] holds the keys
-    unsigned int whist[UNIT_WARPS][RADIX_BINS];  // 16 KB: per-warp digit counts; afterwards the counts of the items
+    MsdItem buf[2][UNIT_CAP];                    // ping-pong of the sort; afterwards buf[other] holds the keys
+    unsigned int whist[UNIT_CAP * 2 > UNIT_WARPS * RADIX_BINS ? UNIT_CAP * 2 : UNIT_WARPS * RADIX_BINS]; // bin extents, per-warp digit counts [UNIT_WARPS][RADIX_BINS], afterwards the values of the items
     unsigned int bin_excl[RADIX_BINS];
     unsigned int scan_tmp[RADIX_BINS / 32];
     uint8_t stage[UNIT_STAGE + 16];              // key bytes of the unit's rows, back to back from offset 0
@@ -335,7 +339,6 @@ struct __align__(16) UnitSmem {
     unsigned int prefix_part, unit, first, count, dfirst, fallback, maxbin, inexact;
     unsigned long long sumlen;
 };
-static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned long long) * UNIT_CAP, "counts fit where the warp histograms were");
 
 #ifdef MRGPU_UNIT_TIMING   // build with -DMRGPU_UNIT_TIMING=<unit>: globaltimer stamps of that unit's phases in Ctl::dbg
 #define UT(k) do { if (threadIdx.x == 0 && sm.unit == (MRGPU_UNIT_TIMING)) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); ctl->dbg[k] = (long long)t_; } } while (0)
@@ -345,13 +348,16 @@ static_assert(sizeof(unsigned int) * UNIT_WARPS * RADIX_BINS >= sizeof(unsigned 
 #define UT0 do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
+template <uint32_t UNIT_CAP, int MIN_CTAS>
+__global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const MsdItem *in, EntryArrays ent, const uint8_t *bytes,
                                                                 RowArrays rows, uint32_t num_reducers, uint32_t op,
                                                                 unsigned long long key_bytes_cap, RowsStatus st, Ctl *ctl,
                                                                 MsdBins *mb, bool distinct)
 {
     extern __shared__ __align__(16) uint8_t unit_smem_raw[];
-    UnitSmem &sm = *(UnitSmem *)unit_smem_raw;
+    constexpr int UNIT_ITEMS = UNIT_CAP / UNIT_THREADS;
+    using Smem = UnitSmem<UNIT_CAP>;
+    Smem &sm = *(Smem *)unit_smem_raw;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt = lanemask_lt();
     const unsigned long long n = ctl->n;
     if (tid == 0) {
@@ -389,7 +395,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
     UT(1);
 
     // ---- load; every item learns where its bin lies inside the unit
-    unsigned int *ext = &sm.whist[0][0];            // [i] = bin begin | bin size << 16 (free until the passes / the counts)
+    unsigned int *ext = &sm.whist[0];            // [i] = bin begin | bin size << 16 (free until the passes / the counts)
     {
         uint32_t big = 0;
         unsigned long long lsum = 0;
@@ -526,7 +532,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
     // peer masks); every warp takes an equal share of the items, a multiple of 32
     const uint32_t blk = ((m + UNIT_WARPS * 32 - 1) / (UNIT_WARPS * 32)) * 32, rounds = blk / 32;
     for (uint32_t pass = 0; pass < (small_bins ? 0u : npass); ++pass) {
-        for (uint32_t i = tid; i < UNIT_WARPS * RADIX_BINS; i += UNIT_THREADS) (&sm.whist[0][0])[i] = 0;
+        for (uint32_t i = tid; i < UNIT_WARPS * RADIX_BINS; i += UNIT_THREADS) (&sm.whist[0])[i] = 0;
         __syncthreads();
         MsdItem it[UNIT_ITEMS];
         uint32_t dg[UNIT_ITEMS], rk[UNIT_ITEMS];
@@ -551,7 +557,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
             if (valid) {
                 const uint32_t leader = __ffs((int)peers) - 1;
                 uint32_t old = 0;
-                if (lane == leader) { old = sm.whist[warp][d]; sm.whist[warp][d] = old + __popc(peers); }
+                if (lane == leader) { old = sm.whist[warp * RADIX_BINS + d]; sm.whist[warp * RADIX_BINS + d] = old + __popc(peers); }
                 old = __shfl_sync(act, old, leader);
                 r = old + __popc(peers & lt);
             }
@@ -563,7 +569,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
         if (tid < RADIX_BINS) {
             unsigned int run = 0;
 #pragma unroll
-            for (int w = 0; w < UNIT_WARPS; ++w) { const unsigned int c = sm.whist[w][tid]; sm.whist[w][tid] = run; run += c; }
+            for (int w = 0; w < UNIT_WARPS; ++w) { const unsigned int c = sm.whist[w * RADIX_BINS + tid]; sm.whist[w * RADIX_BINS + tid] = run; run += c; }
             tcount = run;
             tincl = run;
 #pragma unroll
@@ -581,7 +587,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
         for (int i = 0; i < UNIT_ITEMS; ++i) {
             if ((uint32_t)i >= rounds) break;
             const uint32_t idx = wbase + i * 32 + lane;
-            if (idx < m) sm.buf[cur ^ 1][sm.bin_excl[dg[i]] + sm.whist[warp][dg[i]] + rk[i]] = it[i];
+            if (idx < m) sm.buf[cur ^ 1][sm.bin_excl[dg[i]] + sm.whist[warp * RADIX_BINS + dg[i]] + rk[i]] = it[i];
         }
         __syncthreads();
         cur ^= 1;
@@ -589,7 +595,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, 4) msd_unit_kernel(const MsdItem
     MsdItem *sorted = sm.buf[cur];
     UT(3);
     ulonglong2 *skey = (ulonglong2 *)sm.buf[cur ^ 1];       // (k0, k1) of sorted[i], filled below
-    unsigned long long *scnt = (unsigned long long *)&sm.whist[0][0];
+    unsigned long long *scnt = (unsigned long long *)&sm.whist[0];
 
     auto same_word = [&](uint32_t a, uint32_t b) { return sorted[a].low == sorted[b].low && sorted[a].bin == sorted[b].bin; };
     // ---- entries of the sorted items: one 32-byte gather each; key, value and partition stay in shared
