@@ -43,7 +43,7 @@ constexpr uint32_t UNIT_CAP_DISTINCT = 1024, UNIT_CAP_SHUFFLED = 1536;
 constexpr int UNIT_THREADS = 256;
 constexpr int UNIT_WARPS = UNIT_THREADS / 32;
 constexpr uint32_t UNIT_STAGE = 12 * 1024 - 16;   // key bytes of a unit staged for coalesced stores (more: written directly)
-constexpr uint32_t UNIT_COUNT_SORT_MAX = 192; // bins up to this size are ordered by counting inside the bin
+constexpr uint32_t UNIT_COUNT_SORT_MAX = 48;  // units whose largest bin is at most this: bins ordered by counting inside the bin (b compares per item); fuller ones: radix passes (~14 compares' worth per pass)
 constexpr uint32_t MSD_TIE_GROUP = 64;        // keys equal in their first 7 bytes (copies of one key included) a unit orders itself
 
 enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
