@@ -60,8 +60,21 @@ __global__ void __launch_bounds__(1024, 1) map_records_kernel(RecordsParams p)
             if (cur == sk) { way = q; break; }
         }
         const unsigned long long x = op_encode(p.op, v);
-        if (way >= 0) op_apply(&tsum[bucket * 4 + way], x, p.op);
-        else gtable_add(p.gtab, p.gmask, nullptr, key_of_u32(k), x, p.err, p.op);
+        if (way >= 0) {
+            unsigned long long *sum = &tsum[bucket * 4 + way];
+            if (p.op == OP_SUM || p.op == OP_COUNT) {
+                // a 64-bit shared-memory add is a compare-and-swap loop, and the heavy hitters send a
+                // quarter of all records to four addresses: two native 32-bit adds instead (x < 2^32;
+                // the low word's carry goes to the high word; the flush below reads them together)
+                const unsigned int lo = (unsigned int)x;
+                const unsigned int old = atomicAdd((unsigned int *)sum, lo);
+                if (old + lo < old) atomicAdd((unsigned int *)sum + 1, 1u);
+            } else {
+                op_apply(sum, x, p.op);
+            }
+        } else {
+            gtable_add(p.gtab, p.gmask, nullptr, key_of_u32(k), x, p.err, p.op);
+        }
     }
     for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d);
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(p.records, mine);
