@@ -1057,8 +1057,8 @@ int launch_msd(mr_ctx *ctx)
     cudaStream_t s = ctx->stream;
     using SmemD = UnitSmem<UNIT_CAP_DISTINCT>;
     using SmemS = UnitSmem<UNIT_CAP_SHUFFLED>;
-    static_assert(sizeof(SmemD) <= 55 * 1024, "four units per SM");
-    static_assert(sizeof(SmemS) <= 74 * 1024, "three units per SM");
+    static_assert(sizeof(SmemD) <= 56 * 1024 - 512, "four units per SM");
+    static_assert(sizeof(SmemS) <= 75 * 1024 - 256, "three units per SM");
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
     CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_DISTINCT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemD)));
     CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_SHUFFLED, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemS)));

@@ -43,7 +43,10 @@ constexpr uint32_t UNIT_CAP_DISTINCT = 1024, UNIT_CAP_SHUFFLED = 1536;
 constexpr int UNIT_THREADS = 256;
 constexpr int UNIT_WARPS = UNIT_THREADS / 32;
 constexpr uint32_t UNIT_STAGE = 12 * 1024 - 16;   // key bytes of a unit staged for coalesced stores (more: written directly)
-constexpr uint32_t UNIT_COUNT_SORT_MAX = 48;  // units whose largest bin is at most this: bins ordered by counting inside the bin (b compares per item); fuller ones: radix passes (~14 compares' worth per pass)
+#ifndef MRGPU_COUNT_SORT_MAX
+#define MRGPU_COUNT_SORT_MAX 48
+#endif
+constexpr uint32_t UNIT_COUNT_SORT_MAX = MRGPU_COUNT_SORT_MAX;  // units whose largest bin is at most this: bins ordered by counting inside the bin (b compares per item); fuller ones: radix passes (~14 compares' worth per pass)
 constexpr uint32_t MSD_TIE_GROUP = 64;        // keys equal in their first 7 bytes (copies of one key included) a unit orders itself
 
 enum : uint32_t { MSD_FB_WIDE = 1u, MSD_FB_BIN = 4u, MSD_FB_TIES = 8u };
@@ -338,6 +341,7 @@ struct __align__(16) UnitSmem {
     unsigned long long prefix_h, prefix_b;
     unsigned int prefix_part, unit, first, count, dfirst, fallback, maxbin, inexact;
     unsigned long long sumlen;
+    unsigned char iflag[UNIT_CAP];               // per item: continues its predecessor's word / another key; later: starts a row
 };
 
 #ifdef MRGPU_UNIT_TIMING   // build with -DMRGPU_UNIT_TIMING=<unit>: globaltimer stamps of that unit's phases in Ctl::dbg
@@ -609,82 +613,113 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
     }
     __syncthreads();
     UT(4);
-    // ---- keys that agree in the whole sort word and have 8+ bytes are ordered by their later bytes: the
-    // first member of such a group orders it in place (insertion sort, full-key compares out of shared
-    // memory).  Equal keys -- the same key from several ranks -- stay where they are and merge below.
+    // ---- keys that agree in the whole sort word and have 8+ bytes are ordered by their later bytes.
+    // First every item says (iflag) whether it continues its predecessor's sort word (1) and, if so,
+    // whether it is another key (2); only groups that hold different keys are ordered -- by their first
+    // member, in place (insertion sort, full-key compares out of shared memory).  Copies of one key,
+    // which is what a shuffle delivers most, cost one 16-byte compare each.
+    unsigned char *iflag = sm.iflag;
+    auto same_key_at = [&](uint32_t x, uint32_t y) {
+        const ulonglong2 ka = skey[x], kb = skey[y];
+        if (ka.x == kb.x && ka.y == kb.y) return true;
+        if ((ka.y >> 56) != 0xFFu) return false;          // inline keys: the 128 bits ARE the key
+        Key A, B; A.k0 = ka.x; A.k1 = ka.y; B.k0 = kb.x; B.k1 = kb.y;
+        return same_key(A, B, bytes);
+    };
     for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
-        if (!(sorted[i].bin & MSD_FLAG8)) continue;
-        if (i > 0 && same_word(i, i - 1)) continue;
-        uint32_t g = 1;
-        while (i + g < m && g <= MSD_TIE_GROUP && same_word(i, i + g)) ++g;
-        if (g == 1) continue;
-        if (g > MSD_TIE_GROUP) { atomicOr(&ctl->msd_fallback, MSD_FB_TIES); sm.fallback = 1; continue; }
-        bool moved = false;
-        for (uint32_t a = 1; a < g; ++a) {
-            const ulonglong2 kx2 = skey[i + a];
-            Key kx; kx.k0 = kx2.x; kx.k1 = kx2.y;
-            const unsigned long long cx = scnt[i + a];
-            const uint32_t px = sorted[i + a].val;
-            uint32_t b = a;
-            while (b > 0) {
-                Key kb; kb.k0 = skey[i + b - 1].x; kb.k1 = skey[i + b - 1].y;
-                if (!key_less(kx, kb, 1, 0, bytes, 1)) break;      // equal keys: "not less" (entry order 1 > 0), so they stay
-                skey[i + b] = skey[i + b - 1]; scnt[i + b] = scnt[i + b - 1]; sorted[i + b].val = sorted[i + b - 1].val;
-                --b;
-            }
-            if (b != a) { skey[i + b] = kx2; scnt[i + b] = cx; sorted[i + b].val = px; moved = true; }
-            else if (!moved) {
-                Key kp; kp.k0 = skey[i + a - 1].x; kp.k1 = skey[i + a - 1].y;
-                moved = !same_key(kx, kp, bytes);             // different keys that already stood in order
-            }
+        uint32_t f = 0;
+        if (i > 0 && same_word(i, i - 1)) {
+            f = 1;
+            if ((sorted[i].bin & MSD_FLAG8) && !same_key_at(i, i - 1)) f = 3;
         }
-        if (moved) atomicAdd(&ctl->tie_small, 1u);
+        iflag[i] = (unsigned char)f;
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+        if ((iflag[i] & 1) || !(sorted[i].bin & MSD_FLAG8)) continue;
+        uint32_t g = 1, need = 0;
+        while (i + g < m && g <= MSD_TIE_GROUP && (iflag[i + g] & 1)) { need |= iflag[i + g] & 2u; ++g; }
+        if (g > MSD_TIE_GROUP) { atomicOr(&ctl->msd_fallback, MSD_FB_TIES); sm.fallback = 1; continue; }
+        if (!need) continue;
+        for (uint32_t a2 = 1; a2 < g; ++a2) {
+            const ulonglong2 kx2 = skey[i + a2];
+            Key kx; kx.k0 = kx2.x; kx.k1 = kx2.y;
+            const unsigned long long cx = scnt[i + a2];
+            const uint32_t px = sorted[i + a2].val;
+            uint32_t b2 = a2;
+            while (b2 > 0) {
+                Key kb; kb.k0 = skey[i + b2 - 1].x; kb.k1 = skey[i + b2 - 1].y;
+                if (!key_less(kx, kb, 1, 0, bytes, 1)) break;      // equal keys: "not less", so they stay
+                skey[i + b2] = skey[i + b2 - 1]; scnt[i + b2] = scnt[i + b2 - 1]; sorted[i + b2].val = sorted[i + b2 - 1].val;
+                --b2;
+            }
+            if (b2 != a2) { skey[i + b2] = kx2; scnt[i + b2] = cx; sorted[i + b2].val = px; }
+        }
+        atomicAdd(&ctl->tie_small, 1u);
     }
     __syncthreads();
     // a unit that declined still takes part in the look-back below (with nothing), so that no later
     // unit waits for it; the rows are rewritten by the LSD path anyway
     const bool declined = sm.fallback != 0;
+    // heads (after the ordering): an item starts a row unless it repeats its predecessor's key
+    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+        bool head = i == 0 || !same_word(i, i - 1);   // the first item of a unit starts a bin: always a new key
+        if (!head && (sorted[i].bin & MSD_FLAG8)) head = !same_key_at(i, i - 1);
+        iflag[i] = head ? 4 : 0;
+    }
+    __syncthreads();
     UT(5);
     Key key[UNIT_ITEMS];
     uint32_t part[UNIT_ITEMS], len[UNIT_ITEMS];
+    uint32_t headmask = 0, nh = 0;
+    unsigned long long nb = 0;
 #pragma unroll
     for (int j = 0; j < UNIT_ITEMS; ++j) {
         const uint32_t i = base + j;
         part[j] = 0; len[j] = 0; key[j].k0 = 0; key[j].k1 = 0;
-        if (i < m) {
+        if (i < m && !declined) {
             key[j].k0 = skey[i].x; key[j].k1 = skey[i].y;
             part[j] = sorted[i].val;
             len[j] = key_len(key[j]);
+            if (iflag[i]) { headmask |= 1u << j; ++nh; nb += len[j]; }
         }
     }
-    // heads, and for every head the merged value of the equal keys that follow it (the same key from
-    // other ranks: merge_min_keys, utils.lua:232-247, with the job's reducer)
-    uint32_t headmask = 0, nh = 0;
-    unsigned long long nb = 0;
-    unsigned long long cval[UNIT_ITEMS];
+    // merged values (merge_min_keys, utils.lua:232-247, with the job's reducer): a thread folds the runs
+    // inside its own items; a run that began in an earlier thread's items gets this thread's part added
+    // atomically after the heads have stored theirs.  The sums live in the sorted items' `low` slots,
+    // whose sort words are not needed any more.
+    const bool additive = op == OP_SUM || op == OP_COUNT;
+    auto fold = [&](unsigned long long x, unsigned long long y) { return additive ? x + y : max(x, y); };
+    unsigned long long lead_acc = 0, acc = 0;
+    bool lead = false;
+    int open_j = -1;
 #pragma unroll
     for (int j = 0; j < UNIT_ITEMS; ++j) {
         const uint32_t i = base + j;
-        cval[j] = 0;
-        if (i >= m || declined) continue;
-        bool head = i == 0 || !same_word(i, i - 1);   // the first item of a unit starts a bin: always a new key
-        if (!head && (sorted[i].bin & MSD_FLAG8)) {
-            Key pk; pk.k0 = skey[i - 1].x; pk.k1 = skey[i - 1].y;
-            head = !same_key(key[j], pk, bytes);
+        if (i >= m || declined) break;
+        const unsigned long long v = scnt[i];
+        if ((headmask >> j) & 1u) {
+            if (open_j >= 0) sorted[base + open_j].low = acc;
+            open_j = j; acc = v;
+        } else if (open_j >= 0) {
+            acc = fold(acc, v);
+        } else {
+            lead_acc = lead ? fold(lead_acc, v) : v;
+            lead = true;
         }
-        if (!head) continue;
-        headmask |= 1u << j; ++nh; nb += len[j];
-        unsigned long long c = scnt[i];
-        for (uint32_t q = i + 1; q < m; ++q) {
-            if (!same_word(q, i)) break;
-            if (sorted[q].bin & MSD_FLAG8) {
-                Key a; a.k0 = skey[q].x; a.k1 = skey[q].y;
-                if (!same_key(a, key[j], bytes)) break;
-            }
-            c = (op == OP_SUM || op == OP_COUNT) ? c + scnt[q] : max(c, scnt[q]);
-        }
-        cval[j] = c;
     }
+    if (open_j >= 0) sorted[base + open_j].low = acc;
+    __syncthreads();
+    if (lead) {
+        uint32_t h = base - 1;                        // the run's head lies in an earlier thread's items
+        while (!iflag[h]) --h;
+        if (additive) atomicAdd(&sorted[h].low, lead_acc);
+        else atomicMax(&sorted[h].low, lead_acc);
+    }
+    __syncthreads();
+    unsigned long long cval[UNIT_ITEMS];
+#pragma unroll
+    for (int j = 0; j < UNIT_ITEMS; ++j) cval[j] = ((headmask >> j) & 1u) ? sorted[base + j].low : 0ull;
     uint32_t ih = nh;
     unsigned long long ib = nb;
 #pragma unroll

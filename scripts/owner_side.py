@@ -87,6 +87,16 @@ def main():
         times.append(e0.elapsed_time(e1) * 1e3)
     print(f"ranks {W}: owner 0 reduces {int(info.n_keys)} rows; reduce side per job (us): " + " ".join(f"{t:.0f}" for t in times)
           + f"; flags {int(info.flags):#x}")
+    L = _native.load()
+    if hasattr(L, "mr_debug_stamps"):        # a -DMRGPU_UNIT_TIMING=<unit> build: that unit's phases on owner 0
+        import ctypes as C
+        L.mr_debug_stamps.restype = C.POINTER(C.c_longlong)
+        L.mr_debug_stamps.argtypes = [C.c_void_p]
+        d = L.mr_debug_stamps(ctxs[0]._h)
+        st = [d[i] for i in range(16)]
+        names = ["start", "ticket+range", "load", "sort", "gather", "ties", "heads+merge+stage", "look-back", "rows", "copy-out"]
+        print("unit phases (us): starts %.2f after unit 0; " % ((st[0] - st[15]) / 1e3) +
+              "  ".join(f"{n} +{(st[k] - st[k - 1]) / 1e3:.2f}" for k, n in enumerate(names) if k) + f" | total {(st[9] - st[0]) / 1e3:.2f}")
     for c in ctxs:
         c.close()
 
