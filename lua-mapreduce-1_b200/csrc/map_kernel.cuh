@@ -59,10 +59,17 @@ struct __align__(16) WarpSmem {
     uint32_t stage[(SEG + SEG_AHEAD) / 4]; // 1056 B: the segment + 32 look-ahead bytes
     uint16_t list[SEG / 2];                // token entries (pos | len << 10): short tokens from the
                                            // front, medium tokens from the back (max one per 2 bytes)
-    Key gq[96];                            // keys waiting for the global table: < 64 after a drain
-                                           // (32 left + 32 re-queued at most), + 32 per iteration
-    unsigned long long longq[32];          // arena offsets of 16+ byte tokens
+    Key gq[63];                            // keys waiting for the global table: <= 31 after a drain, + 32 per iteration
+    unsigned long long longq[8];           // arena offsets of 16+ byte tokens
 };
+// The size of this block decides the kernel's speed in an unexpected way: 32 of them + the 96 KB table
+// must fit the SM's 196 KB shared-memory configuration, because the next one (228 KB) leaves 28 KB of
+// L1 -- too little for the loads a CTA of 32 warps keeps in flight (input sectors + one batch of table
+// probes per warp).  Measured on config 2: 525 us in the 228 KB configuration, 446 us in the 196 KB one
+// (profiles/r02/map_variants_3..5.txt, map_carveout*.txt; the same kernel forced back with
+// cudaFuncAttributePreferredSharedMemoryCarveout = 100 is slow again).
+static_assert(sizeof(WarpSmem) == 3152, "32 warps + the 96 KB table must fit the 196 KB shared-memory configuration");
+constexpr uint32_t GQ_KEEP = 32, LONGQ_DRAIN = 6;
 
 template <int LOG2_SLOTS>
 struct MapSmemLayout {
@@ -178,8 +185,11 @@ __device__ __forceinline__ void drain_long(const MapParams &p, WarpSmem *ws, uin
     }
 }
 
+#ifndef MRGPU_V_CTAS
+#define MRGPU_V_CTAS 1
+#endif
 template <int WARPS, int LOG2_SLOTS>
-__global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
+__global__ void __launch_bounds__(WARPS * 32, WARPS < 32 ? MRGPU_V_CTAS : 1) map_combine_kernel(MapParams p)
 {
     using L = MapSmemLayout<LOG2_SLOTS>;
     constexpr uint32_t SLOTS = L::SLOTS;
@@ -198,9 +208,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpSmem *ws = (WarpSmem *)(smem + L::warp_off) + warp;
 
+#ifdef MRGPU_MAP_TIMING
+    const long long mt_k0 = clock64();
+#endif
     for (uint32_t i = tid; i < SLOTS; i += WARPS * 32) { tkeys[i] = 0; tcnt[i] = 0; }
     if (tid == 0) tused = 0;
     __syncthreads();
+#ifdef MRGPU_MAP_TIMING
+    if (blockIdx.x == 7 && warp == 5 && lane == 0) p.dbg[8] = clock64() - mt_k0;
+#endif
 
     const uint32_t lt = lanemask_lt();
     uint32_t nq = 0, nlong = 0; // warp-uniform fills of gq / longq
@@ -350,7 +366,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             if (lane < c) ws->longq[nlong + lane] = base + srcl * 32 + __fns(sl, 0, lane + 1);
             nlong += c;
             __syncwarp();
-            if (nlong > 28) { drain_long(p, ws, nlong, lane); nlong = 0; __syncwarp(); }
+            if (nlong > LONGQ_DRAIN) { drain_long(p, ws, nlong, lane); nlong = 0; __syncwarp(); }
         }
         const bool can_insert = *(volatile unsigned int *)&tused < FILL_LIMIT; // warp-uniform
         uint32_t inserted = 0;
@@ -401,7 +417,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             nq += __popc(gm);
             __syncwarp();
             MT(2); // short tokens: key + CTA table
-            if (nq >= 32) { drain32(); while (nq >= 64) drain32(); MT(4); }
+            if (nq >= 32) { drain32(); while (nq >= GQ_KEEP) drain32(); MT(4); }
         }
 #ifdef MRGPU_V_ONEBYTE
         // ---- 3a'. tokens of one byte: the byte value is the counter index
@@ -417,7 +433,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
         for (uint32_t t0 = 0; t0 < n_med; t0 += 32) {
             const uint32_t j = t0 + lane;
 #ifdef MRGPU_V_DIRECTMED
-            if (n_med - t0 >= 32 && nq < 64) {
+            if (n_med - t0 >= 32 && nq < GQ_KEEP) {
                 const uint32_t e = ws->list[LIST_LAST - j];
                 const uint32_t pos = e & 1023u, len = e >> 10;
                 const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
@@ -438,7 +454,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             nq += min(32u, n_med - t0);
             __syncwarp();
             MT(3); // medium tokens: key build + queue
-            if (nq >= 32) { drain32(); while (nq >= 64) drain32(); MT(4); }
+            if (nq >= 32) { drain32(); while (nq >= GQ_KEEP) drain32(); MT(4); }
         }
         if (inserted) atomicAdd(&tused, inserted);
         __syncwarp();
@@ -454,7 +470,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
     MT_END;
     for (int d = 16; d; d >>= 1) my_tokens += __shfl_xor_sync(0xFFFFFFFFu, my_tokens, d);
     if (lane == 0 && my_tokens) atomicAdd(p.tokens, my_tokens);
+#ifdef MRGPU_MAP_TIMING
+    const long long mt_k1 = clock64();
+#endif
     __syncthreads();
+#ifdef MRGPU_MAP_TIMING
+    const long long mt_k2 = clock64();
+#endif
 #ifdef MRGPU_V_ONEBYTE
     for (uint32_t i = tid; i < 256; i += WARPS * 32)
         if (c1[i]) {
@@ -474,6 +496,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) map_combine_kernel(MapParams p)
             gtable_add(p.gtab, p.gmask, p.arena, k, tcnt[i], p.err);
         }
     }
+#ifdef MRGPU_MAP_TIMING
+    if (blockIdx.x == 7 && warp == 5 && lane == 0) {
+        p.dbg[9] = mt_k2 - mt_k1;            // waiting for the CTA's other warps
+        p.dbg[10] = clock64() - mt_k2;       // this warp's share of the flush
+        p.dbg[11] = tused;
+    }
+#endif
 }
 
 } // namespace mr

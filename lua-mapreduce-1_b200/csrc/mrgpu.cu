@@ -420,6 +420,8 @@ cudaError_t launch_map(mr_ctx *ctx, const MapParams &p)
     cudaError_t ea = cudaFuncSetAttribute(map_combine_kernel<WARPS, LOG2>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (ea != cudaSuccess) return ea;
+    if (const char *cv = getenv("MRGPU_MAP_CARVEOUT"))   // measurement switch: % of the SM's 228 KB kept as shared memory
+        cudaFuncSetAttribute(map_combine_kernel<WARPS, LOG2>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(cv));
     int ctas_per_sm = (int)(227 * 1024 / (smem + 1024));
     ctas_per_sm = std::max(1, std::min(ctas_per_sm, 2048 / (WARPS * 32)));
     uint64_t nwarps_needed = p.nseg;
@@ -834,7 +836,11 @@ static int run_map_round(mr_ctx *ctx)
         case 1: e = launch_map<16, 12>(ctx, p); break;
         case 2: e = launch_map<16, 13>(ctx, p); break;
         case 3: e = launch_map<32, 12>(ctx, p); break;
+#ifdef MRGPU_V_WARPS
+        default: e = launch_map<MRGPU_V_WARPS, MRGPU_V_LOG2>(ctx, p); break;
+#else
         default: e = launch_map<32, 13>(ctx, p); break;
+#endif
         }
         if (e != cudaSuccess) return fail(ctx, MR_ERR_CUDA, "map kernel launch: %s", cudaGetErrorString(e));
     }

@@ -16,3 +16,5 @@ names = ["1 loads+stage+mask", "2 starts/classes/scan/lists", "3a short: key+CTA
 tot = sum(st)
 for nme, v in zip(names, st): print(f"{nme:30s} {v:10d} cycles {v / tot * 100:5.1f}%")
 print("total", tot, "cycles =", tot / 1.965e3, "us")
+x = [d[i] for i in range(8, 12)]
+print(f"table init {x[0]} cycles; wait for the CTA's other warps {x[1]}; flush (this warp) {x[2]}; keys in the CTA table {x[3]}")

@@ -17,7 +17,20 @@ VARIANTS = {
     "directmed": ["-DMRGPU_V_DIRECTMED"],
     "all3": ["-DMRGPU_V_PLAINLDS", "-DMRGPU_V_ONEBYTE", "-DMRGPU_V_DIRECTMED"],
     "asyncclaim": ["-DMRGPU_V_ASYNCCLAIM"],
+    # warps per SM (registers per thread follow from the launch bound) x CTA-table size
+        "w32_12": ["-DMRGPU_V_WARPS=32", "-DMRGPU_V_LOG2=12"],
+    "w32_11": ["-DMRGPU_V_WARPS=32", "-DMRGPU_V_LOG2=11"],
+    "w32_10": ["-DMRGPU_V_WARPS=32", "-DMRGPU_V_LOG2=10"],
+    "w24_12": ["-DMRGPU_V_WARPS=24", "-DMRGPU_V_LOG2=12"],
+    "w16_12x2": ["-DMRGPU_V_WARPS=16", "-DMRGPU_V_LOG2=12", "-DMRGPU_V_CTAS=2"],
+    "w16_11x2": ["-DMRGPU_V_WARPS=16", "-DMRGPU_V_LOG2=11", "-DMRGPU_V_CTAS=2"],
+    "w20_12x2": ["-DMRGPU_V_WARPS=20", "-DMRGPU_V_LOG2=12", "-DMRGPU_V_CTAS=2"],
+    "w20_11x2": ["-DMRGPU_V_WARPS=20", "-DMRGPU_V_LOG2=11", "-DMRGPU_V_CTAS=2"],
+    "w24_11x2": ["-DMRGPU_V_WARPS=24", "-DMRGPU_V_LOG2=11", "-DMRGPU_V_CTAS=2"],
+    "w24_10x2": ["-DMRGPU_V_WARPS=24", "-DMRGPU_V_LOG2=10", "-DMRGPU_V_CTAS=2"],
 }
+if os.environ.get("MAP_VARIANTS"):
+    VARIANTS = {k: VARIANTS[k] for k in os.environ["MAP_VARIANTS"].split(",")}
 
 
 def build():
@@ -25,6 +38,9 @@ def build():
     os.makedirs(OUT, exist_ok=True)
     srcs, _ = b.gpu_sources()
     for name, flags in VARIANTS.items():
+        want = [("32", "13")]
+        if any("V_WARPS" in f for f in flags):
+            want = [(flags[0].split("=")[1], flags[1].split("=")[1])]
         lib = os.path.join(OUT, f"libmrgpu_{name}.so")
         cmd = [b._nvcc()] + b.NVCC_FLAGS + flags + ["-Xptxas=-v", "-o", lib] + srcs
         r = subprocess.run(cmd, capture_output=True, text=True)
@@ -32,7 +48,7 @@ def build():
             print(r.stderr[-3000:]); raise SystemExit(1)
         lines = r.stderr.splitlines()
         for i, l in enumerate(lines):
-            if "map_combine_kernelILi32ELi13" in l and "Compiling" in l:
+            if "map_combine_kernel" in l and "Compiling" in l and any(f"ILi{w}ELi{g}E" in l for w, g in want):
                 print(name, "|", lines[i + 2].strip(), "|", lines[i + 1].strip())
 
 
