@@ -27,6 +27,13 @@
 #pragma once
 #include "common.cuh"
 
+// Measured variants (scripts/map_variants.py, profiles/r02/map_variants_*.txt).  On by default: full
+// batches of medium tokens go from registers straight into flight (-1.1 %); -DMRGPU_V_QUEUEMED restores
+// the trip through the per-warp queue.
+#if !defined(MRGPU_V_QUEUEMED) && !defined(MRGPU_V_DIRECTMED)
+#define MRGPU_V_DIRECTMED 1
+#endif
+
 namespace mr {
 
 constexpr int SEG = 1024;              // bytes per warp segment

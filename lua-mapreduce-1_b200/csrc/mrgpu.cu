@@ -1063,11 +1063,14 @@ int launch_msd(mr_ctx *ctx)
     cudaStream_t s = ctx->stream;
     using SmemD = UnitSmem<UNIT_CAP_DISTINCT>;
     using SmemS = UnitSmem<UNIT_CAP_SHUFFLED>;
-    static_assert(sizeof(SmemD) <= 56 * 1024 - 512, "four units per SM");
-    static_assert(sizeof(SmemS) <= 75 * 1024 - 256, "three units per SM");
+    static_assert(4 * (sizeof(SmemD) + 1024) <= 196 * 1024, "four units per SM in the 196 KB shared-memory configuration");
+    static_assert(3 * (sizeof(SmemS) + 1024) <= 196 * 1024, "three units per SM in the 196 KB shared-memory configuration");
     CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
-    CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_DISTINCT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemD)));
-    CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_SHUFFLED, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemS)));
+    // measurement switches: unused shared memory added to a unit's block (fewer units per SM, smaller carveout)
+    static const size_t pad_d = getenv("MRGPU_UNIT_PAD_D") ? (size_t)atoi(getenv("MRGPU_UNIT_PAD_D")) : 0;
+    static const size_t pad_s = getenv("MRGPU_UNIT_PAD_S") ? (size_t)atoi(getenv("MRGPU_UNIT_PAD_S")) : 0;
+    CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_DISTINCT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(SmemD) + pad_d)));
+    CU(cudaFuncSetAttribute(msd_unit_kernel<UNIT_CAP_SHUFFLED, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(SmemS) + pad_s)));
     // no shuffle: the items are the table's entries, one per distinct key, so every item becomes a row
     // (the compaction kernel left the key lengths in d_ties, which only the LSD path's tie kernels use)
     const bool distinct = !ctx->imported && getenv("MRGPU_MSD_LOOKBACK") == nullptr;
@@ -1081,11 +1084,11 @@ int launch_msd(mr_ctx *ctx)
         (small_units ? UNIT_CAP_DISTINCT : UNIT_CAP_SHUFFLED) - UNIT_W);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;
     if (small_units)
-        msd_unit_kernel<UNIT_CAP_DISTINCT, 4><<<units, UNIT_THREADS, sizeof(SmemD), s>>>(
+        msd_unit_kernel<UNIT_CAP_DISTINCT, 4><<<units, UNIT_THREADS, sizeof(SmemD) + pad_d, s>>>(
             (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
             ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb, distinct);
     else
-        msd_unit_kernel<UNIT_CAP_SHUFFLED, 3><<<units, UNIT_THREADS, sizeof(SmemS), s>>>(
+        msd_unit_kernel<UNIT_CAP_SHUFFLED, 3><<<units, UNIT_THREADS, sizeof(SmemS) + pad_s, s>>>(
             (const MsdItem *)ctx->bufs.item[1], ctx->ent, ctx->bytes_base, ctx->rows, ctx->cfg.num_reducers,
             ctx->cfg.reduce_kind, ctx->key_bytes_cap - 64, ctx->rows_st, ctx->d_ctl, mb, distinct);
     ctx->stats.launches += 3;

@@ -42,7 +42,6 @@ constexpr uint32_t UNIT_W = 512;             // a unit owns the bins that start 
 constexpr uint32_t UNIT_CAP_DISTINCT = 1024, UNIT_CAP_SHUFFLED = 1536;
 constexpr int UNIT_THREADS = 256;
 constexpr int UNIT_WARPS = UNIT_THREADS / 32;
-constexpr uint32_t UNIT_STAGE = 12 * 1024 - 16;   // key bytes of a unit staged for coalesced stores (more: written directly)
 #ifndef MRGPU_COUNT_SORT_MAX
 #define MRGPU_COUNT_SORT_MAX 48
 #endif
@@ -335,7 +334,6 @@ struct __align__(16) UnitSmem {
     unsigned int whist[UNIT_CAP * 2 > UNIT_WARPS * RADIX_BINS ? UNIT_CAP * 2 : UNIT_WARPS * RADIX_BINS]; // bin extents, per-warp digit counts [UNIT_WARPS][RADIX_BINS], afterwards the values of the items
     unsigned int bin_excl[RADIX_BINS];
     unsigned int scan_tmp[RADIX_BINS / 32];
-    uint8_t stage[UNIT_STAGE + 16];              // key bytes of the unit's rows, back to back from offset 0
     unsigned int wh[UNIT_WARPS];
     unsigned long long wb[UNIT_WARPS];
     unsigned long long prefix_h, prefix_b;
@@ -739,12 +737,17 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
     }
     // the unit's key bytes are laid out in shared memory now (offsets inside the unit are known; where the
     // unit starts in the output is not yet), so that this work overlaps the wait for the units before
+    // (staged in the buffer that held the keys: every thread has its keys in registers since the barrier
+    // after the heads' stores.  Four units of 1024 / three of 1536 items then fit the SM's 196 KB
+    // shared-memory configuration -- the 228 KB one slows shared-memory accesses, see map_kernel.cuh.)
+    uint8_t *stage = (uint8_t *)skey;
+    constexpr uint32_t UNIT_STAGE = UNIT_CAP * 16 - 16;   // more key bytes than that: written directly
     const bool staged = !declined && tb <= UNIT_STAGE;
     if (staged) {
         unsigned long long lb = ob;
 #pragma unroll
         for (int j = 0; j < UNIT_ITEMS; ++j)
-            if ((headmask >> j) & 1u) { write_key_bytes(sm.stage + (uint32_t)lb, key[j], len[j], bytes); lb += len[j]; }
+            if ((headmask >> j) & 1u) { write_key_bytes(stage + (uint32_t)lb, key[j], len[j], bytes); lb += len[j]; }
     }
     UT(6);
     // jobs after a shuffle (the same key may have arrived from several ranks): the unit knows its rows
@@ -803,14 +806,14 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
         const uint32_t mis = (uint32_t)(unit_b0 & 15);
         uint8_t *dst = rows.key_bytes + (unit_b0 - mis);                       // 16-byte aligned
         const uint32_t end = mis + (uint32_t)tb;                               // in dst coordinates
-        const uint32_t *sw = (const uint32_t *)sm.stage;
+        const uint32_t *sw = (const uint32_t *)stage;
         for (uint32_t cb = tid * 16; cb < end; cb += UNIT_THREADS * 16) {
             if (cb >= mis && cb + 16 <= end) {
                 const uint32_t so = cb - mis, wi = so >> 2, sh = (so & 3) * 8;
                 const uint32_t x0 = sw[wi], x1 = sw[wi + 1], x2 = sw[wi + 2], x3 = sw[wi + 3], x4 = sw[wi + 4];
                 *(uint4 *)(dst + cb) = make_uint4(funnel_r(x0, x1, sh), funnel_r(x1, x2, sh), funnel_r(x2, x3, sh), funnel_r(x3, x4, sh));
             } else {
-                for (uint32_t q = cb < mis ? mis : cb; q < cb + 16 && q < end; ++q) dst[q] = sm.stage[q - mis];
+                for (uint32_t q = cb < mis ? mis : cb; q < cb + 16 && q < end; ++q) dst[q] = stage[q - mis];
             }
         }
     }

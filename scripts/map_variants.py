@@ -14,8 +14,8 @@ VARIANTS = {
     "base": [],
     "plainlds": ["-DMRGPU_V_PLAINLDS"],
     "onebyte": ["-DMRGPU_V_ONEBYTE"],
-    "directmed": ["-DMRGPU_V_DIRECTMED"],
-    "all3": ["-DMRGPU_V_PLAINLDS", "-DMRGPU_V_ONEBYTE", "-DMRGPU_V_DIRECTMED"],
+    "queuemed": ["-DMRGPU_V_QUEUEMED"],
+    "plainlds_onebyte": ["-DMRGPU_V_PLAINLDS", "-DMRGPU_V_ONEBYTE"],
     "asyncclaim": ["-DMRGPU_V_ASYNCCLAIM"],
     # warps per SM (registers per thread follow from the launch bound) x CTA-table size
         "w32_12": ["-DMRGPU_V_WARPS=32", "-DMRGPU_V_LOG2=12"],
