@@ -1006,11 +1006,27 @@ int mr_map_finish(mr_ctx *ctx)
 
 namespace {
 
+// The two kernels that read the whole table out (compaction, p2p sender) are streaming reads whose tiles
+// sit in ~33-38 KB of shared memory per CTA.  Eight CTAs per SM would put the SM in its 228 KB
+// shared-memory configuration, whose 28 KB of L1 cannot hold the loads in flight: 64 MB then stream at
+// 2.7 TB/s.  Four persistent CTAs per SM in the 164 KB configuration (92 KB of L1) read it 8 us faster
+// (profiles/r02/compact_carveout.txt).  MRGPU_COMPACT_CARVEOUT / MRGPU_COMPACT_PER_SM: measurement switches.
+void table_reader_config(const void *kernel, unsigned *per_sm)
+{
+    int carveout = 72;
+    *per_sm = 4;
+    if (const char *cv = getenv("MRGPU_COMPACT_CARVEOUT")) carveout = atoi(cv);
+    if (const char *g = getenv("MRGPU_COMPACT_PER_SM")) *per_sm = (unsigned)std::max(1, atoi(g));
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+}
+
 // table -> entries with partition ids and owner ranks, sort items, varying-bit masks: one kernel
 int launch_compact(mr_ctx *ctx)
 {
     const uint64_t tiles = (ctx->slots + 256 * COMPACT_ITEMS - 1) / (256 * COMPACT_ITEMS);
-    unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
+    unsigned per_sm;
+    table_reader_config((const void *)compact_partition_kernel, &per_sm);
+    unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * per_sm);
     compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(
         ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
         ctx->bufs.item[0], ctx->max_keys, ctx->d_ctl, ctx->owners(), (uint32_t *)ctx->d_ties);
@@ -1824,7 +1840,9 @@ int mr_shuffle_p2p(mr_ctx *ctx)
     p.slot_bytes = ctx->p2p_slot;
     p.epoch = epoch;
     const uint64_t tiles = (ctx->slots + 256 * P2P_SEND_ITEMS - 1) / (256 * P2P_SEND_ITEMS);
-    const unsigned g = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * 8);
+    unsigned per_sm;
+    table_reader_config((const void *)p2p_send_kernel, &per_sm);
+    const unsigned g = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * per_sm);
     const size_t dyn = 24ull * W;
     if (dyn > 8192) CU(cudaFuncSetAttribute(p2p_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
     p2p_send_kernel<<<g, 256, dyn, s>>>(p, ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind,
