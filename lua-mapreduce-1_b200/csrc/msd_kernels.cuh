@@ -613,9 +613,8 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
     UT(4);
     // ---- keys that agree in the whole sort word and have 8+ bytes are ordered by their later bytes.
     // First every item says (iflag) whether it continues its predecessor's sort word (1) and, if so,
-    // whether it is another key (2); only groups that hold different keys are ordered -- by their first
-    // member, in place (insertion sort, full-key compares out of shared memory).  Copies of one key,
-    // which is what a shuffle delivers most, cost one 16-byte compare each.
+    // whether it is another key (2); only groups that hold different keys are ordered.  Copies of one
+    // key, which is what a shuffle delivers most, cost one 16-byte compare each.
     unsigned char *iflag = sm.iflag;
     auto same_key_at = [&](uint32_t x, uint32_t y) {
         const ulonglong2 ka = skey[x], kb = skey[y];
@@ -633,27 +632,48 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
         iflag[i] = (unsigned char)f;
     }
     __syncthreads();
-    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {
+    for (uint32_t i = tid; i < m; i += UNIT_THREADS) {       // first members: does the group hold different keys?
         if ((iflag[i] & 1) || !(sorted[i].bin & MSD_FLAG8)) continue;
         uint32_t g = 1, need = 0;
         while (i + g < m && g <= MSD_TIE_GROUP && (iflag[i + g] & 1)) { need |= iflag[i + g] & 2u; ++g; }
         if (g > MSD_TIE_GROUP) { atomicOr(&ctl->msd_fallback, MSD_FB_TIES); sm.fallback = 1; continue; }
         if (!need) continue;
-        for (uint32_t a2 = 1; a2 < g; ++a2) {
-            const ulonglong2 kx2 = skey[i + a2];
-            Key kx; kx.k0 = kx2.x; kx.k1 = kx2.y;
-            const unsigned long long cx = scnt[i + a2];
-            const uint32_t px = sorted[i + a2].val;
-            uint32_t b2 = a2;
-            while (b2 > 0) {
-                Key kb; kb.k0 = skey[i + b2 - 1].x; kb.k1 = skey[i + b2 - 1].y;
-                if (!key_less(kx, kb, 1, 0, bytes, 1)) break;      // equal keys: "not less", so they stay
-                skey[i + b2] = skey[i + b2 - 1]; scnt[i + b2] = scnt[i + b2 - 1]; sorted[i + b2].val = sorted[i + b2 - 1].val;
-                --b2;
-            }
-            if (b2 != a2) { skey[i + b2] = kx2; scnt[i + b2] = cx; sorted[i + b2].val = px; }
-        }
+        for (uint32_t a2 = 0; a2 < g; ++a2) iflag[i + a2] |= 8u;           // the members order themselves below
         atomicAdd(&ctl->tie_small, 1u);
+    }
+    __syncthreads();
+    // Every member of such a group counts the members that come before it in the full order (g whole-key
+    // compares, all members at once -- not g^2 / 2 by one thread), takes key, value and partition into
+    // registers, and after the barrier stores them at group begin + count.
+    {
+        ulonglong2 mk[UNIT_ITEMS];
+        unsigned long long mc[UNIT_ITEMS];
+        uint32_t mv[UNIT_ITEMS], md[UNIT_ITEMS];
+#pragma unroll
+        for (int r = 0; r < UNIT_ITEMS; ++r) {
+            const uint32_t i = tid + (uint32_t)r * UNIT_THREADS;
+            md[r] = 0xFFFFFFFFu;
+            mk[r] = make_ulonglong2(0, 0); mc[r] = 0; mv[r] = 0;
+            if (i >= m || !(iflag[i] & 8u)) continue;
+            uint32_t s0 = i;
+            while (iflag[s0] & 1) --s0;
+            uint32_t g = 1;
+            while (s0 + g < m && (iflag[s0 + g] & 1)) ++g;              // <= MSD_TIE_GROUP, checked above
+            const ulonglong2 kx2 = skey[i];
+            Key kx; kx.k0 = kx2.x; kx.k1 = kx2.y;
+            uint32_t rank = 0;
+            for (uint32_t a2 = 0; a2 < g; ++a2) {
+                const uint32_t j = s0 + a2;
+                if (j == i) continue;
+                Key kb; kb.k0 = skey[j].x; kb.k1 = skey[j].y;
+                rank += key_less(kb, kx, j, i, bytes, 1) ? 1u : 0u;     // equal keys keep their order
+            }
+            if (s0 + rank != i) { md[r] = s0 + rank; mk[r] = kx2; mc[r] = scnt[i]; mv[r] = sorted[i].val; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < UNIT_ITEMS; ++r)
+            if (md[r] != 0xFFFFFFFFu) { skey[md[r]] = mk[r]; scnt[md[r]] = mc[r]; sorted[md[r]].val = mv[r]; }
     }
     __syncthreads();
     // a unit that declined still takes part in the look-back below (with nothing), so that no later

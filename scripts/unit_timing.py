@@ -3,8 +3,8 @@
 import ctypes as C, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 OUT = os.path.join(ROOT, "build", "variants")
-UNITS = [3, 150, 290, 300, 420, 505]
-NAMES = ["start", "ticket+range", "load", "sort", "ties", "gather", "heads+scan", "look-back", "rows", "copy-out"]
+UNITS = [5, 300, 590, 700, 1000]
+NAMES = ["start", "ticket+range", "load", "sort", "gather", "ties", "heads+merge+stage", "look-back", "rows", "copy-out"]
 
 def build():
     from lua_mapreduce_1_b200 import build as b
