@@ -313,6 +313,7 @@ struct mr_ctx {
     MsdBins *d_msd = nullptr; // [2], alternating by job (msd_kernels.cuh)
     uint32_t msd_parity = 0;
     bool prefer_lsd = false;  // MRGPU_REDUCE=lsd: always the LSD path
+    unsigned reader_configured = 0; // bit 0 / 1: shared-memory carveout of the compaction / p2p sender set on this device
     uint32_t lsd_jobs_left = 0; // non-zero: the MSD path declined a job of this context; its jobs take the LSD path at once until the owners change
     bool used_msd = false;    // this job's reduce side was launched on the MSD path
     unsigned long long *h_stage = nullptr; // pinned, [MAX_WORLD + 1]
@@ -1011,13 +1012,14 @@ namespace {
 // shared-memory configuration, whose 28 KB of L1 cannot hold the loads in flight: 64 MB then stream at
 // 2.7 TB/s.  Four persistent CTAs per SM in the 164 KB configuration (92 KB of L1) read it 8 us faster
 // (profiles/r02/compact_carveout.txt).  MRGPU_COMPACT_CARVEOUT / MRGPU_COMPACT_PER_SM: measurement switches.
-void table_reader_config(const void *kernel, unsigned *per_sm)
+void table_reader_config(mr_ctx *ctx, unsigned which, const void *kernel, unsigned *per_sm)
 {
-    int carveout = 72;
-    *per_sm = 4;
-    if (const char *cv = getenv("MRGPU_COMPACT_CARVEOUT")) carveout = atoi(cv);
-    if (const char *g = getenv("MRGPU_COMPACT_PER_SM")) *per_sm = (unsigned)std::max(1, atoi(g));
+    static const int carveout = getenv("MRGPU_COMPACT_CARVEOUT") ? atoi(getenv("MRGPU_COMPACT_CARVEOUT")) : 72;
+    static const unsigned ctas = getenv("MRGPU_COMPACT_PER_SM") ? (unsigned)std::max(1, atoi(getenv("MRGPU_COMPACT_PER_SM"))) : 4u;
+    *per_sm = ctas;
+    if (ctx->reader_configured & (1u << which)) return;   // the attribute sticks (per kernel and device): once per context
     cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+    ctx->reader_configured |= 1u << which;
 }
 
 // table -> entries with partition ids and owner ranks, sort items, varying-bit masks: one kernel
@@ -1025,7 +1027,7 @@ int launch_compact(mr_ctx *ctx)
 {
     const uint64_t tiles = (ctx->slots + 256 * COMPACT_ITEMS - 1) / (256 * COMPACT_ITEMS);
     unsigned per_sm;
-    table_reader_config((const void *)compact_partition_kernel, &per_sm);
+    table_reader_config(ctx, 0, (const void *)compact_partition_kernel, &per_sm);
     unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * per_sm);
     compact_partition_kernel<<<grid, 256, 0, ctx->stream>>>(
         ctx->d_gtab, ctx->slots, ctx->bytes_base, ctx->cfg.num_reducers, ctx->cfg.partition_kind, ctx->ent,
@@ -1841,7 +1843,7 @@ int mr_shuffle_p2p(mr_ctx *ctx)
     p.epoch = epoch;
     const uint64_t tiles = (ctx->slots + 256 * P2P_SEND_ITEMS - 1) / (256 * P2P_SEND_ITEMS);
     unsigned per_sm;
-    table_reader_config((const void *)p2p_send_kernel, &per_sm);
+    table_reader_config(ctx, 1, (const void *)p2p_send_kernel, &per_sm);
     const unsigned g = (unsigned)std::min<uint64_t>(tiles, (uint64_t)ctx->sm_count * per_sm);
     const size_t dyn = 24ull * W;
     if (dyn > 8192) CU(cudaFuncSetAttribute(p2p_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
