@@ -661,12 +661,25 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
             while (s0 + g < m && (iflag[s0 + g] & 1)) ++g;              // <= MSD_TIE_GROUP, checked above
             const ulonglong2 kx2 = skey[i];
             Key kx; kx.k0 = kx2.x; kx.k1 = kx2.y;
+            // two inline keys (<= 15 bytes, the usual case) that agree in bytes 0..6: bytes 7..14 as one
+            // big-endian word (zero-padded), then the length -- the order key_less gives, in ten instructions
+            const bool x_inline = !key_is_long(kx);
+            const unsigned long long rx = bswap64((kx.k0 >> 56) | ((kx.k1 & LOW56) << 8));
+            const uint32_t lx = (uint32_t)(kx.k1 >> 56);
             uint32_t rank = 0;
             for (uint32_t a2 = 0; a2 < g; ++a2) {
                 const uint32_t j = s0 + a2;
                 if (j == i) continue;
                 Key kb; kb.k0 = skey[j].x; kb.k1 = skey[j].y;
-                rank += key_less(kb, kx, j, i, bytes, 1) ? 1u : 0u;     // equal keys keep their order
+                bool less;                                              // kb before kx; equal keys keep their order
+                if (x_inline && !key_is_long(kb)) {
+                    const unsigned long long rb = bswap64((kb.k0 >> 56) | ((kb.k1 & LOW56) << 8));
+                    const uint32_t lb = (uint32_t)(kb.k1 >> 56);
+                    less = rb < rx || (rb == rx && (lb < lx || (lb == lx && j < i)));
+                } else {
+                    less = key_less(kb, kx, j, i, bytes, 1);
+                }
+                rank += less ? 1u : 0u;
             }
             if (s0 + rank != i) { md[r] = s0 + rank; mk[r] = kx2; mc[r] = scnt[i]; mv[r] = sorted[i].val; }
         }

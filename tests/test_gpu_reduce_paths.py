@@ -91,6 +91,21 @@ def test_small_tie_groups_are_ordered_inside_the_unit():
     assert_rows_equal(rows, O.run_naive([text], 10), "small tie groups")
 
 
+def test_tie_groups_with_nul_bytes_prefixes_and_the_inline_limit():
+    # one 7-byte prefix, then every awkward tail: none, NUL bytes (a zero-padded compare must still put
+    # the shorter key first), one key a prefix of the next, tails that end exactly at 14 and 15 bytes
+    # (the last inline length) and a 16+-byte key (kept by reference) -- all in one group, both paths
+    rnd = random.Random(5)
+    tails = [b"", b"\x00", b"\x00\x00", b"a", b"a\x00", b"a\x00b", b"ab", b"abc", b"b", b"\xff", b"\xff\x00",
+             b"1234567", b"12345670", b"1234567\x00", b"1234568", b"12345678", b"123456789abcdef", b"z" * 30]
+    keys = [b"PREFIX_" + t for t in tails] + [b"prefix2" + bytes([c]) * n for c in (0, 1, 255) for n in range(1, 9)]
+    text = b" ".join(rnd.choice(keys) for _ in range(6000))
+    both([text], 10)
+    both([text, text[::-1]], 3)
+    # the same keys arriving in copies (what an owner sees after a shuffle): two jobs' worth in one split list
+    both([text] * 3, 10)
+
+
 def test_large_tie_groups_make_the_shared_memory_path_decline():
     # ~250 keys per partition agree in their first 7 bytes: more than a unit orders by itself (64)
     rnd = random.Random(2)
