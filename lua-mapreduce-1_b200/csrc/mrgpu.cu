@@ -1083,7 +1083,7 @@ int launch_msd(mr_ctx *ctx)
     using SmemS = UnitSmem<UNIT_CAP_SHUFFLED>;
     static_assert(4 * (sizeof(SmemD) + 1024) <= 196 * 1024, "four units per SM in the 196 KB shared-memory configuration");
     static_assert(3 * (sizeof(SmemS) + 1024) <= 196 * 1024, "three units per SM in the 196 KB shared-memory configuration");
-    CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((MSD_MAX_BINS + 4) * 4)));
+    CU(cudaFuncSetAttribute(msd_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MSD_SCATTER_SMEM));
     // measurement switches: unused shared memory added to a unit's block (fewer units per SM, smaller carveout)
     static const size_t pad_d = getenv("MRGPU_UNIT_PAD_D") ? (size_t)atoi(getenv("MRGPU_UNIT_PAD_D")) : 0;
     static const size_t pad_s = getenv("MRGPU_UNIT_PAD_S") ? (size_t)atoi(getenv("MRGPU_UNIT_PAD_S")) : 0;
@@ -1097,7 +1097,7 @@ int launch_msd(mr_ctx *ctx)
     ctx->msd_parity ^= 1;
     msd_hist_kernel<<<grid_for(ctx->max_keys, 256 * 4, ctx->sm_count * 4), 256, 0, s>>>(
         ctx->bufs.item[0], ctx->max_keys, ctx->cfg.num_reducers, ctx->d_ctl, mb, other, ctx->d_posv, ctx->rows_st, ctx->rows_tiles);
-    msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024 * 4, ctx->sm_count), 1024, (MSD_MAX_BINS + 4) * 4, s>>>(
+    msd_scatter_kernel<<<grid_for(ctx->max_keys, 1024 * 4, ctx->sm_count), 1024, MSD_SCATTER_SMEM, s>>>(
         ctx->bufs.item[0], ctx->d_posv, (MsdItem *)ctx->bufs.item[1], ctx->d_ctl, mb, distinct ? (const uint32_t *)ctx->d_ties : nullptr,
         (small_units ? UNIT_CAP_DISTINCT : UNIT_CAP_SHUFFLED) - UNIT_W);
     const unsigned units = (unsigned)((ctx->max_keys + UNIT_W - 1) / UNIT_W) + 1;

@@ -34,6 +34,8 @@ namespace mr {
 
 constexpr int MSD_MAX_BITS = 15;
 constexpr uint32_t MSD_MAX_BINS = 1u << MSD_MAX_BITS;
+#define MSD_PAD(b) ((b) + ((b) >> 5))                              // index of bin b in the scatter kernel's shared-memory table
+constexpr uint32_t MSD_SCATTER_SMEM = (MSD_MAX_BINS + MSD_MAX_BINS / 32 + 8) * 4;
 constexpr uint32_t MSD_TARGET_BIN = 8;       // items per bin aimed at (a bin may hold up to the unit size - UNIT_W: room for 64x skew)
 constexpr uint32_t UNIT_W = 512;             // a unit owns the bins that start inside its 512 positions
 // ... so it holds fewer than UNIT_W + largest bin items.  Two sizes of unit: jobs without a shuffle
@@ -247,7 +249,9 @@ __global__ void __launch_bounds__(256) msd_hist_kernel(const SortItem *items, un
 __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items, const uint32_t *tags, MsdItem *out, Ctl *ctl,
                                                            MsdBins *mb, const uint32_t *lens, uint32_t max_bin)
 {
-    extern __shared__ unsigned int msd_start[];    // [bins + 1]
+    // [bins + 1], one pad word per 32 (MSD_PAD): a thread's run of consecutive bins would otherwise hit one
+    // bank with every lane (with 30 K bins -- an owner's share after a shuffle -- the scan took 25 us)
+    extern __shared__ unsigned int msd_start[];
     __shared__ unsigned int wsum[32];
     __shared__ unsigned int s_big;
     __shared__ MsdPlan plan;
@@ -263,11 +267,14 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
     // exclusive scan of the histogram: 1024 threads x (bins / 1024) consecutive bins each
     const uint32_t per = (bins + 1023) / 1024;
     const uint32_t b0 = threadIdx.x * per;
+    // the histogram comes in with coalesced loads; each thread then takes its consecutive bins from shared memory
+    for (uint32_t b = threadIdx.x; b < bins; b += 1024) msd_start[MSD_PAD(b)] = mb->hist[b];
+    __syncthreads();
     unsigned int c[MSD_MAX_BINS / 1024];
     unsigned int sum = 0, big = 0;
 #pragma unroll
     for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k) {
-        c[k] = (k < per && b0 + k < bins) ? mb->hist[b0 + k] : 0;
+        c[k] = (k < per && b0 + k < bins) ? msd_start[MSD_PAD(b0 + k)] : 0;
         sum += c[k];
         big = max(big, c[k]);
     }
@@ -283,8 +290,8 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
     unsigned int run = woff + incl - sum;
 #pragma unroll
     for (uint32_t k = 0; k < MSD_MAX_BINS / 1024; ++k)
-        if (k < per && b0 + k < bins) { msd_start[b0 + k] = run; run += c[k]; }
-    if (threadIdx.x == 0) msd_start[bins] = (unsigned int)n;
+        if (k < per && b0 + k < bins) { msd_start[MSD_PAD(b0 + k)] = run; run += c[k]; }
+    if (threadIdx.x == 0) msd_start[MSD_PAD(bins)] = (unsigned int)n;
     __syncthreads();
     if (s_big) {                                    // every CTA sees the same histogram and takes the same way out
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&ctl->msd_fallback, MSD_FB_BIN);
@@ -292,13 +299,13 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
     }
     {
         const uint32_t g0 = blockIdx.x * blockDim.x + threadIdx.x, gs = gridDim.x * blockDim.x;
-        for (uint32_t i = g0; i <= bins; i += gs) mb->bin_start[i] = msd_start[i];
+        for (uint32_t i = g0; i <= bins; i += gs) mb->bin_start[i] = msd_start[MSD_PAD(i)];
         // unit u owns the bins from the first one that starts at or after u * UNIT_W: bin b is that
         // first bin for every u with start[b-1] < u * UNIT_W <= start[b]
         const uint32_t nunits = (uint32_t)((n + UNIT_W - 1) / UNIT_W);
         for (uint32_t b = g0; b <= bins; b += gs) {
-            const uint32_t hi = msd_start[b] / UNIT_W;                                  // last u with u * W <= start[b]
-            const uint32_t lo = b == 0 ? 0u : (msd_start[b - 1] + UNIT_W) / UNIT_W;      // first u with u * W > start[b-1] ... (start[b-1] / W) + 1
+            const uint32_t hi = msd_start[MSD_PAD(b)] / UNIT_W;                                  // last u with u * W <= start[b]
+            const uint32_t lo = b == 0 ? 0u : (msd_start[MSD_PAD(b - 1)] + UNIT_W) / UNIT_W;      // first u with u * W > start[b-1] ... (start[b-1] / W) + 1
             for (uint32_t u = lo; u <= hi && u <= nunits; ++u) mb->unit_bin[u] = b;
         }
     }
@@ -322,7 +329,7 @@ __global__ void __launch_bounds__(1024) msd_scatter_kernel(const SortItem *items
             o.val = it[q].val;
             o.bin = d | ((tg[q] & MSD_TAG_FLAG8) ? MSD_FLAG8 : 0u);
             if (lens) o.bin |= min(lens[i0 + q * stride], MSD_LEN_MAX) << MSD_LEN_SHIFT;   // jobs of distinct keys: the key's length rides along
-            out[msd_start[d] + (tg[q] >> 16)] = o;
+            out[msd_start[MSD_PAD(d)] + (tg[q] >> 16)] = o;
         }
     }
 }
