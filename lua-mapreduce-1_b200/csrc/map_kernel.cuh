@@ -446,6 +446,9 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS < 32 ? MRGPU_V_CTAS : 1) map
                 const uint32_t wi = pos >> 2, bs = (pos & 3) * 8;
                 const Key key = medium_key(ws->stage[wi], ws->stage[wi + 1], ws->stage[wi + 2], ws->stage[wi + 3], ws->stage[wi + 4], bs, len);
                 drain_direct(key);
+                // the batch that was in flight may have re-queued up to 32 keys: back below GQ_KEEP before
+                // anything else is appended (the queue holds 63: <= 31 kept + 32 new)
+                while (nq >= GQ_KEEP) drain32();
                 continue;
             }
 #endif
