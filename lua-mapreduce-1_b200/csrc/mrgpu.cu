@@ -589,7 +589,9 @@ int mr_ctx_create(const mr_config *cfg, mr_ctx **out)
     CUC(dmalloc(&ctx->rows.part_begin, (uint64_t)cfg->num_reducers + 1));
     CUC(dmalloc(&ctx->d_ctl, 1));
     CUC(dmalloc(&ctx->d_msd, 2));
-    CUC(cudaMemset(ctx->d_msd, 0, 2 * sizeof(MsdBins)));
+    // on the context's stream: a cudaMemset on the default stream is not ordered against a non-blocking
+    // stream, and the first job's histogram kernel counts into this block
+    CUC(cudaMemsetAsync(ctx->d_msd, 0, 2 * sizeof(MsdBins), ctx->stream));
     if (const char *v = getenv("MRGPU_REDUCE")) ctx->prefer_lsd = strcmp(v, "lsd") == 0;
     CUC(cudaMallocHost((void **)&ctx->h_ctl, sizeof(Ctl)));
     CUC(cudaMallocHost((void **)&ctx->h_stage, (MAX_WORLD + 1) * 8));
@@ -1751,6 +1753,7 @@ int mr_p2p_setup(mr_ctx *ctx, uint64_t slot_bytes, mr_peer_info *mine)
     CU(dmalloc(&ctx->d_p2p_win, W));
     CU(dmalloc(&ctx->d_p2p_done, 1));
     CU(cudaMemset(ctx->d_p2p_done, 0, sizeof(unsigned int)));
+    CU(cudaStreamSynchronize(0)); // both clears have happened before the handle leaves this rank
     ctx->p2p_epoch = 0;
     memset(mine, 0, sizeof *mine);
     mine->pid = (uint64_t)getpid();
