@@ -174,6 +174,20 @@ __host__ __device__ __forceinline__ uint32_t msd_pass_digit(unsigned long long l
     return (uint32_t)v & 0xFFu;
 }
 
+// Two inline keys (<= 15 bytes) that agree in bytes 0..6 and have 8 or more: their order is that of
+// (bytes 7..14 as one big-endian word, zero-padded; then the length) -- what key_less / sort_chunk give
+// round by round, in one compare (checked on the host: tests/test_device_helpers_on_host.py).
+__host__ __device__ __forceinline__ unsigned long long inline_tail_word(const Key &k)
+{
+    return bswap64((k.k0 >> 56) | ((k.k1 & LOW56) << 8));
+}
+__host__ __device__ __forceinline__ bool inline_tail_less(const Key &a, const Key &b, bool a_first_if_equal)
+{
+    const unsigned long long ra = inline_tail_word(a), rb = inline_tail_word(b);
+    const uint32_t la = (uint32_t)(a.k1 >> 56), lb = (uint32_t)(b.k1 >> 56);
+    return ra < rb || (ra == rb && (la < lb || (la == lb && a_first_if_equal)));
+}
+
 // ------------------------------------------------------------------ histogram
 // tag of an item, left by the histogram kernel for the scatter: bin | 8+ bytes flag << 15 | place inside the bin << 16
 constexpr uint32_t MSD_TAG_FLAG8 = 1u << 15;
@@ -671,8 +685,6 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
             // two inline keys (<= 15 bytes, the usual case) that agree in bytes 0..6: bytes 7..14 as one
             // big-endian word (zero-padded), then the length -- the order key_less gives, in ten instructions
             const bool x_inline = !key_is_long(kx);
-            const unsigned long long rx = bswap64((kx.k0 >> 56) | ((kx.k1 & LOW56) << 8));
-            const uint32_t lx = (uint32_t)(kx.k1 >> 56);
             uint32_t rank = 0;
             for (uint32_t a2 = 0; a2 < g; ++a2) {
                 const uint32_t j = s0 + a2;
@@ -680,9 +692,7 @@ __global__ void __launch_bounds__(UNIT_THREADS, MIN_CTAS) msd_unit_kernel(const 
                 Key kb; kb.k0 = skey[j].x; kb.k1 = skey[j].y;
                 bool less;                                              // kb before kx; equal keys keep their order
                 if (x_inline && !key_is_long(kb)) {
-                    const unsigned long long rb = bswap64((kb.k0 >> 56) | ((kb.k1 & LOW56) << 8));
-                    const uint32_t lb = (uint32_t)(kb.k1 >> 56);
-                    less = rb < rx || (rb == rx && (lb < lx || (lb == lx && j < i)));
+                    less = inline_tail_less(kb, kx, j < i);
                 } else {
                     less = key_less(kb, kx, j, i, bytes, 1);
                 }

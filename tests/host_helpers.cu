@@ -179,4 +179,22 @@ uint32_t th_msd_pass_digit(uint64_t low, uint32_t lbin, uint32_t low_bits, uint3
     return msd_pass_digit(low, lbin, low_bits, pass);
 }
 
+// order of two inline keys that agree in bytes 0..6 (msd_kernels.cuh: the tie groups' one-word compare),
+// and the same decision made the long way: sort_chunk round by round as key_less does
+int th_inline_tail_less(uint64_t a0, uint64_t a1, uint64_t b0, uint64_t b1, int a_first_if_equal)
+{
+    Key a, b; a.k0 = a0; a.k1 = a1; b.k0 = b0; b.k1 = b1;
+    return inline_tail_less(a, b, a_first_if_equal != 0) ? 1 : 0;
+}
+int th_rounds_less(uint64_t a0, uint64_t a1, uint64_t b0, uint64_t b1, int a_first_if_equal)
+{
+    Key a, b; a.k0 = a0; a.k1 = a1; b.k0 = b0; b.k1 = b1;
+    for (uint32_t r = 1;; ++r) {
+        const uint64_t ca = sort_chunk(a, nullptr, r), cb = sort_chunk(b, nullptr, r);
+        if (ca != cb) return ca < cb ? 1 : 0;
+        if ((ca & 0xFF) < 8) break;
+    }
+    return a_first_if_equal ? 1 : 0;
+}
+
 } // extern "C"

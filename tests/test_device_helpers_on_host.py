@@ -65,6 +65,9 @@ def lib():
     L.th_msd_extract.argtypes = [C.POINTER(C.c_uint32), C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
     L.th_msd_pass_digit.restype = C.c_uint32
     L.th_msd_pass_digit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
+    for f in (L.th_inline_tail_less, L.th_rounds_less):
+        f.restype = C.c_int
+        f.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int]
     return L
 
 
@@ -306,3 +309,30 @@ def test_msd_plan_bins_and_low_words_order_like_the_keys_and_unit_passes_sort_th
         for p in range(npass):
             order.sort(key=lambda i: lib.th_msd_pass_digit(items[i][1], items[i][0], low_bits, p))
         assert [items[i] for i in order] == sorted(items)
+
+
+def inline_key(b):
+    """(k0, k1) of a key of 1..15 bytes as the kernels hold it: bytes 0..7 little-endian in k0, bytes
+    8..14 in k1's low 56 bits, the length in k1's top byte (common.cuh)."""
+    assert 1 <= len(b) <= 15
+    padded = b + bytes(16 - len(b))
+    return int.from_bytes(padded[:8], "little"), int.from_bytes(padded[8:15], "little") | len(b) << 56
+
+
+def test_one_word_order_of_inline_keys_that_share_seven_bytes(lib):
+    # the tie groups of msd_unit_kernel: keys equal in bytes 0..6, 8..15 bytes long.  The one-compare
+    # order must be the byte order with the shorter key first (Python's bytes order), and must agree with
+    # the round-by-round order key_less takes from sort_chunk -- NUL bytes, prefixes, lengths 14/15 included
+    rnd = random.Random(12)
+    prefix = b"PREFIX_"
+    tails = [b"\x00", b"\x00\x00", b"a", b"a\x00", b"a\x00b", b"ab", b"\xff", b"\xff\x00", b"1234567", b"12345670",
+             b"1234567\x00", b"1234568", b"12345678", b"\x00" * 8, b"\x00" * 7, b"\x00" * 7 + b"\x01"]
+    tails += [bytes(rnd.choice([0, 0, 1, 97, 98, 255]) for _ in range(rnd.randrange(1, 9))) for _ in range(300)]
+    keys = sorted({prefix + t for t in tails})
+    for a in keys:
+        for b in rnd.sample(keys, 40):
+            ka, kb = inline_key(a), inline_key(b)
+            for first in (0, 1):
+                want = a < b or (a == b and bool(first))
+                assert bool(lib.th_inline_tail_less(*ka, *kb, first)) == want, (a, b, first)
+                assert bool(lib.th_rounds_less(*ka, *kb, first)) == want, (a, b, first)
